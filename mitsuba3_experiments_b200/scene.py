@@ -1,0 +1,644 @@
+"""Scene ingestion: Mitsuba-style scene dictionaries -> flat ``b2_scene_desc`` buffers.
+
+The reference's integrators receive a live ``mi.Scene`` (built by ``mi.load_dict`` from dictionaries such
+as ``mi.cornell_box()``, mitsuba3/src/python/python/util.py:568-703).  Our CUDA kernels cannot call back into
+Mitsuba plugins, so this module understands the same dictionary schema for the plugin types on the hot path
+ and flattens it:
+
+* shapes ``rectangle`` (rectangle.cpp:102-176), ``cube`` (cube.cpp:105-163), ``obj`` (obj.cpp subset) and a raw
+  ``mesh`` (explicit arrays) -> world-space vertex/normal/uv/face buffers (Mesh layout, mesh.h:564-568)
+* bsdfs ``diffuse``, ``roughconductor``, ``dielectric``, ``twosided`` (single nested BRDF), ``ref``
+* textures ``rgb`` / plain lists, ``bitmap`` (filename | data array; fp16 storage rule of bitmap.cpp:231-246)
+* emitters ``area``, ``envmap`` (Hierarchical2D pyramid, distr_2d.h:403-509), ``constant``
+* sensor ``perspective`` (perspective.cpp:173-199, sensor.h:229-265, sensor.cpp:147-200), ``hdrfilm``,
+  rfilters ``gaussian`` / ``tent`` / ``box``, sampler ``independent``
+
+Host-side only: no numerics of the render loop live here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import os
+
+import numpy as np
+
+from . import capi
+
+RAY_EPSILON = np.float32(2.0 ** -24 * 1500.0)
+
+
+# ---------------------------------------------------------------------------------------------
+# ScalarTransform4f stand-in (transform.h): chained like ``T().translate(..).rotate(..).scale(..)``
+# ---------------------------------------------------------------------------------------------
+class Transform4f:
+    def __init__(self, matrix=None):
+        self.matrix = np.eye(4, dtype=np.float64) if matrix is None else np.asarray(matrix, dtype=np.float64).reshape(4, 4)
+
+    def __matmul__(self, other):
+        if isinstance(other, Transform4f):
+            return Transform4f(self.matrix @ other.matrix)
+        v = np.asarray(other, dtype=np.float64)
+        r = self.matrix @ np.append(v, 1.0)
+        return r[:3] / r[3]
+
+    def translate(self, v):
+        m = np.eye(4); m[:3, 3] = np.asarray(v, dtype=np.float64)
+        return Transform4f(self.matrix @ m)
+
+    def scale(self, v):
+        v = np.broadcast_to(np.asarray(v, dtype=np.float64), (3,))
+        return Transform4f(self.matrix @ np.diag([v[0], v[1], v[2], 1.0]))
+
+    def rotate(self, axis, angle):
+        a = np.asarray(axis, dtype=np.float64); a = a / np.linalg.norm(a)
+        s, c = math.sin(math.radians(angle)), math.cos(math.radians(angle))
+        x, y, z = a
+        m = np.eye(4)
+        m[:3, :3] = [[x * x + (1 - x * x) * c, x * y * (1 - c) - z * s, x * z * (1 - c) + y * s],
+                     [x * y * (1 - c) + z * s, y * y + (1 - y * y) * c, y * z * (1 - c) - x * s],
+                     [x * z * (1 - c) - y * s, y * z * (1 - c) + x * s, z * z + (1 - z * z) * c]]
+        return Transform4f(self.matrix @ m)
+
+    def look_at(self, origin, target, up):
+        o, t, u = (np.asarray(a, dtype=np.float64) for a in (origin, target, up))
+        d = (t - o) / np.linalg.norm(t - o)
+        left = np.cross(u, d); left /= np.linalg.norm(left)
+        new_up = np.cross(d, left)
+        m = np.eye(4); m[:3, 0] = left; m[:3, 1] = new_up; m[:3, 2] = d; m[:3, 3] = o
+        return Transform4f(self.matrix @ m)
+
+    def inverse(self):
+        return Transform4f(np.linalg.inv(self.matrix))
+
+    def f32(self):
+        return self.matrix.astype(np.float32)
+
+
+T = Transform4f
+
+
+def _as_matrix(v):
+    if v is None:
+        return np.eye(4)
+    if isinstance(v, Transform4f):
+        return v.matrix
+    if hasattr(v, "matrix"):  # mi.ScalarTransform4f
+        return np.array(v.matrix, dtype=np.float64).reshape(4, 4)
+    return np.asarray(v, dtype=np.float64).reshape(4, 4)
+
+
+def _rgb(v, default=None):
+    """Accept {'type':'rgb','value':..}, {'type':'srgb',..}, {'type':'spectrum','value':x}, lists and scalars."""
+    if v is None:
+        v = default
+    if isinstance(v, dict):
+        if v.get("type") in ("rgb", "srgb", "spectrum", "uniform"):
+            v = v["value"]
+        else:
+            raise ValueError(f"unsupported colour texture {v.get('type')!r}")
+    a = np.broadcast_to(np.asarray(v, dtype=np.float32), (3,)).copy()
+    return a
+
+
+def srgb_to_linear(x):
+    x = np.asarray(x, dtype=np.float32)
+    return np.where(x <= 0.04045, x * np.float32(1.0 / 12.92), ((x + np.float32(0.055)) * np.float32(1.0 / 1.055)) ** np.float32(2.4)).astype(np.float32)
+
+
+def parse_fov(props, aspect):
+    """mitsuba3/src/render/sensor.cpp:147-200 (fov variant only)."""
+    fov = float(props["fov"])
+    axis = str(props.get("fov_axis", "x")).lower()
+    if axis == "smaller":
+        axis = "y" if aspect > 1 else "x"
+    elif axis == "larger":
+        axis = "x" if aspect > 1 else "y"
+    if axis == "x":
+        return fov
+    if axis == "y":
+        return math.degrees(2.0 * math.atan(math.tan(0.5 * math.radians(fov)) * aspect))
+    if axis == "diagonal":
+        diagonal = 2.0 * math.tan(0.5 * math.radians(fov))
+        width = diagonal / math.sqrt(1.0 + 1.0 / (aspect * aspect))
+        return math.degrees(2.0 * math.atan(width * 0.5))
+    raise ValueError("fov_axis must be one of smaller, larger, diagonal, x, y")
+
+
+def perspective_projection(film_size, crop_size, crop_offset, fov_x, near, far):
+    """camera -> sample space (sensor.h:229-265, transform.h:233-251)."""
+    fs = np.asarray(film_size, dtype=np.float64)
+    rel_size = np.asarray(crop_size, dtype=np.float64) / fs
+    rel_offset = np.asarray(crop_offset, dtype=np.float64) / fs
+    aspect = fs[0] / fs[1]
+    recip = 1.0 / (far - near)
+    cot = 1.0 / math.tan(math.radians(fov_x * 0.5))
+    persp = np.diag([cot, cot, far * recip, 0.0]); persp[2, 3] = -near * far * recip; persp[3, 2] = 1.0
+
+    def sc(x, y, z):
+        return np.diag([x, y, z, 1.0])
+
+    def tr(x, y, z):
+        m = np.eye(4); m[:3, 3] = [x, y, z]; return m
+
+    return sc(1.0 / rel_size[0], 1.0 / rel_size[1], 1.0) @ tr(-rel_offset[0], -rel_offset[1], 0.0) @ \
+        sc(-0.5, -0.5 * aspect, 1.0) @ tr(-1.0, -1.0 / aspect, 0.0) @ persp
+
+
+def gaussian_coeffs(stddev):
+    """rfilters/gaussian.cpp:48-92 (non-CUDA branch): scaled Remez fit, shifted to reach 0 at the radius."""
+    coeff = [9.992604880e-1, -4.977025247e-1, 1.222248550e-1, -1.932406282e-2, 2.136713061e-3, -1.679873860e-4,
+             9.202145248e-6, -3.329417433e-7, 7.128382794e-9, -6.821193280e-11]
+    cs, scale = [], 1.0
+    for c in coeff:
+        cs.append(np.float32(c * scale)); scale /= float(stddev) ** 2
+    radius = np.float32(4.0 * stddev)
+
+    def fma(a, b, c):  # float32 fma emulated through float64
+        return np.float32(np.float64(a) * np.float64(b) + np.float64(c))
+
+    def estrin(x, c):
+        n = len(c); n_fma = n // 2; n_rec = (n - 1) // 2
+        r = [fma(x, c[2 * i + 1], c[2 * i]) for i in range(n_fma)]
+        if n_rec == n_fma:
+            r.append(c[n - 1])
+        return r[0] if n_rec == 0 else estrin(np.float32(x * x), r)
+
+    cs[0] = np.float32(cs[0] - estrin(np.float32(radius * radius), cs))
+    return np.array(cs, dtype=np.float32), float(radius)
+
+
+# ---------------------------------------------------------------------------------------------
+# Hierarchical2D<Float,0> pyramid (core/distr_2d.h:403-509) for envmap importance sampling
+# ---------------------------------------------------------------------------------------------
+def _swizzle_index(x, y, width):
+    return ((x & 1) | (((x & ~1) | (y & 1)) << 1)) + ((y & ~1) * width)
+
+
+def build_hierarchical2d(data):
+    """data: [H][W] float32 (vertex values of the bilinear interpolant). Returns (flat f32, offsets, widths, sizes)."""
+    data = np.ascontiguousarray(data, dtype=np.float32)
+    h, w = data.shape
+    npx, npy = w - 1, h - 1
+    max_level = max(int(math.ceil(math.log2(max(npx, npy)))), 0)
+    level_sizes = [(w, h)]
+    lx, ly = npx, npy
+    for _ in range(max_level, -1, -1):
+        lx += lx & 1; ly += ly & 1
+        level_sizes.append((lx, ly)); lx >>= 1; ly >>= 1
+    levels = [np.zeros(sx * sy, dtype=np.float32) for sx, sy in level_sizes]
+    # level 1: patch averages (float32 arithmetic, summed in double)
+    avg = np.float32(0.25) * (data[:-1, :-1] + data[:-1, 1:] + data[1:, :-1] + data[1:, 1:])
+    total = float(np.sum(avg.astype(np.float64)))
+    scale = np.float32((npx * npy) / total)
+    yy, xx = np.meshgrid(np.arange(npy), np.arange(npx), indexing="ij")
+    levels[1][_swizzle_index(xx, yy, level_sizes[1][0])] = avg
+    levels[0][:] = data.reshape(-1) * scale
+    levels[1] *= scale
+    cur = (npx, npy)
+    for lvl in range(2, max_level + 2):
+        cur = ((cur[0] + 1) >> 1, (cur[1] + 1) >> 1)
+        yy, xx = np.meshgrid(np.arange(cur[1]), np.arange(cur[0]), indexing="ij")
+        src = _swizzle_index(xx * 2, yy * 2, level_sizes[lvl - 1][0])
+        l0 = levels[lvl - 1]
+        levels[lvl][_swizzle_index(xx, yy, level_sizes[lvl][0])] = l0[src] + l0[src + 1] + l0[src + 2] + l0[src + 3]
+    offsets, off = [], 0
+    for l in levels:
+        offsets.append(off); off += l.size
+    flat = np.concatenate(levels).astype(np.float32)
+    return flat, offsets, [s[0] for s in level_sizes], [l.size for l in levels]
+
+
+def build_alias_table(pmf):
+    """Vose alias table over a discrete pmf (fast envmap mode; not what the reference does)."""
+    p = np.asarray(pmf, dtype=np.float64).reshape(-1)
+    n = p.size
+    q = p * (n / p.sum())
+    prob = np.ones(n, dtype=np.float32); alias = np.arange(n, dtype=np.uint32)
+    small = [i for i in range(n) if q[i] < 1.0]; large = [i for i in range(n) if q[i] >= 1.0]
+    while small and large:
+        s = small.pop(); l = large.pop()
+        prob[s] = q[s]; alias[s] = l
+        q[l] = q[l] + q[s] - 1.0
+        (small if q[l] < 1.0 else large).append(l)
+    return prob, alias
+
+
+LUMA = np.array([0.212671, 0.715160, 0.072169], dtype=np.float32)
+
+_CUBE_V = np.array([[1, -1, -1], [1, -1, 1], [-1, -1, 1], [-1, -1, -1], [1, 1, -1], [-1, 1, -1], [-1, 1, 1], [1, 1, 1],
+                    [1, -1, -1], [1, 1, -1], [1, 1, 1], [1, -1, 1], [1, -1, 1], [1, 1, 1], [-1, 1, 1], [-1, -1, 1],
+                    [-1, -1, 1], [-1, 1, 1], [-1, 1, -1], [-1, -1, -1], [1, 1, -1], [1, -1, -1], [-1, -1, -1], [-1, 1, -1]], dtype=np.float64)
+_CUBE_N = np.repeat(np.array([[0, -1, 0], [0, 1, 0], [1, 0, 0], [0, 0, 1], [-1, 0, 0], [0, 0, -1]], dtype=np.float64), 4, axis=0)
+_CUBE_UV = np.tile(np.array([[0, 1], [1, 1], [1, 0], [0, 0]], dtype=np.float32), (6, 1))
+_CUBE_F = np.array([[0, 1, 2], [3, 0, 2], [4, 5, 6], [7, 4, 6], [8, 9, 10], [11, 8, 10], [12, 13, 14], [15, 12, 14],
+                    [16, 17, 18], [19, 16, 18], [20, 21, 22], [23, 20, 22]], dtype=np.uint32)
+
+
+def _xf_points(m, p):
+    p = np.asarray(p, dtype=np.float64)
+    return (p @ m[:3, :3].T + m[:3, 3]).astype(np.float32)
+
+
+def _xf_normals(m, n):
+    it = np.linalg.inv(m[:3, :3]).T
+    r = np.asarray(n, dtype=np.float64) @ it.T
+    r /= np.linalg.norm(r, axis=-1, keepdims=True)
+    return r.astype(np.float32)
+
+
+def load_obj(path, flip_tex_coords=True):
+    """Minimal Wavefront OBJ reader (obj.cpp subset): v / vt / vn / f with fan triangulation and vertex dedup."""
+    vs, vts, vns, keys, faces = [], [], [], {}, []
+    out_v, out_t, out_n = [], [], []
+    with open(path) as fh:
+        for line in fh:
+            tok = line.split()
+            if not tok:
+                continue
+            if tok[0] == "v": vs.append([float(x) for x in tok[1:4]])
+            elif tok[0] == "vt": vts.append([float(tok[1]), float(tok[2])])
+            elif tok[0] == "vn": vns.append([float(x) for x in tok[1:4]])
+            elif tok[0] == "f":
+                idx = []
+                for t in tok[1:]:
+                    parts = (t.split("/") + ["", ""])[:3]
+                    key = tuple(int(p) if p else 0 for p in parts)
+                    key = tuple((k + len(src) + 1) if k < 0 else k for k, src in zip(key, (vs, vts, vns)))
+                    if key not in keys:
+                        keys[key] = len(out_v)
+                        out_v.append(vs[key[0] - 1])
+                        out_t.append(vts[key[1] - 1] if key[1] else [0.0, 0.0])
+                        out_n.append(vns[key[2] - 1] if key[2] else [0.0, 0.0, 0.0])
+                    idx.append(keys[key])
+                for i in range(1, len(idx) - 1):
+                    faces.append([idx[0], idx[i], idx[i + 1]])
+    uv = np.asarray(out_t, dtype=np.float32).reshape(-1, 2)
+    if flip_tex_coords and len(vts):
+        uv[:, 1] = 1.0 - uv[:, 1]
+    return (np.asarray(out_v, dtype=np.float64).reshape(-1, 3), np.asarray(out_n, dtype=np.float64).reshape(-1, 3) if vns else None,
+            uv if vts else None, np.asarray(faces, dtype=np.uint32).reshape(-1, 3))
+
+
+class SceneDesc:
+    """Flat, C-ABI ready scene.  Keeps every numpy buffer alive; ``.c`` is the ctypes ``b2_scene_desc``."""
+
+    def __init__(self, scene_dict: dict, base_path: str = "."):
+        self.base_path = base_path
+        self.bsdf_ids: dict[str, int] = {}
+        self.bsdf_names: list[str] = []
+        self.bsdfs: list[capi.Bsdf] = []
+        self.textures: list[capi.Texture] = []
+        self.texture_arrays: list[np.ndarray] = []
+        self.meshes: list[capi.Mesh] = []
+        self.mesh_names: list[str] = []
+        self.emitters: list[capi.Emitter] = []
+        self.emitter_names: list[str] = []
+        self._pos, self._nrm, self._uv, self._faces = [], [], [], []
+        self._nv = 0
+        self._nf = 0
+        self._cdf = []
+        self._ncdf = 0
+        self.env = None
+        self.integrator_props = {}
+        self.spp = 4
+        self._keep = []
+        self._parse(scene_dict)
+        self._finalize()
+
+    # ------------------------------------------------------------------ BSDFs / textures
+    def _add_texture(self, spec) -> int:
+        if "data" in spec:
+            arr = np.asarray(spec["data"])
+            raw = True
+        else:
+            from PIL import Image
+            path = spec["filename"]
+            if not os.path.isabs(path):
+                path = os.path.join(self.base_path, path)
+            img = Image.open(path).convert("RGB")
+            arr = np.asarray(img)
+            raw = bool(spec.get("raw", False))
+        if arr.dtype == np.uint8:
+            lin = arr.astype(np.float32) / np.float32(255.0)
+            if not raw:
+                lin = srgb_to_linear(lin)
+            fmt = spec.get("format", "auto")
+            arr = lin.astype(np.float16) if fmt in ("auto", "fp16") else lin.astype(np.float32)
+        elif arr.dtype == np.float16:
+            pass
+        else:
+            arr = arr.astype(np.float32)
+        if arr.ndim != 3 or arr.shape[2] != 3:
+            raise ValueError("bitmap textures must be [H][W][3]")
+        arr = np.ascontiguousarray(arr)
+        t = capi.Texture()
+        t.data = arr.ctypes.data
+        t.height, t.width = arr.shape[0], arr.shape[1]
+        t.format = capi.TEX_F16 if arr.dtype == np.float16 else capi.TEX_F32
+        t.wrap = {"repeat": capi.WRAP_REPEAT, "mirror": capi.WRAP_MIRROR, "clamp": capi.WRAP_CLAMP}[spec.get("wrap_mode", "repeat")]
+        t.filter = {"bilinear": capi.FILTER_BILINEAR, "nearest": capi.FILTER_NEAREST}[spec.get("filter_type", "bilinear")]
+        to_uv = np.asarray(spec.get("to_uv", np.eye(3)), dtype=np.float32).reshape(3, 3)
+        t.to_uv[:] = to_uv.reshape(-1).tolist()
+        self.textures.append(t); self.texture_arrays.append(arr)
+        return len(self.textures) - 1
+
+    def _reflectance(self, b: capi.Bsdf, spec, default):
+        if isinstance(spec, dict) and spec.get("type") == "bitmap":
+            b.reflectance_tex = self._add_texture(spec)
+            b.reflectance[:] = [1.0, 1.0, 1.0]
+        else:
+            b.reflectance_tex = -1
+            b.reflectance[:] = _rgb(spec, default).tolist()
+
+    def _add_bsdf(self, spec: dict, name: str | None) -> int:
+        t = spec["type"]
+        if t == "ref":
+            return self.bsdf_ids[spec["id"]]
+        flags = 0
+        if t == "twosided":
+            nested = [v for k, v in spec.items() if isinstance(v, dict)]
+            if len(nested) != 1:
+                raise ValueError("twosided: exactly one nested BRDF is supported")
+            spec = nested[0]
+            if spec["type"] == "ref":
+                raise ValueError("twosided: nested ref not supported")
+            t = spec["type"]; flags |= capi.BSDF_FLAG_TWOSIDED
+        b = capi.Bsdf()
+        b.flags = flags; b.reflectance_tex = -1; b.sample_visible = 1
+        b.reflectance[:] = [1, 1, 1]; b.transmittance[:] = [1, 1, 1]; b.eta[:] = [0, 0, 0]; b.k[:] = [1, 1, 1]
+        b.alpha_u = b.alpha_v = 0.1; b.ior = 1.0
+        if t == "diffuse":
+            b.type = capi.BSDF_DIFFUSE
+            self._reflectance(b, spec.get("reflectance"), 0.5)
+        elif t == "roughconductor":
+            b.type = capi.BSDF_ROUGHCONDUCTOR
+            if spec.get("material", "none") != "none":
+                raise ValueError("roughconductor: named materials need Mitsuba's ior database; pass eta/k")
+            b.eta[:] = _rgb(spec.get("eta"), 0.0).tolist(); b.k[:] = _rgb(spec.get("k"), 1.0).tolist()
+            b.distribution = {"beckmann": capi.MF_BECKMANN, "ggx": capi.MF_GGX}[str(spec.get("distribution", "beckmann")).lower()]
+            b.sample_visible = int(bool(spec.get("sample_visible", True)))
+            if "alpha_u" in spec or "alpha_v" in spec:
+                b.alpha_u, b.alpha_v = float(spec["alpha_u"]), float(spec["alpha_v"])
+            else:
+                b.alpha_u = b.alpha_v = float(spec.get("alpha", 0.1))
+            self._reflectance(b, spec.get("specular_reflectance"), 1.0)
+        elif t == "dielectric":
+            if flags & capi.BSDF_FLAG_TWOSIDED:
+                raise ValueError("Only materials without a transmission component can be nested!")
+            b.type = capi.BSDF_DIELECTRIC
+            iors = {"bk7": 1.5046, "air": 1.000277, "vacuum": 1.0, "water": 1.3330, "diamond": 2.419}
+            def ior(v, d):
+                v = spec.get(v, d)
+                return float(iors[v]) if isinstance(v, str) else float(v)
+            b.ior = ior("int_ior", "bk7") / ior("ext_ior", "air")
+            b.reflectance[:] = _rgb(spec.get("specular_reflectance"), 1.0).tolist()
+            b.transmittance[:] = _rgb(spec.get("specular_transmittance"), 1.0).tolist()
+        else:
+            raise ValueError(f"unsupported BSDF type {t!r} (hot-path scope: diffuse, roughconductor, dielectric, twosided)")
+        self.bsdfs.append(b)
+        idx = len(self.bsdfs) - 1
+        self.bsdf_names.append(name or f"__bsdf{idx}")
+        if name:
+            self.bsdf_ids[name] = idx
+        if spec.get("id"):
+            self.bsdf_ids[spec["id"]] = idx
+        return idx
+
+    # ------------------------------------------------------------------ shapes
+    def _add_shape(self, name: str, spec: dict):
+        t = spec["type"]
+        m = _as_matrix(spec.get("to_world"))
+        kind = capi.SHAPE_MESH
+        if t == "rectangle":
+            kind = capi.SHAPE_RECTANGLE
+            idx = np.arange(4)
+            xf, yf = (idx & 1).astype(np.float64), ((idx & 2) >> 1).astype(np.float64)
+            pos = _xf_points(m, np.stack([xf * 2 - 1, yf * 2 - 1, np.zeros(4)], axis=1))
+            nrm = np.repeat(_xf_normals(m, [[0.0, 0.0, 1.0]]), 4, axis=0)
+            uv = np.stack([xf, yf], axis=1).astype(np.float32)
+            faces = np.array([[1, 2, 0], [1, 3, 2]], dtype=np.uint32)
+        elif t == "cube":
+            pos = _xf_points(m, _CUBE_V); nrm = _xf_normals(m, _CUBE_N); uv = _CUBE_UV.copy(); faces = _CUBE_F.copy()
+        elif t == "obj":
+            path = spec["filename"]
+            if not os.path.isabs(path):
+                path = os.path.join(self.base_path, path)
+            v, n, uv, faces = load_obj(path, bool(spec.get("flip_tex_coords", True)))
+            pos = _xf_points(m, v); nrm = _xf_normals(m, n) if n is not None and not spec.get("face_normals", False) else None
+        elif t == "mesh":  # raw arrays (procedural scenes); positions are object space
+            pos = _xf_points(m, np.asarray(spec["positions"], dtype=np.float64).reshape(-1, 3))
+            nrm = _xf_normals(m, np.asarray(spec["normals"]).reshape(-1, 3)) if spec.get("normals") is not None else None
+            uv = np.asarray(spec["texcoords"], dtype=np.float32).reshape(-1, 2) if spec.get("texcoords") is not None else None
+            faces = np.asarray(spec["faces"], dtype=np.uint32).reshape(-1, 3)
+        else:
+            raise ValueError(f"unsupported shape type {t!r} (hot-path scope: rectangle, cube, obj, mesh)")
+        bsdf_spec = spec.get("bsdf")
+        if bsdf_spec is None:
+            bsdf_spec = {"type": "diffuse"}
+        bsdf = self._add_bsdf(bsdf_spec, None)
+        mesh = capi.Mesh()
+        mesh.first_vertex, mesh.n_vertices = self._nv, len(pos)
+        mesh.first_face, mesh.n_faces = self._nf, len(faces)
+        mesh.bsdf = bsdf; mesh.emitter = -1
+        mesh.flags = (capi.MESH_HAS_NORMALS if nrm is not None else 0) | (capi.MESH_HAS_UV if uv is not None else 0) | \
+                     (capi.MESH_FLIP_NORMALS if spec.get("flip_normals", False) else 0)
+        self._pos.append(pos.astype(np.float32))
+        self._nrm.append(nrm.astype(np.float32) if nrm is not None else np.zeros_like(pos, dtype=np.float32))
+        self._uv.append(uv.astype(np.float32) if uv is not None else np.zeros((len(pos), 2), dtype=np.float32))
+        self._faces.append(faces.astype(np.uint32) + np.uint32(self._nv))
+        mesh_index = len(self.meshes)
+        em_spec = spec.get("emitter")
+        if em_spec is not None:
+            if em_spec["type"] != "area":
+                raise ValueError("only `area` emitters can be attached to shapes")
+            e = capi.Emitter()
+            e.type = capi.EMITTER_AREA; e.mesh = mesh_index; e.shape_kind = kind
+            e.radiance[:] = _rgb(em_spec.get("radiance"), 1.0).tolist()
+            e.to_world[:] = m.astype(np.float32).reshape(-1).tolist()
+            p = pos.astype(np.float64); f = faces
+            tri_area = 0.5 * np.linalg.norm(np.cross(p[f[:, 1]] - p[f[:, 0]], p[f[:, 2]] - p[f[:, 0]]), axis=1)
+            if kind == capi.SHAPE_RECTANGLE:
+                du = (m[:3, :3] @ np.array([2.0, 0, 0])).astype(np.float32); dv = (m[:3, :3] @ np.array([0, 2.0, 0])).astype(np.float32)
+                area = np.float32(np.linalg.norm(np.cross(du, dv)))
+                n = _xf_normals(m, [[0.0, 0.0, 1.0]])[0]
+                if spec.get("flip_normals", False):
+                    n = -n
+                e.normal[:] = n.tolist(); e.inv_area = float(np.float32(1.0) / area); e.cdf_offset = 0
+            else:
+                cdf = np.cumsum(tri_area.astype(np.float32).astype(np.float64)).astype(np.float32)
+                e.normal[:] = [0, 0, 0]; e.inv_area = float(np.float32(1.0) / cdf[-1]); e.cdf_offset = self._ncdf
+                self._cdf.append(cdf); self._ncdf += len(cdf)
+            mesh.emitter = len(self.emitters)
+            self.emitters.append(e); self.emitter_names.append(name)
+        self.meshes.append(mesh); self.mesh_names.append(name)
+        self._nv += len(pos); self._nf += len(faces)
+
+    # ------------------------------------------------------------------ environment emitters
+    def _add_env(self, name, spec):
+        e = capi.Emitter(); e.mesh = -1; e.shape_kind = 0; e.inv_area = 0.0; e.cdf_offset = 0
+        e.normal[:] = [0, 0, 0]; e.to_world[:] = np.eye(4, dtype=np.float32).reshape(-1).tolist()
+        if spec["type"] == "constant":
+            e.type = capi.EMITTER_CONSTANT
+            e.radiance[:] = _rgb(spec.get("radiance"), 1.0).tolist()
+            self.env = {"type": "constant"}
+        else:
+            e.type = capi.EMITTER_ENVMAP
+            e.radiance[:] = [1, 1, 1]
+            if "data" in spec:
+                img = np.asarray(spec["data"], dtype=np.float32)
+            else:
+                import cv2
+                os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
+                path = spec["filename"] if os.path.isabs(spec["filename"]) else os.path.join(self.base_path, spec["filename"])
+                img = cv2.imread(path, cv2.IMREAD_UNCHANGED)[:, :, 2::-1].astype(np.float32)
+            h, w, _ = img.shape
+            if w < 2 or h < 3:
+                raise ValueError("the environment map resolution must be at least 2x3 pixels")
+            data = np.concatenate([img, img[:, :1]], axis=1).astype(np.float32)          # envmap.cpp:223-230
+            theta_scale = np.float32(1.0 / (h - 1) * np.pi)
+            sin_theta = np.sin((np.arange(h, dtype=np.float32) * theta_scale).astype(np.float32)).astype(np.float32)
+            lum = (img @ LUMA).astype(np.float32) * sin_theta[:, None]
+            lum = np.concatenate([lum, lum[:, :1]], axis=1).astype(np.float32)
+            flat, offs, widths, sizes = build_hierarchical2d(lum)
+            self.env = {"type": "envmap", "data": np.ascontiguousarray(data), "warp": flat, "offsets": offs, "widths": widths,
+                        "sizes": sizes, "scale": float(spec.get("scale", 1.0)), "to_world": _as_matrix(spec.get("to_world")),
+                        "lum": lum}
+        self.emitters.append(e); self.emitter_names.append(name)
+
+    # ------------------------------------------------------------------ sensor
+    def _add_sensor(self, spec):
+        if spec["type"] != "perspective":
+            raise ValueError("only the `perspective` sensor is on the hot path")
+        film = spec.get("film", {"type": "hdrfilm"})
+        fw, fh = int(film.get("width", 768)), int(film.get("height", 576))
+        cw, ch = int(film.get("crop_width", fw)), int(film.get("crop_height", fh))
+        cox, coy = int(film.get("crop_offset_x", 0)), int(film.get("crop_offset_y", 0))
+        if film.get("sample_border", False):
+            raise ValueError("film.sample_border is not supported yet")
+        near, far = float(spec.get("near_clip", 1e-2)), float(spec.get("far_clip", 1e4))
+        x_fov = parse_fov(spec, fw / fh)
+        c2s = perspective_projection((fw, fh), (cw, ch), (cox, coy), x_fov, near, far)
+        s = capi.Sensor()
+        s.sample_to_camera[:] = np.linalg.inv(c2s).astype(np.float32).reshape(-1).tolist()
+        s.to_world[:] = _as_matrix(spec.get("to_world")).astype(np.float32).reshape(-1).tolist()
+        s.near_clip, s.far_clip = near, far
+        s.film_width, s.film_height = fw, fh
+        s.crop_offset_x, s.crop_offset_y, s.crop_width, s.crop_height = cox, coy, cw, ch
+        rf = film.get("rfilter", {"type": "gaussian"})
+        s.gaussian_coeff[:] = [0.0] * 10
+        if rf["type"] == "gaussian":
+            coeff, radius = gaussian_coeffs(float(rf.get("stddev", 0.5)))
+            s.rfilter = capi.RFILTER_GAUSSIAN; s.rfilter_radius = radius; s.gaussian_coeff[:] = coeff.tolist()
+        elif rf["type"] == "tent":
+            s.rfilter = capi.RFILTER_TENT; s.rfilter_radius = float(rf.get("radius", 1.0))
+        elif rf["type"] == "box":
+            s.rfilter = capi.RFILTER_BOX; s.rfilter_radius = 0.5
+        else:
+            raise ValueError(f"unsupported rfilter {rf['type']!r}")
+        if int(math.ceil(s.rfilter_radius - 0.5)) * 2 + 1 > 5:
+            raise ValueError("reconstruction filter footprint larger than 5x5 is not supported")
+        self.sensor = s
+        self.spp = int(spec.get("sampler", {}).get("sample_count", 4))
+        if spec.get("sampler", {}).get("type", "independent") != "independent":
+            raise ValueError("only the `independent` sampler is on the hot path")
+
+    # ------------------------------------------------------------------ driver
+    def _parse(self, d):
+        if d.get("type") != "scene":
+            raise ValueError("expected a dictionary with type == 'scene'")
+        have_sensor = False
+        for name, v in d.items():
+            if not isinstance(v, dict):
+                continue
+            t = v.get("type")
+            if t in ("diffuse", "roughconductor", "dielectric", "twosided"):
+                self._add_bsdf(v, name)
+        for name, v in d.items():   # declaration order defines the emitter order (scene.cpp:26-66)
+            if not isinstance(v, dict):
+                continue
+            t = v.get("type")
+            if t in ("rectangle", "cube", "obj", "mesh"):
+                self._add_shape(name, v)
+            elif t in ("envmap", "constant"):
+                if self.env is not None:
+                    raise ValueError("Only one environment emitter can be specified per scene.")
+                self._add_env(name, v)
+            elif t == "perspective":
+                if not have_sensor:
+                    self._add_sensor(v); have_sensor = True
+            elif t in ("path", "prb", "mypath", "path_test", "b2path", "b2path_mis", "b2prb"):
+                self.integrator_props = {k: v[k] for k in v if k != "type"}
+                self.integrator_props["type"] = t
+            elif t in ("diffuse", "roughconductor", "dielectric", "twosided"):
+                pass
+            else:
+                raise ValueError(f"unsupported scene element {name!r} of type {t!r}")
+        if not have_sensor:
+            raise ValueError("scene has no sensor")
+
+    def _finalize(self):
+        def cat(lst, shape, dt):
+            return np.ascontiguousarray(np.concatenate(lst, axis=0).astype(dt)) if lst else np.zeros(shape, dtype=dt)
+        self.positions = cat(self._pos, (0, 3), np.float32)
+        self.normals = cat(self._nrm, (0, 3), np.float32)
+        self.texcoords = cat(self._uv, (0, 2), np.float32)
+        self.faces = cat(self._faces, (0, 3), np.uint32)
+        self.area_cdf = cat(self._cdf, (0,), np.float32)
+        c = capi.SceneDesc()
+        c.abi_version = capi.B2_ABI_VERSION
+        c.n_vertices, c.n_faces = len(self.positions), len(self.faces)
+        c.n_meshes, c.n_bsdfs, c.n_textures, c.n_emitters = len(self.meshes), len(self.bsdfs), len(self.textures), len(self.emitters)
+        c.positions = self.positions.ctypes.data; c.normals = self.normals.ctypes.data
+        c.texcoords = self.texcoords.ctypes.data; c.faces = self.faces.ctypes.data
+        self._meshes_c = (capi.Mesh * max(1, len(self.meshes)))(*self.meshes)
+        self._bsdfs_c = (capi.Bsdf * max(1, len(self.bsdfs)))(*self.bsdfs)
+        self._tex_c = (capi.Texture * max(1, len(self.textures)))(*self.textures)
+        self._em_c = (capi.Emitter * max(1, len(self.emitters)))(*self.emitters)
+        c.meshes = self._meshes_c; c.bsdfs = self._bsdfs_c; c.textures = self._tex_c; c.emitters = self._em_c
+        c.area_cdf = self.area_cdf.ctypes.data if len(self.area_cdf) else None
+        c.n_area_cdf = len(self.area_cdf)
+        c.sensor = self.sensor
+        if self.env is not None:
+            ev = capi.Envmap()
+            if len(self.positions):
+                lo, hi = self.positions.min(axis=0).astype(np.float32), self.positions.max(axis=0).astype(np.float32)
+                center = ((lo + hi) * np.float32(0.5)).astype(np.float32)
+                radius = np.float32(np.linalg.norm((hi - center).astype(np.float32)))
+                radius = max(RAY_EPSILON, np.float32(radius * (np.float32(1.0) + RAY_EPSILON)))   # envmap.cpp:337-344
+            else:
+                center, radius = np.zeros(3, np.float32), RAY_EPSILON
+            ev.bsphere_center[:] = center.tolist(); ev.bsphere_radius = float(radius)
+            ev.to_world[:] = np.eye(4, dtype=np.float32).reshape(-1).tolist(); ev.from_world[:] = np.eye(4, dtype=np.float32).reshape(-1).tolist()
+            ev.n_levels = 0; ev.scale = 1.0; ev.width = ev.height = 0
+            if self.env["type"] == "envmap":
+                e = self.env
+                ev.data = e["data"].ctypes.data; ev.height, ev.width = e["data"].shape[:2]
+                ev.scale = e["scale"]
+                ev.to_world[:] = e["to_world"].astype(np.float32).reshape(-1).tolist()
+                ev.from_world[:] = np.linalg.inv(e["to_world"]).astype(np.float32).reshape(-1).tolist()
+                ev.n_levels = len(e["offsets"])
+                if ev.n_levels > capi.B2_MAX_WARP_LEVELS:
+                    raise ValueError("envmap too large")
+                ev.warp_data = e["warp"].ctypes.data
+                for i, (o, w, sz) in enumerate(zip(e["offsets"], e["widths"], e["sizes"])):
+                    ev.level_offset[i], ev.level_width[i], ev.level_size[i] = o, w, sz
+                lum = e["lum"]
+                patch = 0.25 * (lum[:-1, :-1] + lum[:-1, 1:] + lum[1:, :-1] + lum[1:, 1:])
+                e["alias_prob"], e["alias_idx"] = build_alias_table(patch) if patch.size <= (1 << 22) else (None, None)
+                ev.alias_prob = e["alias_prob"].ctypes.data if e["alias_prob"] is not None else None
+                ev.alias_idx = e["alias_idx"].ctypes.data if e["alias_idx"] is not None else None
+            self._env_c = ev
+            c.envmap = C.pointer(ev)
+        self.c = c
+
+    # ------------------------------------------------------------------ helpers
+    @property
+    def film_shape(self):
+        return (self.sensor.crop_height, self.sensor.crop_width)
+
+    def bsdf_index(self, name: str) -> int:
+        return self.bsdf_ids[name]
+
+    def texture_array(self, bsdf_index: int) -> np.ndarray:
+        return self.texture_arrays[self.bsdfs[bsdf_index].reflectance_tex]
