@@ -1,0 +1,386 @@
+// capi.cu -- the extern "C" boundary declared in include/b2path.h (host side: handles, uploads, launches).
+// No CPU fallback exists: every entry point either runs the CUDA path or fails with an error string.
+#include "b2_build.h"
+#include "b2_render.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+using namespace b2;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) { g_err = msg; return code; }
+#define CUDA_OK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return fail(-10, std::string(#x) + ": " + cudaGetErrorString(e_)); } while (0)
+
+struct b2_ctx { int device = 0, sm_count = 0; };
+
+struct b2_scene {
+    b2_ctx *ctx = nullptr;
+    DScene d{};
+    Bvh bvh;
+    std::vector<void *> allocs;
+    std::vector<b2_bsdf> bsdfs;                 // host mirror (for set_param / grad target validation)
+    std::vector<DTexture> textures;             // host mirror of the device texture records
+    std::vector<size_t> texture_bytes;
+    DBsdf *bsdfs_dev = nullptr;
+    uint32_t *face_mesh_dev = nullptr;
+    uint32_t *unit_counter = nullptr;
+    unsigned long long *counters_dev = nullptr;
+    float *wfilm = nullptr;                     // weight film of the PRB sample set
+    uint64_t launches = 0;
+
+    template <typename T> cudaError_t upload(const T *host, size_t n, T *&dev) {
+        void *q = nullptr; cudaError_t e = cudaMalloc(&q, std::max<size_t>(n * sizeof(T), 16)); if (e != cudaSuccess) return e;
+        allocs.push_back(q); dev = (T *) q;
+        if (n && host) e = cudaMemcpy(q, host, n * sizeof(T), cudaMemcpyHostToDevice);
+        return e;
+    }
+    ~b2_scene() { for (void *q : allocs) cudaFree(q); bvh_free(bvh); }
+};
+
+extern "C" {
+
+const char *b2_last_error(void) { return g_err.c_str(); }
+int b2_abi_version(void) { return B2_ABI_VERSION; }
+
+int b2_init(int device, b2_ctx **out) {
+    if (!out) return fail(-1, "b2_init: null output");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) return fail(-2, std::string("b2_init: no CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e));
+    if (device < 0 || device >= n) return fail(-3, "b2_init: device index out of range");
+    CUDA_OK(cudaSetDevice(device));
+    cudaDeviceProp prop; CUDA_OK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(-4, "b2_init: this library is built for sm_100a (B200) only");
+    b2_ctx *c = new b2_ctx; c->device = device; c->sm_count = prop.multiProcessorCount;
+    *out = c; return 0;
+}
+void b2_shutdown(b2_ctx *ctx) { delete ctx; }
+
+static void m3x4(const float *m16, float *m12) { std::memcpy(m12, m16, 12 * sizeof(float)); }
+
+int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
+    if (!ctx || !desc || !out) return fail(-1, "b2_scene_create: null argument");
+    if (desc->abi_version != B2_ABI_VERSION) return fail(-2, "b2_scene_create: ABI version mismatch");
+    if (desc->n_emitters && !desc->emitters) return fail(-2, "b2_scene_create: emitters missing");
+    CUDA_OK(cudaSetDevice(ctx->device));
+    std::unique_ptr<b2_scene> s(new b2_scene); s->ctx = ctx;
+    DScene &d = s->d;
+    float *pos, *nrm, *uv; uint32_t *faces;
+    CUDA_OK(s->upload(desc->positions, (size_t) desc->n_vertices * 3, pos));
+    CUDA_OK(s->upload(desc->normals, (size_t) desc->n_vertices * 3, nrm));
+    CUDA_OK(s->upload(desc->texcoords, (size_t) desc->n_vertices * 2, uv));
+    CUDA_OK(s->upload(desc->faces, (size_t) desc->n_faces * 3, faces));
+    d.pos = pos; d.nrm = nrm; d.uv = uv; d.faces = faces; d.n_faces = desc->n_faces;
+    // meshes + face -> mesh table
+    std::vector<DMesh> meshes(desc->n_meshes); std::vector<uint32_t> face_mesh(desc->n_faces, 0);
+    for (uint32_t i = 0; i < desc->n_meshes; ++i) {
+        const b2_mesh &m = desc->meshes[i];
+        if (m.bsdf < 0 || (uint32_t) m.bsdf >= desc->n_bsdfs) return fail(-2, "b2_scene_create: mesh references a missing BSDF");
+        if ((uint64_t) m.first_face + m.n_faces > desc->n_faces) return fail(-2, "b2_scene_create: mesh face range out of bounds");
+        meshes[i] = DMesh{ m.bsdf, m.emitter, m.flags, m.first_face, m.n_faces, { 0, 0, 0 } };
+        for (uint32_t f = 0; f < m.n_faces; ++f) face_mesh[m.first_face + f] = i;
+    }
+    for (size_t i = 0; i < (size_t) desc->n_faces * 3; ++i)
+        if (desc->faces[i] >= desc->n_vertices) return fail(-2, "b2_scene_create: face index out of bounds");
+    DMesh *meshes_dev; CUDA_OK(s->upload(meshes.data(), meshes.size(), meshes_dev)); d.meshes = meshes_dev;
+    CUDA_OK(s->upload(face_mesh.data(), face_mesh.size(), s->face_mesh_dev));
+    // textures
+    s->textures.resize(desc->n_textures); s->texture_bytes.resize(desc->n_textures);
+    for (uint32_t i = 0; i < desc->n_textures; ++i) {
+        const b2_texture &t = desc->textures[i];
+        size_t bytes = (size_t) t.width * t.height * 3 * (t.format == B2_TEX_F16 ? 2 : 4);
+        uint8_t *data; CUDA_OK(s->upload((const uint8_t *) t.data, bytes, data));
+        DTexture &o = s->textures[i];
+        o.data = data; o.width = t.width; o.height = t.height; o.format = t.format; o.wrap = t.wrap; o.filter = t.filter; o.pad = 0;
+        for (int k = 0; k < 6; ++k) o.to_uv[k] = t.to_uv[k];
+        s->texture_bytes[i] = bytes;
+    }
+    DTexture *tex_dev; CUDA_OK(s->upload(s->textures.data(), s->textures.size(), tex_dev)); d.textures = tex_dev;
+    // BSDFs
+    s->bsdfs.assign(desc->bsdfs, desc->bsdfs + desc->n_bsdfs);
+    std::vector<DBsdf> bs(desc->n_bsdfs);
+    for (uint32_t i = 0; i < desc->n_bsdfs; ++i) {
+        const b2_bsdf &b = desc->bsdfs[i]; DBsdf &o = bs[i];
+        if (b.reflectance_tex >= (int) desc->n_textures) return fail(-2, "b2_scene_create: BSDF references a missing texture");
+        if (b.type < 0 || b.type > B2_BSDF_DIELECTRIC) return fail(-2, "b2_scene_create: unsupported BSDF type");
+        o.type = b.type; o.flags = b.flags; o.tex = b.reflectance_tex; o.distribution = b.distribution; o.sample_visible = b.sample_visible;
+        for (int k = 0; k < 3; ++k) { o.refl[k] = b.reflectance[k]; o.eta[k] = b.eta[k]; o.k[k] = b.k[k]; o.trans[k] = b.transmittance[k]; }
+        o.alpha_u = b.alpha_u; o.alpha_v = b.alpha_v; o.ior = b.ior;
+    }
+    CUDA_OK(s->upload(bs.data(), bs.size(), s->bsdfs_dev)); d.bsdfs = s->bsdfs_dev;
+    // emitters
+    std::vector<DEmitter> ems(desc->n_emitters); d.env_emitter = -1;
+    for (uint32_t i = 0; i < desc->n_emitters; ++i) {
+        const b2_emitter &e = desc->emitters[i]; DEmitter &o = ems[i];
+        o.type = e.type; o.mesh = e.mesh; o.shape_kind = e.shape_kind; o.cdf_offset = e.cdf_offset; o.inv_area = e.inv_area; o.pad = 0.f;
+        for (int k = 0; k < 3; ++k) { o.radiance[k] = e.radiance[k]; o.normal[k] = e.normal[k]; }
+        m3x4(e.to_world, o.to_world);
+        if (e.type != B2_EMITTER_AREA) d.env_emitter = (int) i;
+        else if (e.mesh < 0 || (uint32_t) e.mesh >= desc->n_meshes) return fail(-2, "b2_scene_create: area emitter without a mesh");
+    }
+    DEmitter *em_dev; CUDA_OK(s->upload(ems.data(), ems.size(), em_dev)); d.emitters = em_dev; d.n_emitters = desc->n_emitters;
+    float *cdf; CUDA_OK(s->upload(desc->area_cdf, desc->n_area_cdf, cdf)); d.area_cdf = cdf;
+    // environment
+    std::memset(&d.env, 0, sizeof(d.env));
+    if (desc->envmap) {
+        const b2_envmap &e = *desc->envmap; DEnvmap &o = d.env;
+        o.present = 1; o.width = e.width; o.height = e.height; o.n_levels = e.n_levels; o.scale = e.scale; o.bsphere_radius = e.bsphere_radius;
+        for (int k = 0; k < 3; ++k) o.bsphere_center[k] = e.bsphere_center[k];
+        m3x4(e.to_world, o.to_world); m3x4(e.from_world, o.from_world);
+        if (e.n_levels > 0) {
+            if (e.n_levels > B2_MAX_WARP_LEVELS) return fail(-2, "b2_scene_create: too many warp levels");
+            float *data; CUDA_OK(s->upload(e.data, (size_t) e.width * e.height * 3, data)); o.data = data;
+            // repack the Hierarchical2D levels so that every level starts on a 16-byte boundary (2x2 blocks -> one float4 load)
+            std::vector<float> packed; uint32_t off = 0;
+            for (int l = 0; l < e.n_levels; ++l) {
+                o.level_offset[l] = off; o.level_width[l] = e.level_width[l];
+                packed.resize(off + ((e.level_size[l] + 3u) & ~3u), 0.f);
+                std::memcpy(packed.data() + off, e.warp_data + e.level_offset[l], sizeof(float) * e.level_size[l]);
+                off = (uint32_t) packed.size();
+            }
+            float *warp; CUDA_OK(s->upload(packed.data(), packed.size(), warp)); o.warp = warp;
+            if (e.alias_prob && e.alias_idx) {
+                size_t n = (size_t) (e.width - 1) * (e.height - 1);
+                float *ap; uint32_t *ai; CUDA_OK(s->upload(e.alias_prob, n, ap)); CUDA_OK(s->upload(e.alias_idx, n, ai));
+                o.alias_prob = ap; o.alias_idx = ai;
+            }
+        }
+    }
+    // sensor
+    {
+        const b2_sensor &e = desc->sensor; DSensor &o = d.sensor;
+        if (e.crop_width <= 0 || e.crop_height <= 0) return fail(-2, "b2_scene_create: empty film");
+        std::memcpy(o.sample_to_camera, e.sample_to_camera, sizeof(o.sample_to_camera)); std::memcpy(o.to_world, e.to_world, sizeof(o.to_world));
+        o.near_clip = e.near_clip; o.far_clip = e.far_clip;
+        o.crop_offset_x = e.crop_offset_x; o.crop_offset_y = e.crop_offset_y; o.crop_width = e.crop_width; o.crop_height = e.crop_height;
+        o.rfilter = e.rfilter; o.rfilter_radius = e.rfilter_radius; o.inv_radius = 1.f / e.rfilter_radius;
+        std::memcpy(o.gaussian_coeff, e.gaussian_coeff, sizeof(o.gaussian_coeff));
+        o.scale_x = 1.f / (float) e.crop_width; o.scale_y = 1.f / (float) e.crop_height;
+        o.offset_x = -(float) e.crop_offset_x * o.scale_x; o.offset_y = -(float) e.crop_offset_y * o.scale_y;
+        int n = e.rfilter == B2_RFILTER_BOX ? 0 : (int) std::ceil(e.rfilter_radius - .5f);
+        if (n > 2) return fail(-2, "b2_scene_create: reconstruction filter footprint larger than 5x5");
+    }
+    CUDA_OK(cudaMalloc((void **) &s->unit_counter, 16)); s->allocs.push_back(s->unit_counter);
+    CUDA_OK(cudaMalloc((void **) &s->counters_dev, sizeof(unsigned long long) * C_N)); s->allocs.push_back(s->counters_dev);
+    d.nodes = nullptr; d.tris = nullptr; d.n_nodes = 0;
+    *out = s.release();
+    return 0;
+}
+
+void b2_scene_destroy(b2_scene *scene) {
+    if (!scene) return;
+    cudaSetDevice(scene->ctx->device);
+    delete scene;
+}
+
+int b2_scene_build_accel(b2_scene *s, int builder, uintptr_t stream, b2_build_stats *stats) {
+    if (!s) return fail(-1, "b2_scene_build_accel: null scene");
+    if (builder != 0) return fail(-2, "b2_scene_build_accel: unknown builder (0 = LBVH -> compressed 8-wide)");
+    CUDA_OK(cudaSetDevice(s->ctx->device));
+    bvh_free(s->bvh);
+    std::string err;
+    if (!bvh_build(s->d.pos, s->d.faces, s->face_mesh_dev, s->d.n_faces, (cudaStream_t) stream, s->bvh, err)) return fail(-11, err);
+    s->d.nodes = s->bvh.nodes; s->d.tris = s->bvh.tris; s->d.n_nodes = s->bvh.n_nodes;
+    if (stats) {
+        stats->ms_morton_sort = s->bvh.ms_morton_sort; stats->ms_lbvh = s->bvh.ms_lbvh; stats->ms_collapse = s->bvh.ms_collapse; stats->ms_total = s->bvh.ms_total;
+        stats->n_nodes8 = s->bvh.n_nodes; stats->n_tris = s->bvh.n_tris; stats->max_depth = s->bvh.depth;
+        stats->node_bytes = s->bvh.node_bytes; stats->tri_bytes = s->bvh.tri_bytes;
+    }
+    return 0;
+}
+
+int b2_scene_set_param(b2_scene *s, const char *key, const void *dev_ptr, size_t bytes, uintptr_t stream) {
+    if (!s || !key || !dev_ptr) return fail(-1, "b2_scene_set_param: null argument");
+    CUDA_OK(cudaSetDevice(s->ctx->device));
+    int idx = -1; char what[32] = { 0 };
+    if (std::sscanf(key, "%d.reflectance.%31s", &idx, what) != 2 || idx < 0 || idx >= (int) s->bsdfs.size())
+        return fail(-2, std::string("b2_scene_set_param: unknown key '") + key + "'");
+    if (!std::strcmp(what, "value")) {
+        if (bytes != 3 * sizeof(float)) return fail(-2, "b2_scene_set_param: reflectance.value expects 3 floats");
+        if (s->bsdfs[idx].reflectance_tex >= 0) return fail(-2, "b2_scene_set_param: BSDF has a textured reflectance; use .data");
+        CUDA_OK(cudaMemcpyAsync(&s->bsdfs_dev[idx].refl[0], dev_ptr, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t) stream));
+        return 0;
+    }
+    if (!std::strcmp(what, "data")) {
+        int t = s->bsdfs[idx].reflectance_tex;
+        if (t < 0) return fail(-2, "b2_scene_set_param: BSDF has a constant reflectance; use .value");
+        if (s->textures[t].format != B2_TEX_F32) return fail(-2, "b2_scene_set_param: only fp32 textures are differentiable parameters (bitmap.cpp:208-218)");
+        if (bytes != s->texture_bytes[t]) return fail(-2, "b2_scene_set_param: texture size mismatch");
+        CUDA_OK(cudaMemcpyAsync((void *) s->textures[t].data, dev_ptr, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t) stream));
+        return 0;
+    }
+    return fail(-2, std::string("b2_scene_set_param: unknown key '") + key + "'");
+}
+
+// integrator.cpp:139-152,247-265
+static int derive_passes(const b2_scene *s, const b2_render_args *a, uint32_t &spp_per_pass, uint32_t &n_passes, uint64_t &wavefront) {
+    if (a->spp == 0) return fail(-2, "render: spp must be > 0");
+    const uint64_t npix = (uint64_t) s->d.sensor.crop_width * s->d.sensor.crop_height, limit = 0xffffffffull;
+    spp_per_pass = a->spp_per_pass ? std::min(a->spp_per_pass, a->spp) : a->spp;
+    wavefront = npix * spp_per_pass;
+    if (wavefront > limit) { spp_per_pass /= (uint32_t) ((wavefront + limit - 1) / limit); wavefront = npix * spp_per_pass; }
+    if (spp_per_pass == 0 || a->spp % spp_per_pass) return fail(-2, "sample_count must be a multiple of spp_per_pass");
+    n_passes = a->spp / spp_per_pass;
+    return 0;
+}
+
+static int setup_params(b2_scene *s, const b2_render_args *a, int mode, bool count, RenderParams &p, int &blocks, size_t &smem, uint64_t lane_begin, uint64_t lane_end) {
+    uint32_t spp_per_pass, n_passes; uint64_t wavefront;
+    if (int rc = derive_passes(s, a, spp_per_pass, n_passes, wavefront)) return rc;
+    if (!s->d.nodes && s->d.n_faces) return fail(-3, "render: b2_scene_build_accel has not been called");
+    if (a->max_depth < 0) return fail(-2, "render: max_depth = -1 (unbounded) is not supported; pass a finite depth");
+    const DSensor &sn = s->d.sensor;
+    p.sc = s->d;
+    p.seed = a->seed; p.spp_per_pass = spp_per_pass; p.n_passes = mode == MODE_RENDER ? n_passes : 1;
+    p.spp_shift = 0xffffffffu;
+    for (uint32_t k = 0; k < 32; ++k) if ((1u << k) == spp_per_pass) p.spp_shift = k;
+    p.max_depth = a->max_depth; p.rr_depth = a->rr_depth; p.env_warp = a->env_warp;
+    p.filter_n = sn.rfilter == B2_RFILTER_BOX ? 0 : (int) std::ceil(sn.rfilter_radius - .5f);
+    p.lane_begin = lane_begin; p.lane_end = lane_end ? std::min(lane_end, wavefront) : wavefront;
+    if (p.lane_begin > p.lane_end) return fail(-2, "render: lane_begin > lane_end");
+    const uint32_t W = (uint32_t) sn.crop_width;
+    // unit = run of pixels of one row x all samples; aim for >= 8 units per resident CTA, 1k..8k lanes per unit
+    const int variant = mode == MODE_RENDER ? a->variant : B2_VARIANT_PRB;
+    if (variant < 0 || variant > B2_VARIANT_PRB) return fail(-2, "render: unknown variant");
+    uint64_t shard_lanes = p.lane_end - p.lane_begin;
+    uint64_t target = a->chunk_lanes ? a->chunk_lanes : std::min<uint64_t>(8192, std::max<uint64_t>(1024, shard_lanes / ((uint64_t) s->ctx->sm_count * 2 * 8 + 1)));
+    uint32_t P = (uint32_t) std::min<uint64_t>(W, std::max<uint64_t>(1, (target + spp_per_pass - 1) / spp_per_pass));
+    p.unit_pixels = P; p.units_per_row = (W + P - 1) / P;
+    p.tile_cols = P + 2 * p.filter_n + 1; p.tile_rows = 2 * p.filter_n + 2;
+    smem = mode == MODE_BACKWARD ? 0 : sizeof(float4) * (size_t) p.tile_cols * p.tile_rows;
+    if (smem > 200 * 1024) return fail(-2, "render: film tile does not fit in shared memory (lower chunk_lanes)");
+    if (p.lane_end > p.lane_begin) {
+        uint64_t pix0 = p.lane_begin / spp_per_pass, pix1 = (p.lane_end - 1) / spp_per_pass;
+        p.unit_begin = (uint32_t) ((pix0 / W) * p.units_per_row + (pix0 % W) / P);
+        p.unit_end = (uint32_t) ((pix1 / W) * p.units_per_row + (pix1 % W) / P) + 1;
+    } else p.unit_begin = p.unit_end = 0;
+    p.unit_counter = s->unit_counter; p.counters = count ? s->counters_dev : nullptr;
+    p.grad_in = nullptr; p.wfilm = nullptr; p.n_targets = 0; p.film = nullptr;
+    int occ = render_occupancy(variant, mode, count, smem);
+    if (occ <= 0) return fail(-12, "render: kernel cannot be resident (occupancy 0)");
+    uint32_t units = p.unit_end - p.unit_begin;
+    blocks = (int) std::max<uint32_t>(1, std::min<uint32_t>(units, (uint32_t) (occ * s->ctx->sm_count)));
+    return 0;
+}
+
+static void export_counters(const unsigned long long *h, uint64_t launches, b2_counters *o) {
+    o->samples = h[C_SAMPLES]; o->closest_rays = h[C_CLOSEST]; o->shadow_rays = h[C_SHADOW]; o->vertices = h[C_VERTICES]; o->tex_evals = h[C_TEX];
+    o->nee_area = h[C_NEE_AREA]; o->nee_env = h[C_NEE_ENV]; o->env_escapes = h[C_ESCAPES]; o->splat_taps = h[C_TAPS]; o->grad_atomics = h[C_GRAD];
+    o->node_fetches = h[C_NODES]; o->tri_fetches = h[C_TRIS]; o->launches = launches;
+}
+
+int b2_render(b2_scene *s, const b2_render_args *a, float *film, uintptr_t stream, b2_counters *counters) {
+    if (!s || !a || !film) return fail(-1, "b2_render: null argument");
+    CUDA_OK(cudaSetDevice(s->ctx->device));
+    cudaStream_t st = (cudaStream_t) stream;
+    RenderParams p; int blocks; size_t smem; const bool count = counters != nullptr;
+    if (int rc = setup_params(s, a, MODE_RENDER, count, p, blocks, smem, a->lane_begin, a->lane_end)) return rc;
+    p.film = film;
+    uint64_t launches = 0;
+    CUDA_OK(cudaMemsetAsync(s->unit_counter, 0, 16, st));
+    if (count) CUDA_OK(cudaMemsetAsync(s->counters_dev, 0, sizeof(unsigned long long) * C_N, st));
+    if (p.unit_end > p.unit_begin) { launch_render(a->variant, MODE_RENDER, count, p, blocks, smem, st); launches++; }
+    CUDA_OK(cudaGetLastError());
+    if (count) {
+        unsigned long long h[C_N];
+        CUDA_OK(cudaMemcpyAsync(h, s->counters_dev, sizeof(h), cudaMemcpyDeviceToHost, st));
+        CUDA_OK(cudaStreamSynchronize(st));
+        export_counters(h, launches, counters);
+    }
+    s->launches += launches;
+    return 0;
+}
+
+int b2_develop(b2_scene *s, const float *film, float *image, uintptr_t stream) {
+    if (!s || !film || !image) return fail(-1, "b2_develop: null argument");
+    CUDA_OK(cudaSetDevice(s->ctx->device));
+    launch_develop(film, image, (uint32_t) s->d.sensor.crop_width * s->d.sensor.crop_height, (cudaStream_t) stream);
+    CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_in, const b2_grad_target *targets, int n_targets,
+                       uintptr_t stream, b2_counters *counters) {
+    if (!s || !a || !grad_in || (n_targets && !targets)) return fail(-1, "b2_render_backward: null argument");
+    if (n_targets < 0 || n_targets > kMaxGradTargets) return fail(-2, "b2_render_backward: too many gradient targets");
+    CUDA_OK(cudaSetDevice(s->ctx->device));
+    cudaStream_t st = (cudaStream_t) stream;
+    uint32_t spp_per_pass, n_passes; uint64_t wavefront;
+    if (int rc = derive_passes(s, a, spp_per_pass, n_passes, wavefront)) return rc;
+    if (n_passes != 1) return fail(-2, "render_backward: wavefront exceeds 2^32 lanes (common.py:358-363)");
+    const size_t film_bytes = sizeof(float) * 4 * (size_t) s->d.sensor.crop_width * s->d.sensor.crop_height;
+    if (!s->wfilm) { CUDA_OK(cudaMalloc((void **) &s->wfilm, film_bytes)); s->allocs.push_back(s->wfilm); }
+    const bool count = counters != nullptr;
+    uint64_t launches = 0;
+    // (1) weight film of this sample set: splat weight 1 for every lane of the wavefront (common.py:728-744)
+    {
+        RenderParams p; int blocks; size_t smem;
+        if (int rc = setup_params(s, a, MODE_WEIGHTS, false, p, blocks, smem, 0, 0)) return rc;
+        p.film = s->wfilm;
+        CUDA_OK(cudaMemsetAsync(s->wfilm, 0, film_bytes, st));
+        CUDA_OK(cudaMemsetAsync(s->unit_counter, 0, 16, st));
+        launch_render(B2_VARIANT_PRB, MODE_WEIGHTS, false, p, blocks, smem, st); launches++;
+        CUDA_OK(cudaGetLastError());
+    }
+    // (2) primal pass + adjoint replay per lane (common.py:750-773)
+    {
+        RenderParams p; int blocks; size_t smem;
+        if (int rc = setup_params(s, a, MODE_BACKWARD, count, p, blocks, smem, a->lane_begin, a->lane_end)) return rc;
+        p.grad_in = grad_in; p.wfilm = s->wfilm; p.n_targets = n_targets;
+        for (int t = 0; t < n_targets; ++t) {
+            const b2_grad_target &g = targets[t];
+            if (g.bsdf < 0 || g.bsdf >= (int) s->bsdfs.size() || !g.grad) return fail(-2, "b2_render_backward: bad gradient target");
+            const bool textured = s->bsdfs[g.bsdf].reflectance_tex >= 0;
+            if ((g.kind == 1) != textured) return fail(-2, "b2_render_backward: target kind does not match the BSDF's reflectance");
+            if (s->bsdfs[g.bsdf].type == B2_BSDF_DIELECTRIC) return fail(-2, "b2_render_backward: dielectric reflectance is not a supported target");
+            p.targets[t] = GradTargetDev{ g.bsdf, g.kind, g.grad };
+        }
+        CUDA_OK(cudaMemsetAsync(s->unit_counter, 0, 16, st));
+        if (count) CUDA_OK(cudaMemsetAsync(s->counters_dev, 0, sizeof(unsigned long long) * C_N, st));
+        if (p.unit_end > p.unit_begin) { launch_render(B2_VARIANT_PRB, MODE_BACKWARD, count, p, blocks, smem, st); launches++; }
+        CUDA_OK(cudaGetLastError());
+    }
+    if (count) {
+        unsigned long long h[C_N];
+        CUDA_OK(cudaMemcpyAsync(h, s->counters_dev, sizeof(h), cudaMemcpyDeviceToHost, st));
+        CUDA_OK(cudaStreamSynchronize(st));
+        export_counters(h, launches, counters);
+    }
+    s->launches += launches;
+    return 0;
+}
+
+int b2_trace(b2_scene *s, const float *rays, uint64_t n, int any_hit, b2_hit *hits, uintptr_t stream) {
+    if (!s || (n && (!rays || !hits))) return fail(-1, "b2_trace: null argument");
+    if (!s->d.nodes && s->d.n_faces) return fail(-3, "b2_trace: b2_scene_build_accel has not been called");
+    CUDA_OK(cudaSetDevice(s->ctx->device));
+    launch_trace(s->d, rays, n, any_hit, hits, (cudaStream_t) stream);
+    CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int b2_render_host(b2_scene *s, const b2_render_args *a, float *film_host, float *image_host, b2_counters *counters) {
+    if (!s || !a || !film_host) return fail(-1, "b2_render_host: null argument");
+    CUDA_OK(cudaSetDevice(s->ctx->device));
+    const size_t npix = (size_t) s->d.sensor.crop_width * s->d.sensor.crop_height;
+    float *film = nullptr, *image = nullptr;
+    CUDA_OK(cudaMalloc((void **) &film, npix * 16));
+    cudaError_t e = cudaMalloc((void **) &image, npix * 12);
+    if (e != cudaSuccess) { cudaFree(film); return fail(-10, cudaGetErrorString(e)); }
+    int rc = 0;
+    auto guard = [&](cudaError_t err) { if (err != cudaSuccess && rc == 0) rc = fail(-10, cudaGetErrorString(err)); };
+    guard(cudaMemcpy(film, film_host, npix * 16, cudaMemcpyHostToDevice));
+    if (rc == 0) rc = b2_render(s, a, film, 0, counters);
+    if (rc == 0 && image_host) rc = b2_develop(s, film, image, 0);
+    if (rc == 0) guard(cudaMemcpy(film_host, film, npix * 16, cudaMemcpyDeviceToHost));
+    if (rc == 0 && image_host) guard(cudaMemcpy(image_host, image, npix * 12, cudaMemcpyDeviceToHost));
+    cudaFree(film); cudaFree(image);
+    return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,154 @@
+"""Device-side scene handle: thin Python wrapper over the C-ABI (``capi``) using PyTorch only for device
+memory, streams and DLPack exchange.
+
+Mirrors what the reference's integrators get from a live ``mi.Scene``: an acceleration structure that is built once
+(``Scene`` constructor, mitsuba3/src/render/scene.cpp:22-111) and parameters that can be updated in place
+(``SceneParameters.update``, mitsuba3/src/python/python/util.py:271-337).  All numerics live in ``csrc``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+from .scene import SceneDesc
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def as_device_tensor(x, device, dtype=None):
+    """Accept torch tensors, numpy arrays and anything exporting ``__dlpack__`` (e.g. Dr.Jit ``TensorXf``)."""
+    torch = _torch()
+    if isinstance(x, torch.Tensor):
+        t = x
+    elif hasattr(x, "__dlpack__"):
+        t = torch.from_dlpack(x)
+    else:
+        t = torch.as_tensor(np.asarray(x))
+    if dtype is not None and t.dtype != dtype:
+        t = t.to(dtype)
+    return t.to(device).contiguous()
+
+
+class DeviceScene:
+    """Owns a ``b2_scene`` on one CUDA device."""
+
+    def __init__(self, scene, device: int = 0, base_path: str = "."):
+        torch = _torch()
+        self.lib = capi.load_library()
+        if not torch.cuda.is_available():
+            raise capi.B2Error("b2path needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.desc = scene if isinstance(scene, SceneDesc) else SceneDesc(scene, base_path)
+        self.device = torch.device("cuda", device)
+        self.ctx = C.c_void_p()
+        capi.check(self.lib.b2_init(device, C.byref(self.ctx)))
+        self.handle = C.c_void_p()
+        capi.check(self.lib.b2_scene_create(self.ctx, C.byref(self.desc.c), C.byref(self.handle)))
+        self.build_stats = capi.BuildStats()
+        capi.check(self.lib.b2_scene_build_accel(self.handle, 0, self._stream(), C.byref(self.build_stats)))
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.b2_scene_destroy(self.handle); self.handle = None
+        if getattr(self, "ctx", None):
+            self.lib.b2_shutdown(self.ctx); self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _stream(self) -> int:
+        return int(_torch().cuda.current_stream(self.device).cuda_stream)
+
+    @property
+    def film_shape(self):
+        return self.desc.film_shape
+
+    def rebuild_accel(self):
+        capi.check(self.lib.b2_scene_build_accel(self.handle, 0, self._stream(), C.byref(self.build_stats)))
+        return self.build_stats.as_dict()
+
+    def make_args(self, seed=0, spp=None, max_depth=8, rr_depth=4, variant=capi.VARIANT_PATH, spp_per_pass=0,
+                  lane_begin=0, lane_end=0, chunk_lanes=0, env_warp=capi.ENV_WARP_HIERARCHICAL):
+        a = capi.RenderArgs()
+        a.seed = int(seed) & 0xffffffff
+        a.spp = int(spp or self.desc.spp); a.spp_per_pass = int(spp_per_pass)
+        a.max_depth, a.rr_depth, a.variant = int(max_depth), int(rr_depth), int(variant)
+        a.kernel = capi.KERNEL_MEGAKERNEL; a.env_warp = int(env_warp)
+        a.lane_begin, a.lane_end, a.chunk_lanes = int(lane_begin), int(lane_end), int(chunk_lanes)
+        return a
+
+    def wavefront_size(self, spp, spp_per_pass=0):
+        """Lanes per pass (integrator.cpp:247-265)."""
+        h, w = self.film_shape
+        spp_pp = min(spp_per_pass, spp) if spp_per_pass else spp
+        n = h * w * spp_pp
+        if n > 0xffffffff:
+            spp_pp //= (n + 0xffffffff - 1) // 0xffffffff
+            n = h * w * spp_pp
+        return n
+
+    def new_film(self):
+        h, w = self.film_shape
+        return _torch().zeros((h, w, 4), dtype=_torch().float32, device=self.device)
+
+    def render_film(self, film=None, counters=False, **kw):
+        """Accumulates RGBW into ``film`` ([H, W, 4] float32 on this device) and returns (film, counters | None)."""
+        a = self.make_args(**kw)
+        if film is None:
+            film = self.new_film()
+        cnt = capi.Counters() if counters else None
+        capi.check(self.lib.b2_render(self.handle, C.byref(a), film.data_ptr(), self._stream(), C.byref(cnt) if counters else None))
+        return film, (cnt.as_dict() if counters else None)
+
+    def develop(self, film):
+        h, w = self.film_shape
+        img = _torch().empty((h, w, 3), dtype=_torch().float32, device=self.device)
+        capi.check(self.lib.b2_develop(self.handle, film.data_ptr(), img.data_ptr(), self._stream()))
+        return img
+
+    def render(self, **kw):
+        film, cnt = self.render_film(**kw)
+        return self.develop(film), cnt
+
+    def render_host(self, film_host: np.ndarray, image_host: np.ndarray | None = None, **kw):
+        """Host-buffer entry point (``b2_render_host``): upload, render, develop and download inside the call."""
+        a = self.make_args(**kw)
+        capi.check(self.lib.b2_render_host(self.handle, C.byref(a), film_host.ctypes.data,
+                                           image_host.ctypes.data if image_host is not None else None, None))
+        return film_host, image_host
+
+    def render_backward(self, grad_in, targets, counters=False, **kw):
+        """targets: list of (bsdf_index, kind, grad tensor on this device); gradients are accumulated in place."""
+        kw.pop("variant", None)
+        a = self.make_args(variant=capi.VARIANT_PRB, **kw)
+        gi = as_device_tensor(grad_in, self.device, _torch().float32)
+        arr = (capi.GradTarget * max(1, len(targets)))()
+        for i, (b, k, g) in enumerate(targets):
+            assert g.is_cuda and g.dtype == _torch().float32 and g.is_contiguous()
+            arr[i].bsdf, arr[i].kind, arr[i].grad = int(b), int(k), g.data_ptr()
+        cnt = capi.Counters() if counters else None
+        capi.check(self.lib.b2_render_backward(self.handle, C.byref(a), gi.data_ptr(), arr, len(targets), self._stream(),
+                                               C.byref(cnt) if counters else None))
+        return cnt.as_dict() if counters else None
+
+    def trace(self, rays, any_hit=False):
+        torch = _torch()
+        r = as_device_tensor(rays, self.device, torch.float32).reshape(-1, 8)
+        hits = torch.empty((r.shape[0], 4), dtype=torch.float32, device=self.device)
+        capi.check(self.lib.b2_trace(self.handle, r.data_ptr(), r.shape[0], int(any_hit), hits.data_ptr(), self._stream()))
+        torch.cuda.synchronize(self.device)
+        out = hits.cpu().numpy()
+        return out.view(np.dtype([("t", "f4"), ("u", "f4"), ("v", "f4"), ("prim", "u4")])).reshape(-1)
+
+    def set_param(self, bsdf_index: int, what: str, value):
+        """what = 'value' (3 floats) | 'data' ([H, W, 3] fp32 texture)."""
+        t = as_device_tensor(value, self.device, _torch().float32)
+        key = f"{int(bsdf_index)}.reflectance.{what}".encode()
+        capi.check(self.lib.b2_scene_set_param(self.handle, key, t.data_ptr(), t.numel() * 4, self._stream()))

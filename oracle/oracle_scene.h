@@ -183,7 +183,8 @@ struct Scene {
             if (n.count) {
                 for (uint32_t i = 0; i < n.count; ++i) {
                     uint32_t f = prims[n.left + i]; float t, u, v; c.tris++;
-                    if (tri_test(ray, f, ray.maxt, t, u, v) && (t < best.t || !best.valid())) best = Hit{ t, u, v, f };
+                    // deterministic tie rule: equal t -> lower face index wins, independent of traversal order
+                    if (tri_test(ray, f, ray.maxt, t, u, v) && (!best.valid() || t < best.t || (t == best.t && f < best.face))) best = Hit{ t, u, v, f };
                 }
             } else { stack[sp++] = n.left; stack[sp++] = n.left + 1; }
         }
