@@ -1,0 +1,75 @@
+"""Small scene dictionaries shared by the CPU and GPU tests (all generated from integer seeds)."""
+import numpy as np
+
+from mitsuba3_experiments_b200.scene import T
+from mitsuba3_experiments_b200.scenes import cornell_box
+
+
+def value_noise_texture(h=64, w=96, seed=2, dtype=np.float32):
+    rng = np.random.RandomState(seed)
+    t = rng.uniform(0.15, 0.95, size=(h, w, 3)).astype(np.float32)
+    return t.astype(dtype)
+
+
+def sky_envmap(h=32, w=64):
+    """Closed-form lat-long map: sky gradient plus a bright lobe (kept small for the tests)."""
+    v, u = np.meshgrid((np.arange(h) + 0.5) / h, (np.arange(w) + 0.5) / w, indexing="ij")
+    sky = 0.3 + 0.7 * (1.0 - v)
+    sun = 40.0 * np.exp(-((u - 0.3) ** 2 + (v - 0.25) ** 2) / 0.004)
+    img = np.stack([sky * 0.6 + sun, sky * 0.8 + sun * 0.9, sky + sun * 0.7], axis=-1)
+    return img.astype(np.float32)
+
+
+def random_mesh(n_tris, seed, extent=1.0, size=0.15):
+    rng = np.random.RandomState(seed)
+    c = rng.uniform(-extent, extent, size=(n_tris, 1, 3))
+    v = c + rng.uniform(-size, size, size=(n_tris, 3, 3))
+    pos = v.reshape(-1, 3).astype(np.float32)
+    faces = np.arange(3 * n_tris, dtype=np.uint32).reshape(-1, 3)
+    return pos, faces
+
+
+def materials_scene(width=48, height=40, spp=8, envmap=True, filter_type="gaussian", mesh_light=True):
+    """Cornell box variant exercising every BSDF / emitter / texture path of the scope table."""
+    d = cornell_box(width, height, spp)
+    d["sensor"]["film"]["rfilter"] = {"type": filter_type}
+    d["metal"] = {"type": "twosided", "nested": {"type": "roughconductor", "distribution": "ggx", "alpha": 0.2,
+                                                  "eta": [1.657, 0.880, 0.521], "k": [9.224, 6.270, 4.837]}}
+    d["beck"] = {"type": "roughconductor", "distribution": "beckmann", "alpha_u": 0.1, "alpha_v": 0.25,
+                 "eta": [0.2, 0.92, 1.1], "k": [3.9, 2.45, 2.14]}
+    d["glass"] = {"type": "dielectric", "int_ior": 1.5, "ext_ior": 1.0}
+    d["tex"] = {"type": "twosided", "nested": {"type": "diffuse", "reflectance": {"type": "bitmap", "data": value_noise_texture(), "raw": True}}}
+    d["tex16"] = {"type": "diffuse", "reflectance": {"type": "bitmap", "data": value_noise_texture(32, 32, 5, np.float16),
+                                                     "wrap_mode": "mirror", "to_uv": [[2.5, 0, 0.1], [0, 2.5, -0.2], [0, 0, 1]]}}
+    d["small-box"]["bsdf"] = {"type": "ref", "id": "glass"}
+    d["large-box"]["bsdf"] = {"type": "ref", "id": "metal"}
+    d["back"]["bsdf"] = {"type": "ref", "id": "tex"}
+    d["floor"]["bsdf"] = {"type": "ref", "id": "tex16"}
+    d["red-wall"]["bsdf"] = {"type": "ref", "id": "beck"}
+    if mesh_light:
+        pos = np.array([[-0.6, 0.2, -0.6], [-0.3, 0.2, -0.6], [-0.45, 0.45, -0.5], [-0.45, 0.3, -0.3]], np.float32)
+        faces = np.array([[0, 1, 2], [0, 3, 1], [1, 3, 2], [0, 2, 3]], np.uint32)
+        d["tetra-light"] = {"type": "mesh", "positions": pos, "faces": faces, "bsdf": {"type": "ref", "id": "white"},
+                            "emitter": {"type": "area", "radiance": {"type": "rgb", "value": [6.0, 8.0, 5.0]}}}
+    if envmap:
+        del d["ceiling"]
+        d["env"] = {"type": "envmap", "data": sky_envmap(), "scale": 0.8,
+                    "to_world": T().rotate([0, 1, 0], 35.0).rotate([1, 0, 0], 10.0)}
+    return d
+
+
+def triangles_scene(n_tris=20000, width=64, height=48, spp=4, seed=3):
+    """Random-triangle stress scene (C4 in miniature): one rectangle light, constant environment."""
+    pos, faces = random_mesh(n_tris, seed)
+    return {
+        "type": "scene",
+        "sensor": {"type": "perspective", "fov": 40, "near_clip": 0.01, "far_clip": 100.0,
+                   "to_world": T().look_at([0, 0, 3.5], [0, 0, 0], [0, 1, 0]),
+                   "sampler": {"type": "independent", "sample_count": spp},
+                   "film": {"type": "hdrfilm", "width": width, "height": height, "rfilter": {"type": "tent"}}},
+        "soup": {"type": "mesh", "positions": pos, "faces": faces,
+                 "bsdf": {"type": "twosided", "nested": {"type": "diffuse", "reflectance": {"type": "rgb", "value": [0.7, 0.6, 0.5]}}}},
+        "light": {"type": "rectangle", "to_world": T().translate([0, 1.4, 0]).rotate([1, 0, 0], 90).scale(0.5),
+                  "emitter": {"type": "area", "radiance": {"type": "rgb", "value": [50, 50, 50]}}},
+        "sky": {"type": "constant", "radiance": {"type": "rgb", "value": [0.4, 0.5, 0.6]}},
+    }

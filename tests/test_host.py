@@ -1,0 +1,128 @@
+"""CPU-only tests of the host layer: the C-ABI library loads and exports every declared symbol (no compute calls),
+header <-> ctypes struct layouts agree, scene ingestion, integrator properties and error behaviour."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+import pytest
+
+from mitsuba3_experiments_b200 import capi
+from mitsuba3_experiments_b200.scene import SceneDesc, parse_fov, gaussian_coeffs
+from mitsuba3_experiments_b200.scenes import cornell_box
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_loads_and_exports_all_symbols():
+    if not os.path.exists(capi.LIB_PATH):
+        capi.build_library()
+    lib = capi.load_library()
+    header = open(os.path.join(ROOT, "include", "b2path.h")).read()
+    declared = set(re.findall(r"\b(b2_[a-z_]+)\s*\(", header))
+    assert declared == set(capi.EXPORTS), declared ^ set(capi.EXPORTS)
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.b2_abi_version() == capi.B2_ABI_VERSION
+
+
+def test_no_gpu_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    lib = capi.load_library()
+    ctx = C.c_void_p()
+    rc = lib.b2_init(0, C.byref(ctx))
+    assert rc != 0 and b"no CUDA device" in lib.b2_last_error()
+    from mitsuba3_experiments_b200.runtime import DeviceScene
+    with pytest.raises(capi.B2Error):
+        DeviceScene(cornell_box(8, 8))
+
+
+def test_struct_layouts_match_header():
+    """Compile a tiny C program printing sizeof/offsetof for every ABI struct and compare with ctypes."""
+    fields = {
+        "b2_texture": (capi.Texture, ["data", "width", "to_uv"]),
+        "b2_bsdf": (capi.Bsdf, ["type", "reflectance", "k", "ior"]),
+        "b2_mesh": (capi.Mesh, ["first_vertex", "bsdf", "flags"]),
+        "b2_emitter": (capi.Emitter, ["type", "radiance", "to_world", "inv_area", "cdf_offset"]),
+        "b2_envmap": (capi.Envmap, ["data", "scale", "bsphere_radius", "warp_data", "level_size", "alias_idx"]),
+        "b2_sensor": (capi.Sensor, ["sample_to_camera", "near_clip", "crop_height", "rfilter_radius", "gaussian_coeff"]),
+        "b2_scene_desc": (capi.SceneDesc, ["abi_version", "positions", "meshes", "n_area_cdf", "envmap", "sensor"]),
+        "b2_render_args": (capi.RenderArgs, ["seed", "variant", "lane_begin", "lane_end", "chunk_lanes"]),
+        "b2_counters": (capi.Counters, ["samples", "launches"]),
+        "b2_build_stats": (capi.BuildStats, ["ms_total", "n_nodes8", "node_bytes"]),
+        "b2_hit": (capi.Hit, ["t", "prim"]),
+        "b2_grad_target": (capi.GradTarget, ["bsdf", "grad"]),
+    }
+    src = ['#include <stdio.h>', '#include <stddef.h>', '#include "b2path.h"', 'int main(void) {']
+    for s, (_, fs) in fields.items():
+        src.append(f'printf("{s} %zu\\n", sizeof({s}));')
+        for f in fs:
+            src.append(f'printf("{s}.{f} %zu\\n", offsetof({s}, {f}));')
+    src.append("return 0; }")
+    with tempfile.TemporaryDirectory() as td:
+        open(os.path.join(td, "t.c"), "w").write("\n".join(src))
+        subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), "-o", os.path.join(td, "t"), os.path.join(td, "t.c")], check=True)
+        out = subprocess.run([os.path.join(td, "t")], capture_output=True, text=True, check=True).stdout
+    for line in out.strip().splitlines():
+        name, val = line.split()
+        if "." in name:
+            s, f = name.split(".")
+            assert getattr(fields[s][0], f).offset == int(val), name
+        else:
+            assert C.sizeof(fields[name][0]) == int(val), name
+
+
+def test_cornell_box_ingestion():
+    sd = SceneDesc(cornell_box(256, 256, 16))
+    assert sd.c.n_faces == 36 and sd.c.n_vertices == 72 and sd.c.n_emitters == 1 and sd.c.n_bsdfs == 3
+    assert sd.emitters[0].shape_kind == capi.SHAPE_RECTANGLE
+    np.testing.assert_allclose(1.0 / sd.emitters[0].inv_area, 4 * 0.23 * 0.19, rtol=1e-5)
+    # rectangle triangulation (rectangle.cpp:102-110): faces (1,2,0), (1,3,2)
+    first = sd.meshes[0].first_face
+    assert (sd.faces[first:first + 2] - sd.meshes[0].first_vertex).tolist() == [[1, 2, 0], [1, 3, 2]]
+    assert sd.spp == 16 and sd.film_shape == (256, 256)
+    assert sd.sensor.rfilter == capi.RFILTER_GAUSSIAN and abs(sd.sensor.rfilter_radius - 2.0) < 1e-6
+
+
+def test_parse_fov_and_filters():
+    assert parse_fov({"fov": 39.3077, "fov_axis": "smaller"}, 1.0) == pytest.approx(39.3077)
+    assert parse_fov({"fov": 40, "fov_axis": "y"}, 16 / 9) == pytest.approx(65.8, abs=0.2)
+    c, r = gaussian_coeffs(0.5)
+    assert r == 2.0 and c.dtype == np.float32 and len(c) == 10
+    with pytest.raises(ValueError):
+        SceneDesc({"type": "scene", "sensor": {"type": "perspective", "fov": 45, "film": {"type": "hdrfilm", "rfilter": {"type": "gaussian", "stddev": 1.0}}}})
+    with pytest.raises(ValueError):
+        SceneDesc({"type": "scene", "sensor": {"type": "thinlens", "fov": 45}})
+    with pytest.raises(ValueError):
+        SceneDesc({"type": "scene", "s": {"type": "sphere"}, "sensor": {"type": "perspective", "fov": 45}})
+
+
+def test_integrator_props_and_registry():
+    from mitsuba3_experiments_b200 import integrator as I
+    assert (I.Path().max_depth, I.Path().rr_depth) == (8, 4)                       # path.py:23-24
+    assert (I.PathIntegrator().max_depth, I.PathIntegrator().rr_depth) == (8, 2)   # path-mis.py:21-22
+    assert (I.PRBIntegrator().max_depth, I.PRBIntegrator().rr_depth) == (6, 5)     # common.py:28-40
+    assert I.Path({"max_depth": 3, "rr_depth": 2}).max_depth == 3
+    with pytest.raises(RuntimeError):
+        I.Path({"rr_depth": 0})
+    with pytest.raises(RuntimeError):
+        I.Path({"max_depth": -2})
+    with pytest.raises(RuntimeError):
+        I.Path().sample(None, None, None)
+    assert isinstance(I.make_integrator({"type": "path_test", "max_depth": 5}), I.PathIntegrator)
+    I.register_integrator("custom", lambda props: I.Path(props))
+    assert isinstance(I.make_integrator("custom"), I.Path)
+    assert "max_depth = 8" in I.Path().to_string()
+
+
+def test_host_tea_matches_oracle(oracle_lib):
+    from mitsuba3_experiments_b200.integrator import sample_tea_32
+    for v0, v1 in [(0, 1), (1, 1), (12345, 1), (0xffffffff, 7)]:
+        out = np.zeros(2, np.uint32)
+        oracle_lib.orc_tea32(v0, v1, 4, out.ctypes.data_as(C.c_void_p))
+        assert sample_tea_32(v0, v1) == (int(out[0]), int(out[1]))
