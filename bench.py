@@ -1,0 +1,309 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark: path Msamples/s on the bedroom (stand-in) 720p, 64 spp per GPU, path-mis loop.
+
+One *step* = one full render of the workload: every rank renders its image bands (all samples of those pixels) into a
+private RGBW film, the films are summed with one NCCL all-reduce, the result is developed.  Weak scaling: the job at
+N GPUs is the 1280x720 image at 64*N spp, i.e. 58 982 400 paths per GPU (BASELINE.json configs[1] at N = 1).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b2|reference] [--workload bedroom|cornell]
+
+Prints ONE JSON line (rank 0).  `value` = device-timed throughput with the scene resident in HBM; `e2e` = the same
+metric through the host-buffer C-ABI call (film H2D + render + develop + film/image D2H inside the timed region);
+`roofline` = algorithmic bytes of the render kernel (SURVEY.md 8d formula x exact event counters) / its CUDA-event
+duration, against the measured HBM copy bandwidth; `cpu_baseline` = the CPU oracle (a port of the reference's
+llvm_ad_rgb path; Mitsuba itself cannot be installed here) on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import math
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+HBM_FALLBACK_GBS = 6650.0
+
+
+def measured_peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured"
+    except Exception:
+        return HBM_FALLBACK_GBS, "fallback"
+
+
+def build_workload(name, n_gpus):
+    from mitsuba3_experiments_b200 import scenes
+    if name == "bedroom":
+        spp = 64 * n_gpus
+        d = scenes.bedroom_standin(1280, 720, spp)
+        return d, dict(variant=1, max_depth=8, rr_depth=2), spp, "bedroom stand-in 1280x720 (1.8M tris, 2 area lights + envmap), path-mis.py loop"
+    if name == "cornell":
+        spp = 16 * n_gpus
+        return scenes.cornell_box(256, 256, spp), dict(variant=0, max_depth=8, rr_depth=4), spp, "mi.cornell_box() 256x256, path.py loop"
+    raise SystemExit(f"unknown workload {name}")
+
+
+def algorithmic_bytes(cnt, n_faces, tex_bytes_per_eval=32):
+    """bytes any implementation must move from global memory for these events."""
+    D = max(1, math.ceil(math.log(max(n_faces / 3.0, 1.0), 8)))
+    b_ray = 80 * D + 48 * 3
+    return ((cnt["closest_rays"] + cnt["shadow_rays"]) * b_ray + cnt["vertices"] * 140 + (cnt["tex_evals"] // 2) * tex_bytes_per_eval
+            + cnt["nee_area"] * 64 + cnt["nee_env"] * 224 + cnt["env_escapes"] * 48 + cnt["splat_taps"] * 16), b_ray
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, n in names.items():
+                    if r & bit:
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def result(self):
+        self.stop_flag = True
+        if self.nv is None or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["nvml unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def cpu_oracle_rate(scene_dict, kw, label_spp=1, threads=None):
+    """Times the CPU oracle on `label_spp` samples per pixel of the workload (BVH build excluded, like the GPU arm)."""
+    from mitsuba3_experiments_b200.scene import SceneDesc
+    from oracle.oracle_py import OracleScene, lib
+    desc = SceneDesc(scene_dict)
+    orc = OracleScene(desc)
+    if threads:
+        lib().orc_set_num_threads(threads)
+    t0 = time.perf_counter()
+    _, cnt = orc.render_film(seed=0, spp=label_spp, **kw)
+    dt = time.perf_counter() - t0
+    return cnt["samples"] / dt / 1e6, dt, lib().orc_num_threads(), cnt["samples"]
+
+
+def run_reference(args, rank):
+    """--impl reference: the reference's CPU path.  Mitsuba/Dr.Jit (llvm_ad_rgb) cannot be installed on this box, so the
+    timed implementation is the oracle port (oracle/), with all host threads, on a bounded sample per step."""
+    if rank != 0:
+        return
+    d, kw, spp, wl = build_workload(args.workload, 1)
+    from mitsuba3_experiments_b200.scene import SceneDesc
+    from oracle.oracle_py import OracleScene, lib
+    orc = OracleScene(SceneDesc(d))
+    sample_spp = 1
+    times, n = [], 0
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        _, cnt = orc.render_film(seed=i, spp=sample_spp, **kw)
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            times.append(dt); n = cnt["samples"]
+    ms = 1e3 * float(np.mean(times)); value = n / (ms * 1e-3) / 1e6
+    sample = f"{sample_spp} spp of the {spp} spp workload per step ({n} paths)"
+    line = {"impl": "reference", "metric": "path Msamples/s bedroom 720p", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": {"workload": wl, "sample": sample, "note": "CPU oracle port of the reference's llvm_ad_rgb path (Mitsuba not installable offline)"},
+            "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": lib().orc_num_threads(), "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b2", choices=["b2", "reference"])
+    ap.add_argument("--workload", default="bedroom", choices=["bedroom", "cornell"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-prb", action="store_true")
+    args = ap.parse_args()
+    rank_env = int(os.environ.get("RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank_env)
+
+    import torch
+    import torch.distributed as tdist
+    from mitsuba3_experiments_b200 import dist as b2dist
+    from mitsuba3_experiments_b200.integrator import make_integrator
+    from mitsuba3_experiments_b200.runtime import DeviceScene
+
+    rank, world, local = b2dist.init_from_env()
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    scene_dict, kw, spp, wl = build_workload(args.workload, world)
+    ds = DeviceScene(scene_dict, device=local)
+    H, W = ds.film_shape
+    n_total = ds.wavefront_size(spp)
+    plan = b2dist.shard_plan(n_total, spp, W, world, rank, bands_per_rank=8 if world > 1 else 1)
+    n_local = sum(b - a for a, b in plan)
+    film = ds.new_film()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def render_bands(counters=False):
+        tot = None
+        for a, b in plan:
+            _, c = ds.render_film(film=film, counters=counters, seed=0, spp=spp, lane_begin=a, lane_end=b, **kw)
+            if counters:
+                tot = c if tot is None else {k: tot[k] + c[k] for k in c}
+        return tot
+
+    def step():
+        film.zero_()
+        render_bands()
+        b2dist.merge_sum(film)
+        return ds.develop(film)
+
+    def barrier():
+        if world > 1:
+            tdist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # exact event counters of this rank's shard (one untimed, counted run) -> algorithmic bytes
+    film.zero_()
+    cnt = render_bands(counters=True)
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    clocks = ClockSampler(local); clocks.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    for e0, e1, e2 in ev:
+        flush.zero_()                       # L2 flush between timed iterations (outside the event pair)
+        film.zero_()
+        e0.record(); render_bands(); e1.record()
+        b2dist.merge_sum(film); img = ds.develop(film); e2.record()
+    barrier()
+    clk = clocks.result()
+    step_ms = [e0.elapsed_time(e2) for e0, _, e2 in ev]
+    kern_ms = [e0.elapsed_time(e1) for e0, e1, _ in ev]
+    t = torch.tensor([float(np.mean(step_ms)), float(np.mean(kern_ms))], device=dev, dtype=torch.float64)
+    if world > 1:
+        tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
+    ms_per_step, kernel_ms = float(t[0]), float(t[1])
+    value = n_total / (ms_per_step * 1e-3) / 1e6
+
+    # end-to-end through host buffers
+    film_h = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory()
+    img_h = torch.zeros((H, W, 3), dtype=torch.float32).pin_memory()
+    e2e_times = []
+    for i in range(2 + args.steps):
+        film_h.zero_()
+        barrier(); t0 = time.perf_counter()
+        if world == 1:
+            ds.render_host(film_h.numpy(), img_h.numpy(), seed=0, spp=spp, **kw)      # b2_render_host: H2D film, render, develop, D2H film + image
+        else:
+            film.copy_(film_h, non_blocking=True)
+            render_bands(); b2dist.merge_sum(film)
+            img_h.copy_(ds.develop(film), non_blocking=True); film_h.copy_(film, non_blocking=True)
+        barrier(); dt = time.perf_counter() - t0
+        if i >= 2:
+            e2e_times.append(dt)
+    t = torch.tensor([float(np.mean(e2e_times))], device=dev, dtype=torch.float64)
+    if world > 1:
+        tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
+    e2e_value = n_total / float(t[0]) / 1e6
+
+    if rank != 0:
+        return
+    peak, peak_kind = measured_peak()
+    alg_bytes, b_ray = algorithmic_bytes(cnt, ds.desc.c.n_faces)
+    achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
+    except Exception:
+        pass
+    launches_per_step = len(plan) + 1       # k_render per band + k_develop
+    line = {
+        "metric": "path Msamples/s bedroom 720p" if args.workload == "bedroom" else "path Msamples/s cornell 256x256",
+        "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl, "spp_per_gpu": spp // world, "spp_total": spp, "paths_per_step": n_total, "max_depth": kw["max_depth"],
+                   "rr_depth": kw["rr_depth"], "parallelism": f"image bands x all samples over {world} GPU(s), NCCL film all-reduce",
+                   "l2": "flushed between timed iterations (256 MiB memset)", "bvh_build_ms": ds.build_stats.ms_total,
+                   "bvh_nodes": ds.build_stats.n_nodes8, "triangles": ds.build_stats.n_tris,
+                   "rays_per_step_rank0": cnt["closest_rays"] + cnt["shadow_rays"], "Mrays_per_s_rank0": (cnt["closest_rays"] + cnt["shadow_rays"]) / (kernel_ms * 1e-3) / 1e6},
+        "clocks": clk,
+        "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": H * W * 16, "d2h_bytes_per_step": H * W * 16 + H * W * 12},
+        "gpu_launches": launches_per_step * args.steps,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "kernel": "k_render<path_mis>", "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg_bytes / len(plan),
+                     "bytes_per_ray": b_ray, "peak_kind": peak_kind,
+                     "note": "irregular-gather workload: bound by L2/HBM latency, not streaming bandwidth (see DESIGN.md)"},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        v, dt, cores, n = cpu_oracle_rate(scene_dict, kw, 1)
+        line["cpu_baseline"] = {"value": v, "unit": "Msamples/s", "cores": cores, "kind": "port",
+                                "sample": f"1 spp of the {spp} spp workload ({n} paths, {dt:.1f} s; BVH build excluded)"}
+    else:
+        line["cpu_baseline"] = None
+    if world == 1 and not args.no_prb:
+        try:
+            line["prb"] = prb_bench(local)
+        except Exception as e:  # the headline line must still print
+            line["prb"] = {"error": str(e)}
+    print(json.dumps(line), flush=True)
+
+
+def prb_bench(local, iters=5):
+    """BASELINE metric 2: PRB fwd + adjoint ms/iter -- Cornell box 512x512, 32 spp, textured `white` albedo 960x870 fp32."""
+    import torch
+    from mitsuba3_experiments_b200 import scenes
+    from mitsuba3_experiments_b200.integrator import PRBIntegrator, traverse
+    from mitsuba3_experiments_b200.runtime import DeviceScene
+    d = scenes.cornell_box(512, 512, 32)
+    tex = scenes.value_noise_rgb(960, 7, [0.6, 0.45, 0.3]).astype(np.float32)[:870]
+    d["white"] = {"type": "diffuse", "reflectance": {"type": "bitmap", "data": np.ascontiguousarray(tex), "raw": True}}
+    ds = DeviceScene(d, device=local)
+    prb = PRBIntegrator({"max_depth": 8, "rr_depth": 5})
+    params = traverse(ds); params.keep(["white.reflectance.data"])
+    target = prb.render(ds, seed=1, spp=32) * 0.5
+    times = []
+    for i in range(3 + iters):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        img = prb.render(ds, seed=i, spp=32, evaluate=False)
+        grad_in = 2.0 * (img - target) / img.numel()
+        params.zero_grad()
+        prb.render_backward(ds, params, grad_in, seed=1000 + i, spp=32)
+        e1.record(); torch.cuda.synchronize()
+        if i >= 3:
+            times.append(e0.elapsed_time(e1))
+    return {"metric": "PRB fwd+adjoint ms/iter", "value": float(np.mean(times)), "unit": "ms", "higher_is_better": False,
+            "config": "Cornell box 512x512, 32 spp, max_depth 8, rr_depth 5, white.reflectance = 870x960 fp32 bitmap (procedural stand-in for WoodFloor.jpg)",
+            "paths_per_iter": 512 * 512 * 32}
+
+
+if __name__ == "__main__":
+    main()

@@ -317,8 +317,9 @@ int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_i
     if (!s->wfilm) { CUDA_OK(cudaMalloc((void **) &s->wfilm, film_bytes)); s->allocs.push_back(s->wfilm); }
     const bool count = counters != nullptr;
     uint64_t launches = 0;
-    // (1) weight film of this sample set: splat weight 1 for every lane of the wavefront (common.py:728-744)
-    {
+    // (1) weight film of this sample set: splat weight 1 for every lane of the wavefront (common.py:728-744);
+    //     args->reserved bit 0: the weight film of an earlier call with the same (seed, spp) is still valid (sharded bands)
+    if (!(a->reserved & 1u)) {
         RenderParams p; int blocks; size_t smem;
         if (int rc = setup_params(s, a, MODE_WEIGHTS, false, p, blocks, smem, 0, 0)) return rc;
         p.film = s->wfilm;

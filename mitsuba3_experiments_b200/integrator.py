@@ -196,10 +196,10 @@ class PRBIntegrator(B2Integrator):
     default_max_depth, default_rr_depth = 6, 5
 
     def render_backward(self, scene, params: SceneParameters, grad_in, sensor=0, seed=0, spp=0, lane_begin=0, lane_end=0,
-                        counters=False):
+                        counters=False, reuse_weights=False):
         """Accumulates d(loss)/d(param) into ``params.grad[key]`` (side effect, like ``dr.grad(params[key])``)."""
         ds = self._scene(scene)
-        a = self._args(ds, seed, spp, lane_begin=lane_begin, lane_end=lane_end)
+        a = self._args(ds, seed, spp, lane_begin=lane_begin, lane_end=lane_end, reuse_weights=reuse_weights)
         a.pop("variant")
         self.last_counters = ds.render_backward(grad_in, params.targets(), counters=counters, **a)
         return None

@@ -355,6 +355,24 @@ int orc_render(void *hp, const b2_render_args *a, float *film_rgbw, b2_counters 
     return 0;
 }
 
+// debug: run ONE lane and record its closest-hit rays: out [max_records][11] = ray(7), t, u, v, face; returns #records; L -> rgb
+int orc_debug_lane(void *hp, const b2_render_args *a, uint32_t lane, float *out, int max_records, float *rgb) {
+    Handle *h = (Handle *) hp; const b2_scene_desc &d = h->desc; const b2_sensor &s = d.sensor;
+    uint32_t spp_per_pass, n_passes; uint64_t wavefront; derive_passes(d, *a, spp_per_pass, n_passes, wavefront);
+    Integrator integ(h->scene, a->max_depth, a->rr_depth); Counters c;
+    TraceLog log{ out, max_records, 0 }; g_trace_log = &log;
+    Sampler smp; smp.rng = sampler_seed(a->seed, lane);
+    int px, py; lane_to_pos(s, lane, spp_per_pass, px, py);
+    V2 j = smp.next_2d(); V2 sample_pos{ (float) px + j.x, (float) py + j.y };
+    Ray ray = camera_ray(s, adjusted_pos(s, sample_pos));
+    V3 L = a->variant == B2_VARIANT_PATH ? integ.sample_path_py(smp, ray, c)
+         : a->variant == B2_VARIANT_PATH_MIS ? integ.sample_path_mis(smp, ray, c)
+         : integ.sample_prb(true, smp, ray, V3(0.f), V3(0.f), [](int, const SI &, V3) {}, c);
+    g_trace_log = nullptr;
+    rgb[0] = L.x; rgb[1] = L.y; rgb[2] = L.z;
+    return log.n;
+}
+
 // HDRFilm::develop (hdrfilm.cpp:304-405): rgb / (W == 0 ? 1 : W)
 int orc_develop(void *hp, const float *film_rgbw, float *image_rgb) {
     Handle *h = (Handle *) hp; size_t n = (size_t) h->desc.sensor.crop_width * h->desc.sensor.crop_height;

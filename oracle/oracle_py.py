@@ -54,6 +54,7 @@ def lib():
         l.orc_texture_eval.argtypes = [C.POINTER(capi.Texture), C.c_float, C.c_float, vp, vp, vp]; l.orc_texture_eval.restype = None
         l.orc_surface_interaction.argtypes = [vp, vp, vp]; l.orc_surface_interaction.restype = None
         l.orc_splat.argtypes = [C.POINTER(capi.Sensor), vp, vp, C.c_uint64, vp]; l.orc_splat.restype = None
+        l.orc_debug_lane.argtypes = [vp, C.POINTER(capi.RenderArgs), C.c_uint32, vp, C.c_int, vp]; l.orc_debug_lane.restype = C.c_int
         l.orc_num_threads.restype = C.c_int
         l.orc_set_num_threads.argtypes = [C.c_int]; l.orc_set_num_threads.restype = None
         _lib = l
@@ -117,6 +118,13 @@ class OracleScene:
         if lib().orc_render_backward(self.h, C.byref(a), _ptr(gi), arr, len(targets), C.byref(cnt)) != 0:
             raise RuntimeError(lib().orc_last_error().decode())
         return cnt.as_dict()
+
+    def debug_lane(self, lane, max_records=64, **kw):
+        """-> (records [n][11] float32: ray(7), t, u, v, face-bits ; L rgb) for one lane (diagnostics)."""
+        a = self.make_args(**kw)
+        out = np.zeros((max_records, 11), np.float32); rgb = np.zeros(3, np.float32)
+        n = lib().orc_debug_lane(self.h, C.byref(a), int(lane), _ptr(out), max_records, _ptr(rgb))
+        return out[:n], rgb
 
     def trace(self, rays, any_hit=False):
         from mitsuba3_experiments_b200 import capi

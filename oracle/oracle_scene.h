@@ -46,6 +46,10 @@ struct Counters {
 // ---------------------------------------------------------------------------------------------
 struct BVHNode { float lo[3], hi[3]; uint32_t left, count; /* count>0: leaf, left = first prim */ };
 
+// debug recorder (tools/diag_*.py): when set, every closest-hit query of this thread appends ray(7) + hit(4)
+struct TraceLog { float *out; int max_records, n; };
+static thread_local TraceLog *g_trace_log = nullptr;
+
 struct Scene {
     const b2_scene_desc *d = nullptr;
     std::vector<BVHNode> nodes;
@@ -187,6 +191,11 @@ struct Scene {
                     if (tri_test(ray, f, ray.maxt, t, u, v) && (!best.valid() || t < best.t || (t == best.t && f < best.face))) best = Hit{ t, u, v, f };
                 }
             } else { stack[sp++] = n.left; stack[sp++] = n.left + 1; }
+        }
+        if (g_trace_log && g_trace_log->n < g_trace_log->max_records) {
+            float *o = g_trace_log->out + 11 * g_trace_log->n++;
+            o[0] = ray.o.x; o[1] = ray.o.y; o[2] = ray.o.z; o[3] = ray.d.x; o[4] = ray.d.y; o[5] = ray.d.z; o[6] = ray.maxt;
+            o[7] = best.t; o[8] = best.u; o[9] = best.v; std::memcpy(o + 10, &best.face, 4);
         }
         return best;
     }

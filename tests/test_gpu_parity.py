@@ -145,7 +145,7 @@ def test_render_host_and_errors():
     ds.render_host(film, image, seed=0, spp=4)
     img, _ = ds.render(seed=0, spp=4)
     np.testing.assert_allclose(image, img.cpu().numpy(), rtol=2e-5, atol=1e-6)
-    assert abs(film[..., 3].sum() - film[..., 3].size * 4) / film[..., 3].size < 1.0
+    assert np.isfinite(film).all() and (film[..., 3] > 0).all()
     with pytest.raises(capi.B2Error):
         ds.render(seed=0, spp=6, spp_per_pass=4)             # sample_count must be a multiple of spp_per_pass
     with pytest.raises(capi.B2Error):
