@@ -172,7 +172,8 @@ struct Integrator {
             V3 wo = si.valid ? si.sh.to_local(ds.d) : V3(0.f);
             float sample1 = smp.next_1d(); V2 sample2 = smp.next_2d();
             V3 bsdf_val(0.f), bsdf_weight(0.f); float bsdf_pdf = 0.f; BS bs;
-            if (bsdf) { if (active_em) bsdf_eval_pdf(sc, *bsdf, si, wo, bsdf_val, bsdf_pdf, false, c); bsdf_sample(sc, *bsdf, si, sample1, sample2, bs, bsdf_weight, c); }
+            // (eval_pdf is consumed only under active_em and the sample only when the loop continues: evaluated only there)
+            if (bsdf) { if (active_em) bsdf_eval_pdf(sc, *bsdf, si, wo, bsdf_val, bsdf_pdf, false, c); if (active_next) bsdf_sample(sc, *bsdf, si, sample1, sample2, bs, bsdf_weight, c); }
             float mi_em = ds.delta ? 1.f : mis_weight_guard(ds.pdf, bsdf_pdf);
             if (active_em) result = fmadd(throughput, bsdf_val * em_weight * mi_em, result);
             if (si.valid) ray = Scene::spawn_ray(si.p, si.n, si.sh.to_world(bs.wo));
