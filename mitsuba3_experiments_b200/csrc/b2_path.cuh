@@ -1,0 +1,287 @@
+// b2_path.cuh -- per-lane path state and ONE bounce of the three loop formulations (device code shared by the
+// persistent megakernel in render.cu and the wavefront kernels in wavefront.cu).
+//   loops    path.py:194-302 (B2_VARIANT_PATH), path-mis.py:24-155 == integrators/path.cpp:94-327 (B2_VARIANT_PATH_MIS),
+//            ad/integrators/prb.py:63-265 (B2_VARIANT_PRB, primal and adjoint)
+//   driver   SamplingIntegrator::render_sample (src/render/integrator.cpp:419-491)
+//   film     ImageBlock::put (src/render/imageblock.cpp:174-560), rfilters (gaussian.cpp:94-103, tent.cpp:53-55, box.cpp:41-43)
+#pragma once
+#include "b2_render.cuh"
+#include "b2_shade.cuh"
+
+namespace b2 {
+
+// ------------------------------------------------------------------------------------------ filters / film
+B2_DEV float rfilter_eval(const DSensor &s, float x) {
+    if (s.rfilter == B2_RFILTER_GAUSSIAN) return fmaxf(estrin10(sqr(x), s.gaussian_coeff), 0.f);
+    if (s.rfilter == B2_RFILTER_TENT) return fmaxf(0.f, 1.f - fabsf(x * s.inv_radius));
+    return (x >= -.5f && x < .5f) ? 1.f : 0.f;
+}
+
+// Footprint of ImageBlock::put (coalesced variant imageblock.cpp:433-508; box fast path :210-233).
+// Calls f(x, y, weight) with crop-relative pixel coordinates for every in-bounds tap.
+template <class F>
+B2_DEV uint32_t film_taps(const RenderParams &p, f2 pos, F &&f) {
+    const DSensor &s = p.sc.sensor;
+    uint32_t taps = 0;
+    if (s.rfilter == B2_RFILTER_BOX) {
+        const int px = (int) floorf(pos.x) - s.crop_offset_x, py = (int) floorf(pos.y) - s.crop_offset_y;
+        if ((unsigned) px < (unsigned) s.crop_width && (unsigned) py < (unsigned) s.crop_height) { f(px, py, 1.f); taps = 1; }
+        return taps;
+    }
+    const int n = p.filter_n, count = 2 * n + 1;
+    const int pix = (int) floorf(pos.x) - n, piy = (int) floorf(pos.y) - n;
+    const int lx = pix - s.crop_offset_x, ly = piy - s.crop_offset_y;
+    float relx = (float) pix + .5f - pos.x, rely = (float) piy + .5f - pos.y;
+    float wx[5], wy[5];
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+        if (i < count) { wx[i] = rfilter_eval(s, relx); wy[i] = rfilter_eval(s, rely); relx += 1.f; rely += 1.f; }
+        else { wx[i] = 0.f; wy[i] = 0.f; }
+    }
+#pragma unroll
+    for (int ys = 0; ys < 5; ++ys) {
+        if (ys >= count) break;
+        const unsigned y = (unsigned) (ly + ys); if (y >= (unsigned) s.crop_height) continue;
+#pragma unroll
+        for (int xs = 0; xs < 5; ++xs) {
+            if (xs >= count) break;
+            const unsigned x = (unsigned) (lx + xs); if (x >= (unsigned) s.crop_width) continue;
+            taps++; f((int) x, (int) y, wy[ys] * wx[xs]);
+        }
+    }
+    return taps;
+}
+
+// ------------------------------------------------------------------------------------------ sensor
+// PerspectiveCamera::sample_ray_differential (sensors/perspective.cpp:239-280)
+B2_DEV Ray camera_ray(const DSensor &s, f2 position_sample) {
+    const f3 near_p = xf_point_persp(s.sample_to_camera, f3(position_sample.x, position_sample.y, 0.f));
+    const f3 dl = normalize(near_p);
+    Ray r;
+    r.o = f3(s.to_world[3], s.to_world[7], s.to_world[11]);
+    r.d = xf_vector(s.to_world, dl);
+    const float inv_z = rcp(dl.z), near_t = s.near_clip * inv_z, far_t = s.far_clip * inv_z;
+    r.o = r.o + r.d * near_t;
+    r.maxt = far_t - near_t;
+    return r;
+}
+
+B2_DEV float mis_isfinite(float a, float b) {      // path.py:10-18, common.py:1338-1346
+    const float a2 = sqr(a), b2 = sqr(b), w = a2 / (a2 + b2);
+    return finite_(w) ? w : 0.f;
+}
+B2_DEV float mis_guard(float a, float b) {         // path-mis.py:9-15 + isfinite (path.cpp:340-345), see DESIGN.md
+    const float a2 = sqr(a), w = a2 / fma_(b, b, a2);
+    return (a > 0.f && finite_(w)) ? w : 0.f;
+}
+
+// ------------------------------------------------------------------------------------------ per-lane path state
+struct Path {
+    Pcg32 rng;
+    Ray ray;
+    f3 f, L;                 // throughput (f / throughput / beta) and radiance (L / result)
+    float eta;
+    uint32_t depth;
+    f3 prev_p; float prev_pdf;
+    bool prev_delta, first, valid_ray, adjoint;
+    f2 pos;                  // splat position (sample_pos, or the pixel for the box filter: integrator.cpp:490)
+    f3 dL;                   // adjoint radiance (backward mode)
+    uint32_t lane, pass;
+};
+
+template <int V>
+B2_DEV void start_path(const RenderParams &p, Path &s) {
+    const DSensor &sn = p.sc.sensor;
+    // lane -> pixel (integrator.cpp:293-310)
+    uint32_t idx = s.lane;
+    idx = (p.spp_shift != 0xffffffffu) ? (idx >> p.spp_shift) : (idx / p.spp_per_pass);
+    const uint32_t y = idx / (uint32_t) sn.crop_width, x = idx - (uint32_t) sn.crop_width * y;
+    const int px = (int) x + sn.crop_offset_x, py = (int) y + sn.crop_offset_y;
+    const f2 j = s.rng.next_2d();
+    const f2 sample_pos{ (float) px + j.x, (float) py + j.y };
+    const f2 adjusted{ fma_(sample_pos.x, sn.scale_x, sn.offset_x), fma_(sample_pos.y, sn.scale_y, sn.offset_y) };
+    s.ray = camera_ray(sn, adjusted);
+    s.pos = sn.rfilter == B2_RFILTER_BOX ? f2{ (float) px, (float) py } : sample_pos;
+    s.f = f3(1.f); s.L = f3(0.f); s.eta = 1.f;
+    s.depth = (V == B2_VARIANT_PATH) ? 1u : 0u;
+    s.prev_p = f3(0.f); s.prev_pdf = 1.f; s.prev_delta = true; s.first = true;
+    s.valid_ray = p.sc.env_emitter >= 0;
+}
+
+struct GradSink {               // shared-memory accumulators for constant-albedo targets
+    float *s_const;             // [kMaxGradTargets][3]
+};
+
+// One bounce.  Returns true while the path continues.  RNG discipline: every entered loop iteration of the
+// reference consumes exactly 6 draws (2 emitter, 1 + 2 BSDF, 1 roulette), also on its last iteration.
+// Deferred next-event-estimation record of the wavefront formulation: the shadow ray and the two factors of the
+// contribution, L <- fma(a, b, L) once the ray is known to arrive (b = 1 where the reference writes a plain add).
+struct ShadowRec { bool valid, tex; Ray ray; f3 a, b; };   // tex: a texture evaluation is counted iff the ray arrives
+
+// path.py evaluates ray_intersect with `active &= depth < max_depth` (path.py:235): no first intersection at all when
+// max_depth <= 1.
+template <int V>
+B2_DEV bool first_trace_needed(const RenderParams &p, const Path &s) {
+    return !(V == B2_VARIANT_PATH && s.first && !(s.depth < (uint32_t) p.max_depth));
+}
+
+// WF = false: the closest hit and the shadow ray are traced here (megakernel).  WF = true: `pre_hit` holds the closest
+// hit found by the wavefront trace kernel for s.ray, and the shadow ray is recorded in `so` instead of being traced.
+template <int V, bool ADJ, bool COUNT, bool WF = false>
+B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counters<COUNT> &cnt, const Hit *pre_hit = nullptr, ShadowRec *so = nullptr) {
+    static_assert(!(WF && ADJ), "the adjoint replay needs the visibility before the gradient: megakernel only");
+    const DScene &sc = p.sc;
+    const uint32_t max_depth = (uint32_t) p.max_depth;
+    Hit h; h.face = 0xffffffffu; h.t = s.ray.maxt; h.u = h.v = 0.f; h.mesh = 0;
+    if (WF) h = *pre_hit;
+    else if (first_trace_needed<V>(p, s)) { cnt.add(C_CLOSEST); bvh_trace<false>(sc, s.ray.o, s.ray.d, s.ray.maxt, h, cnt); }
+    SI si; make_si(sc, s.ray, h, si, cnt);
+
+    // ---- emission seen by the incoming ray, MIS-weighted against the previous bounce's emitter sampling
+    f3 Le(0.f);
+    bool active_next;
+    if (V == B2_VARIANT_PATH) {
+        if (s.first) {
+            s.L += emitter_eval(sc, si.emitter, si, cnt);                                   // path.py:238-239
+            active_next = s.depth < max_depth;
+            if (active_next && !si.valid) { s.rng.skip(6); return false; }                  // body runs once with a null BSDF
+        } else {
+            DS ds2; direction_sample(si, s.prev_p, ds2);
+            const float em_pdf = pdf_emitter_direction(sc, ds2, !s.prev_delta);
+            const float mis_bsdf = mis_isfinite(s.prev_pdf, em_pdf);
+            const f3 le = s.prev_pdf > 0.f ? emitter_eval(sc, ds2.emitter, si, cnt) : f3(0.f);
+            s.L += s.f * le * mis_bsdf;                                                     // path.py:290-292
+            s.depth += 1;
+            active_next = s.depth < max_depth && si.valid;                                  // path.py:297-300
+        }
+        s.first = false;
+        if (!active_next) return false;
+    } else {
+        DS ds2; direction_sample(si, s.prev_p, ds2);
+        const float em_pdf = pdf_emitter_direction(sc, ds2, !s.prev_delta);
+        if (V == B2_VARIANT_PATH_MIS) {
+            const float mis_bsdf = mis_guard(s.prev_pdf, em_pdf);
+            const f3 le = s.prev_pdf > 0.f ? emitter_eval(sc, ds2.emitter, si, cnt) : f3(0.f);
+            s.L = fmadd(s.f, le * mis_bsdf, s.L);                                           // path-mis.py:75-86
+        } else {
+            const float mis = mis_isfinite(s.prev_pdf, em_pdf);
+            Le = s.f * mis * emitter_eval(sc, ds2.emitter, si, cnt);                        // prb.py:113-134
+        }
+        active_next = (s.depth + 1 < max_depth) && si.valid;
+        if (!active_next) {
+            if (V == B2_VARIANT_PATH_MIS) { if (si.valid) s.valid_ray = true; }
+            else s.L = ADJ ? (s.L - Le) : (s.L + Le);
+            s.rng.skip(6);
+            return false;
+        }
+        if (V == B2_VARIANT_PATH_MIS) s.valid_ray = true;
+    }
+
+    // ---- emitter sampling (NEE) + BSDF sampling.  si is valid from here on.
+    const DBsdf &bsdf = sc.bsdfs[si.bsdf];
+    ReflCache rc;
+    auto refl = [&]() { return reflectance(sc, bsdf, si, rc, cnt); };
+    auto ones = []() { return f3(1.f); };
+    bool active_em = (bsdf_lobes(bsdf) & LOBE_SMOOTH) != 0;
+    DS ds; f3 em_weight;
+    sample_emitter_direction(sc, si, s.rng.next_2d(), active_em, p.env_warp, ds, em_weight, cnt, [&](const Ray &sr) {
+        if (WF) { so->valid = true; so->ray = sr; return false; }
+        Hit hs; cnt.add(C_SHADOW);
+        return bvh_trace<true>(sc, sr.o, sr.d, sr.maxt, hs, cnt);
+    });
+    if (V != B2_VARIANT_PATH_MIS) active_em = active_em && ds.pdf != 0.f;
+    const f3 wo = si.sh.to_local(ds.d);
+    const float s1 = s.rng.next_1d(); const f2 s2 = s.rng.next_2d();
+    f3 bsdf_val(0.f), bsdf_weight(0.f); float bsdf_pdf = 0.f; BS bs;
+    if (WF && V != B2_VARIANT_PATH_MIS) {
+        // path.py / prb.py evaluate the BSDF only for unoccluded emitter samples; the wavefront evaluates it before
+        // the visibility is known, so the texture-evaluation *event* is counted by the trace kernel on arrival
+        Counters<false> quiet; bool tex = false;
+        if (active_em) bsdf_eval_pdf(bsdf, si.wi, wo, [&]() { tex = bsdf.tex >= 0; return reflectance(sc, bsdf, si, rc, quiet); }, bsdf_val, bsdf_pdf);
+        so->tex = tex;
+    } else if (active_em) bsdf_eval_pdf(bsdf, si.wi, wo, refl, bsdf_val, bsdf_pdf);
+    bsdf_sample(bsdf, si.wi, s1, s2, refl, bs, bsdf_weight);
+    const f3 f_before = s.f;
+    float mis_em;
+    if (V == B2_VARIANT_PATH) {
+        mis_em = ds.delta ? 1.f : mis_isfinite(ds.pdf, bsdf_pdf);
+        if (active_em) {                                                                    // path.py:258-259
+            const f3 c = s.f * bsdf_val * em_weight * mis_em;
+            if (WF) { so->a = c; so->b = f3(1.f); } else s.L += c;
+        }
+    } else if (V == B2_VARIANT_PATH_MIS) {
+        mis_em = ds.delta ? 1.f : mis_guard(ds.pdf, bsdf_pdf);
+        if (active_em) {                                                                    // path-mis.py:113-117
+            const f3 c = bsdf_val * em_weight * mis_em;
+            if (WF) { so->a = s.f; so->b = c; } else s.L = fmadd(s.f, c, s.L);
+        }
+    } else {
+        mis_em = ds.delta ? 1.f : mis_isfinite(ds.pdf, bsdf_pdf);
+        const f3 Lr_dir = s.f * mis_em * bsdf_val * em_weight;                              // prb.py:149-162
+        if (WF) { s.L = s.L + Le; so->a = Lr_dir; so->b = f3(1.f); }
+        else s.L = ADJ ? (s.L - Le - Lr_dir) : (s.L + Le + Lr_dir);                         // prb.py:173
+    }
+    s.ray = spawn_ray(si.p, si.n, si.sh.to_world(bs.wo));
+    s.f *= bsdf_weight; s.eta *= bs.eta;
+    s.prev_p = si.p; s.prev_pdf = bs.pdf; s.prev_delta = (bs.type & LOBE_DELTA) != 0;
+
+    // ---- Russian roulette
+    bool active;
+    if (V == B2_VARIANT_PATH) {
+        const float fmax = hmax(s.f), rr_prob = fminf(fmax * sqr(s.eta), 0.95f);
+        const bool rr_active = s.depth >= (uint32_t) p.rr_depth, rr_continue = s.rng.next_1d() < rr_prob;
+        if (rr_active) s.f *= rcp(rr_prob);
+        active = fmax != 0.f && (!rr_active || rr_continue);                                // path.py:268-277
+    } else if (V == B2_VARIANT_PATH_MIS) {
+        s.depth += 1;
+        const float tmax = hmax(s.f), rr_prob = fminf(tmax * sqr(s.eta), 0.95f);
+        const bool rr_active = s.depth >= (uint32_t) p.rr_depth, rr_continue = s.rng.next_1d() < rr_prob;
+        if (rr_active) s.f *= rcp(rr_prob);
+        active = (!rr_active || rr_continue) && tmax != 0.f;                                // path-mis.py:143-153
+    } else {
+        const float beta_max = hmax(s.f), rr_prob = fminf(beta_max * sqr(s.eta), 0.95f);
+        const bool rr_active = s.depth >= (uint32_t) p.rr_depth;
+        if (rr_active) s.f *= rcp(rr_prob);
+        const bool rr_continue = s.rng.next_1d() < rr_prob;
+        active = beta_max != 0.f && (!rr_active || rr_continue);                            // prb.py:188-200
+        if (ADJ) {
+            // d/d(reflectance) of [ Lr_dir + L * bsdf_val / detach(bsdf_weight * pdf) ] (prb.py:202-250); every
+            // supported BSDF is linear in its reflectance, so the derivative is the value with reflectance := 1.
+            f3 g(0.f);
+            if (active_em) {
+                f3 unit; float dummy; bsdf_eval_pdf(bsdf, si.wi, wo, ones, unit, dummy);
+                g += s.dL * (f_before * mis_em * unit * em_weight);
+            }
+            if (active) {
+                const f3 wo2 = si.sh.to_local(s.ray.d);
+                f3 unit; float dummy; bsdf_eval_pdf(bsdf, si.wi, wo2, ones, unit, dummy);
+                const f3 det = bsdf_weight * bs.pdf;
+                const f3 inv(det.x != 0.f ? rcp(det.x) : 0.f, det.y != 0.f ? rcp(det.y) : 0.f, det.z != 0.f ? rcp(det.z) : 0.f);
+                g += s.dL * (s.L * (inv * unit));
+            }
+            if (!is_zero(g)) {
+                for (int t = 0; t < p.n_targets; ++t) {
+                    if (p.targets[t].bsdf != si.bsdf) continue;
+                    if (p.targets[t].kind == 0) {
+                        atomicAdd(gs.s_const + 3 * t, g.x); atomicAdd(gs.s_const + 3 * t + 1, g.y); atomicAdd(gs.s_const + 3 * t + 2, g.z);
+                        cnt.add(C_GRAD, 3);
+                    } else {
+                        uint32_t idx[4]; float w[4]; Counters<false> none;
+                        tex_eval(sc, bsdf.tex, si.uv, idx, w, none);
+                        float *gp = p.targets[t].grad;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            atomicAdd(gp + 3 * (size_t) idx[q], g.x * w[q]); atomicAdd(gp + 3 * (size_t) idx[q] + 1, g.y * w[q]);
+                            atomicAdd(gp + 3 * (size_t) idx[q] + 2, g.z * w[q]);
+                        }
+                        cnt.add(C_GRAD, 12);
+                    }
+                }
+            }
+        }
+        s.depth += 1;
+    }
+    return active;
+}
+
+}  // namespace b2

@@ -509,8 +509,11 @@ B2_DEV float pdf_emitter_direction(const DScene &sc, const DS &ds, bool active) 
 }
 
 // Scene::sample_emitter_direction (scene.cpp:319-369): emitter choice (:252-275), sample, shadow ray
-template <bool COUNT>
-B2_DEV void sample_emitter_direction(const DScene &sc, const SI &ref, f2 sample, bool active, int env_warp, DS &ds, f3 &spec, Counters<COUNT> &cnt) {
+// `occluded(ray)` answers the visibility query: the megakernel traces the shadow ray on the spot, the wavefront shade
+// kernel records it for the next trace launch and answers "visible" (the contribution is then added by the trace
+// kernel only if the ray arrives; an occluded sample contributes exactly zero in either formulation).
+template <bool COUNT, class OCC>
+B2_DEV void sample_emitter_direction(const DScene &sc, const SI &ref, f2 sample, bool active, int env_warp, DS &ds, f3 &spec, Counters<COUNT> &cnt, OCC &&occluded) {
     ds.p = f3(); ds.n = f3(); ds.d = f3(); ds.pdf = 0.f; ds.dist = 0.f; ds.delta = false; ds.emitter = -1; spec = f3(0.f);
     const uint32_t n = sc.n_emitters;
     if (!active || n == 0) return;
@@ -525,8 +528,7 @@ B2_DEV void sample_emitter_direction(const DScene &sc, const SI &ref, f2 sample,
     spec *= weight;
     if (ds.pdf != 0.f) {
         const Ray sr = spawn_ray_to(ref.p, ref.n, ds.p);
-        Hit h; cnt.add(C_SHADOW);
-        if (bvh_trace<true>(sc, sr.o, sr.d, sr.maxt, h, cnt)) { spec = f3(0.f); ds.pdf = 0.f; }
+        if (occluded(sr)) { spec = f3(0.f); ds.pdf = 0.f; }
     }
 }
 

@@ -2,6 +2,7 @@
 // No CPU fallback exists: every entry point either runs the CUDA path or fails with an error string.
 #include "b2_build.h"
 #include "b2_render.cuh"
+#include "b2_wavefront.cuh"
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -31,6 +32,7 @@ struct b2_scene {
     uint32_t *unit_counter = nullptr;
     unsigned long long *counters_dev = nullptr;
     float *wfilm = nullptr;                     // weight film of the PRB sample set
+    void *wf_mem = nullptr; uint32_t wf_capacity = 0; WfState wf{};   // wavefront lane state (grown on demand)
     uint64_t launches = 0;
 
     template <typename T> cudaError_t upload(const T *host, size_t n, T *&dev) {
@@ -39,7 +41,7 @@ struct b2_scene {
         if (n && host) e = cudaMemcpy(q, host, n * sizeof(T), cudaMemcpyHostToDevice);
         return e;
     }
-    ~b2_scene() { for (void *q : allocs) cudaFree(q); bvh_free(bvh); }
+    ~b2_scene() { for (void *q : allocs) cudaFree(q); if (wf_mem) cudaFree(wf_mem); bvh_free(bvh); }
 };
 
 extern "C" {
@@ -248,7 +250,8 @@ static int setup_params(b2_scene *s, const b2_render_args *a, int mode, bool cou
     const int variant = mode == MODE_RENDER ? a->variant : B2_VARIANT_PRB;
     if (variant < 0 || variant > B2_VARIANT_PRB) return fail(-2, "render: unknown variant");
     uint64_t shard_lanes = p.lane_end - p.lane_begin;
-    uint64_t target = a->chunk_lanes ? a->chunk_lanes : std::min<uint64_t>(8192, std::max<uint64_t>(1024, shard_lanes / ((uint64_t) s->ctx->sm_count * 2 * 8 + 1)));
+    const bool mega = a->kernel == B2_KERNEL_MEGAKERNEL || mode != MODE_RENDER;
+    uint64_t target = (mega && a->chunk_lanes) ? a->chunk_lanes : std::min<uint64_t>(8192, std::max<uint64_t>(1024, shard_lanes / ((uint64_t) s->ctx->sm_count * 2 * 8 + 1)));
     uint32_t P = (uint32_t) std::min<uint64_t>(W, std::max<uint64_t>(1, (target + spp_per_pass - 1) / spp_per_pass));
     p.unit_pixels = P; p.units_per_row = (W + P - 1) / P;
     p.tile_cols = P + 2 * p.filter_n + 1; p.tile_rows = 2 * p.filter_n + 2;
@@ -284,7 +287,23 @@ int b2_render(b2_scene *s, const b2_render_args *a, float *film, uintptr_t strea
     uint64_t launches = 0;
     CUDA_OK(cudaMemsetAsync(s->unit_counter, 0, 16, st));
     if (count) CUDA_OK(cudaMemsetAsync(s->counters_dev, 0, sizeof(unsigned long long) * C_N, st));
-    if (p.unit_end > p.unit_begin) { launch_render(a->variant, MODE_RENDER, count, p, blocks, smem, st); launches++; }
+    if (a->kernel != B2_KERNEL_WAVEFRONT && a->kernel != B2_KERNEL_MEGAKERNEL) return fail(-2, "render: unknown kernel");
+    if (p.lane_end > p.lane_begin && a->kernel == B2_KERNEL_WAVEFRONT) {
+        // wavefront: lane state of one chunk lives in HBM (188 B per lane); default chunk = 8 Mi lanes (1.6 GB)
+        const uint64_t shard = p.lane_end - p.lane_begin;
+        const uint32_t want = (uint32_t) std::min<uint64_t>(shard, a->chunk_lanes ? std::max<uint32_t>(a->chunk_lanes, 256u) : (8u << 20));
+        if (want > s->wf_capacity) {
+            CUDA_OK(cudaStreamSynchronize(st));
+            if (s->wf_mem) { cudaFree(s->wf_mem); s->wf_mem = nullptr; s->wf_capacity = 0; }
+            CUDA_OK(cudaMalloc(&s->wf_mem, wf_state_bytes(want)));
+            s->wf_capacity = want;
+        }
+        wf_bind(s->wf, s->wf_mem, want);
+        const char *err = nullptr;
+        const long n = wf_render(a->variant, count, p, s->wf, s->ctx->sm_count, st, &err);
+        if (n < 0) return fail(-11, err ? err : "wavefront render failed");
+        launches += (uint64_t) n;
+    } else if (p.unit_end > p.unit_begin) { launch_render(a->variant, MODE_RENDER, count, p, blocks, smem, st); launches++; }
     CUDA_OK(cudaGetLastError());
     if (count) {
         unsigned long long h[C_N];

@@ -1,0 +1,438 @@
+// wavefront.cu -- wavefront kernels of the render loop (default product path for b2_render).
+//
+//   k_wf_generate   lane -> pixel, sampler seeding, sensor ray            integrator.cpp:293-310,419-436, sampler.cpp:129-148,
+//                                                                          perspective.cpp:239-280
+//   k_wf_trace      Scene::ray_intersect_preliminary + Scene::ray_test    scene.cpp:191-235 (Embree/OptiX in the reference)
+//   k_wf_shade<V>   one bounce of path.py / path-mis.py / prb.py          b2_path.cuh (path_step<WF>)
+//   k_wf_splat      ImageBlock::put                                        imageblock.cpp:174-560
+//
+// Trace kernel: persistent warps pull batches of rays from a device-side counter into a warp-private pool; a lane whose
+// ray terminates is refilled at the next slice boundary instead of idling until the slowest ray of its warp is done
+// (the idle lanes of the v1 megakernel were 77 % of all issue slots, profiles/r01_v1_*).  Closest-hit and any-hit rays
+// share the launch; the first entries of the traversal stack live in shared memory ([depth][thread], conflict free),
+// deeper ones in local memory.  Node = five 128-bit loads, triangle = three.
+#include "b2_path.cuh"
+#include "b2_wavefront.cuh"
+
+namespace b2 {
+
+constexpr int kTraceThreads = 256;
+constexpr int kSmemStack = 8;          // stack entries per thread held in shared memory
+constexpr int kLocalStack = 40;        // overflow entries in local memory
+constexpr int kFetchBatch = 96;        // rays a warp takes from the global counter at a time
+#ifndef B2_TRACE_SLICE
+#define B2_TRACE_SLICE 8               // traversal steps between two refill points
+#endif
+
+// ------------------------------------------------------------------------------------------ state <-> registers
+B2_DEV void wf_store_path(const WfState &st, uint32_t slot, const Path &s, bool with_ray) {
+    st.rng[slot] = make_uint4((uint32_t) s.rng.state, (uint32_t) (s.rng.state >> 32), (uint32_t) s.rng.inc, (uint32_t) (s.rng.inc >> 32));
+    uint32_t bits = (s.depth & WF_DEPTH_MASK) | (s.prev_delta ? WF_FLAG_PREV_DELTA : 0u) | (s.first ? WF_FLAG_FIRST : 0u) | (s.valid_ray ? WF_FLAG_VALID_RAY : 0u);
+    st.rad[slot] = make_float4(s.L.x, s.L.y, s.L.z, __uint_as_float(bits));
+    if (with_ray) {
+        st.ray_o[slot] = make_float4(s.ray.o.x, s.ray.o.y, s.ray.o.z, s.ray.maxt);
+        st.ray_d[slot] = make_float4(s.ray.d.x, s.ray.d.y, s.ray.d.z, s.eta);
+        st.thr[slot] = make_float4(s.f.x, s.f.y, s.f.z, s.prev_pdf);
+        st.prev[slot] = make_float4(s.prev_p.x, s.prev_p.y, s.prev_p.z, 0.f);
+    }
+}
+B2_DEV void wf_load_path(const WfState &st, uint32_t slot, Path &s) {
+    const uint4 r = st.rng[slot];
+    s.rng.state = (uint64_t) r.x | ((uint64_t) r.y << 32); s.rng.inc = (uint64_t) r.z | ((uint64_t) r.w << 32);
+    const float4 o = st.ray_o[slot], d = st.ray_d[slot], t = st.thr[slot], l = st.rad[slot], pv = st.prev[slot];
+    s.ray.o = f3(o.x, o.y, o.z); s.ray.maxt = o.w; s.ray.d = f3(d.x, d.y, d.z); s.eta = d.w;
+    s.f = f3(t.x, t.y, t.z); s.prev_pdf = t.w; s.L = f3(l.x, l.y, l.z);
+    const uint32_t bits = __float_as_uint(l.w);
+    s.depth = bits & WF_DEPTH_MASK; s.prev_delta = (bits & WF_FLAG_PREV_DELTA) != 0; s.first = (bits & WF_FLAG_FIRST) != 0;
+    s.valid_ray = (bits & WF_FLAG_VALID_RAY) != 0;
+    s.prev_p = f3(pv.x, pv.y, pv.z);
+    s.adjoint = false; s.dL = f3(0.f); s.pass = 0; s.lane = 0; s.pos = f2{ 0.f, 0.f };
+}
+
+template <bool COUNT>
+B2_DEV void wf_flush_counters(const Counters<COUNT> &cnt, unsigned long long *out) {
+    if constexpr (COUNT) {
+        if (out) {
+#pragma unroll 1
+            for (int k = 0; k < C_N; ++k) {
+                unsigned long long v = cnt.v[k];
+                for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if ((threadIdx.x & 31) == 0 && v) atomicAdd(out + k, v);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ generate
+template <int V>
+__global__ void __launch_bounds__(256) k_wf_generate(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
+    const WfState &st = w.st;
+    if (blockIdx.x == 0 && threadIdx.x < 4) {       // nothing else is in flight: reset the queue bookkeeping
+        const uint32_t k = threadIdx.x;
+        st.ctl->n_closest[k] = (k == (w.it & 3u)) ? w.n : 0u; st.ctl->n_shadow[k] = 0u; st.ctl->fetch[k] = 0u;
+    }
+    uint32_t *q = st.q[w.it & 1u];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < w.n; i += gridDim.x * blockDim.x) {
+        Path s;
+        s.lane = (uint32_t) (w.chunk_begin + i); s.pass = w.pass; s.adjoint = false; s.dL = f3(0.f);
+        if (w.pass == 0) s.rng.seed_lane(p.seed, s.lane);
+        else { const uint4 r = st.rng[i]; s.rng.state = (uint64_t) r.x | ((uint64_t) r.y << 32); s.rng.inc = (uint64_t) r.z | ((uint64_t) r.w << 32); }
+        start_path<V>(p, s);
+        wf_store_path(st, i, s, true);
+        st.pos[i] = make_float2(s.pos.x, s.pos.y);
+        st.hit[i] = make_float4(s.ray.maxt, 0.f, 0.f, __uint_as_float(0xffffffffu));     // a miss, unless trace(it) overwrites it
+        st.hit_mesh[i] = 0u;
+        q[i] = i;
+    }
+}
+
+// ------------------------------------------------------------------------------------------ trace
+struct TraceRay {
+    f3 o, d; float idx, idy, idz, maxt;
+    uint32_t octinv, slot; bool any, tex;
+    float t, u, v; uint32_t face, mesh; bool found;
+    uint2 ng, tg; int sp;
+};
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kTraceThreads, 3) k_wf_trace(const __grid_constant__ DScene sc, const __grid_constant__ WfLaunch w, unsigned long long *counters) {
+    __shared__ uint2 s_stack[kSmemStack][kTraceThreads];
+    const WfState &st = w.st;
+    const uint32_t slot_c = w.it & 3u, slot_s = (w.it + 3u) & 3u;
+    const uint32_t nc = st.ctl->n_closest[slot_c], ns = st.ctl->n_shadow[slot_s], total = nc + ns;
+    const uint32_t *qc = st.q[w.it & 1u], *qs = st.q_shadow[0];
+    uint32_t *fetch = &st.ctl->fetch[slot_c];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    Counters<COUNT> cnt;
+    uint2 l_stack[kLocalStack];
+
+    uint32_t pool_next = 0, pool_end = 0;           // warp-uniform
+    bool exhausted = total == 0;
+    bool have = false;
+    TraceRay r;
+    r.sp = 0; r.any = false; r.tex = false; r.found = false; r.slot = 0; r.ng = make_uint2(0u, 0u); r.tg = make_uint2(0u, 0u);
+
+    for (;;) {
+        // ---- refill idle lanes (warp converged here)
+        const uint32_t need = __ballot_sync(0xffffffffu, !have);
+        if (need && !exhausted) {
+            const uint32_t k = __popc(need), rank = __popc(need & lt_mask);
+            uint32_t my = 0xffffffffu;
+            const uint32_t avail = pool_end - pool_next;
+            if (avail >= k) { if (!have) my = pool_next + rank; pool_next += k; }
+            else {
+                if (!have && rank < avail) my = pool_next + rank;
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(fetch, (uint32_t) kFetchBatch);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                const uint32_t nb = base < total ? min((uint32_t) kFetchBatch, total - base) : 0u;
+                const uint32_t r2 = rank - avail;
+                if (!have && rank >= avail && r2 < nb) my = base + r2;
+                pool_next = base + min(k - avail, nb); pool_end = base + nb;
+                if (nb == 0u) exhausted = true;
+            }
+            if (my != 0xffffffffu) {
+                r.any = my >= nc;
+                r.slot = r.any ? qs[my - nc] : qc[my];
+                const float4 o = r.any ? st.sh_o[r.slot] : st.ray_o[r.slot], d = r.any ? st.sh_d[r.slot] : st.ray_d[r.slot];
+                r.o = f3(o.x, o.y, o.z); r.d = f3(d.x, d.y, d.z); r.maxt = o.w; r.tex = r.any && d.w != 0.f;
+                const float tiny = 1e-30f;
+                r.idx = 1.f / (fabsf(r.d.x) > tiny ? r.d.x : copysignf(tiny, r.d.x));
+                r.idy = 1.f / (fabsf(r.d.y) > tiny ? r.d.y : copysignf(tiny, r.d.y));
+                r.idz = 1.f / (fabsf(r.d.z) > tiny ? r.d.z : copysignf(tiny, r.d.z));
+                r.octinv = (r.d.x >= 0.f ? 1u : 0u) | (r.d.y >= 0.f ? 2u : 0u) | (r.d.z >= 0.f ? 4u : 0u);
+                r.t = r.maxt; r.u = 0.f; r.v = 0.f; r.face = 0xffffffffu; r.mesh = 0u; r.found = false;
+                r.ng = sc.n_nodes ? make_uint2(0u, (1u << (24 + r.octinv)) | 1u) : make_uint2(0u, 0u);
+                r.tg = make_uint2(0u, 0u); r.sp = 0;
+                cnt.add(r.any ? C_SHADOW : C_CLOSEST);
+                have = true;
+            }
+        }
+        if (!__any_sync(0xffffffffu, have)) break;
+        if (!have) continue;
+
+        // ---- traverse for up to B2_TRACE_SLICE steps (same node / triangle arithmetic as bvh_trace, b2_bvh.cuh)
+        bool done = false;
+#pragma unroll 1
+        for (int step = 0; step < B2_TRACE_SLICE && !done; ++step) {
+            if (r.ng.y & 0xff000000u) {
+                const int bit = 31 - __clz(r.ng.y);
+                r.ng.y &= ~(1u << bit);
+                if (r.ng.y & 0xff000000u) {
+                    if (r.sp < kSmemStack) s_stack[r.sp][tid] = r.ng;
+                    else if (r.sp < kSmemStack + kLocalStack) l_stack[r.sp - kSmemStack] = r.ng;
+                    if (r.sp < kSmemStack + kLocalStack) r.sp++;
+                }
+                const uint32_t cslot = (uint32_t) (bit - 24) ^ r.octinv;
+                const uint32_t rel = __popc(r.ng.y & 0xffu & ~(0xffffffffu << cslot));
+                const uint4 *np = sc.nodes + (size_t) (r.ng.x + rel) * 5;
+                const uint4 w0 = __ldg(np), w1 = __ldg(np + 1), w2 = __ldg(np + 2), w3 = __ldg(np + 3), w4 = __ldg(np + 4);
+                cnt.add(C_NODES);
+                const float sx = __uint_as_float((w0.w & 0xffu) << 23), sy = __uint_as_float(((w0.w >> 8) & 0xffu) << 23),
+                            sz = __uint_as_float(((w0.w >> 16) & 0xffu) << 23);
+                const uint32_t imask = w0.w >> 24;
+                const float ax = sx * r.idx, ay = sy * r.idy, az = sz * r.idz;
+                const float bx = (__uint_as_float(w0.x) - r.o.x) * r.idx, by = (__uint_as_float(w0.y) - r.o.y) * r.idy,
+                            bz = (__uint_as_float(w0.z) - r.o.z) * r.idz;
+                uint32_t nhits = 0, thits = 0;
+#pragma unroll
+                for (int s = 0; s < 8; ++s) {
+                    const uint32_t meta = byte_of(w1.z, w1.w, s);
+                    if (meta == 0) continue;
+                    const float lx = (float) byte_of(w2.x, w2.y, s), ly = (float) byte_of(w2.z, w2.w, s), lz = (float) byte_of(w3.x, w3.y, s);
+                    const float hx = (float) byte_of(w3.z, w3.w, s), hy = (float) byte_of(w4.x, w4.y, s), hz = (float) byte_of(w4.z, w4.w, s);
+                    const float t0x = __fmaf_rn(r.octinv & 1u ? lx : hx, ax, bx), t1x = __fmaf_rn(r.octinv & 1u ? hx : lx, ax, bx);
+                    const float t0y = __fmaf_rn(r.octinv & 2u ? ly : hy, ay, by), t1y = __fmaf_rn(r.octinv & 2u ? hy : ly, ay, by);
+                    const float t0z = __fmaf_rn(r.octinv & 4u ? lz : hz, az, bz), t1z = __fmaf_rn(r.octinv & 4u ? hz : lz, az, bz);
+                    const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
+                    const float tf = fminf(fminf(t1x, t1y), t1z) * 1.0000005f;
+                    if (tn <= fminf(tf, r.t)) {
+                        if ((imask >> s) & 1u) nhits |= 1u << (24 + ((uint32_t) s ^ r.octinv));
+                        else thits |= (meta >> 5) << (meta & 31u);
+                    }
+                }
+                r.ng = make_uint2(w1.x, nhits | imask);
+                r.tg = make_uint2(w1.y, thits);
+            } else {
+                r.tg = r.ng; r.ng = make_uint2(0u, 0u);
+            }
+
+            while (r.tg.y) {
+                const int i = __ffs(r.tg.y) - 1;
+                r.tg.y &= r.tg.y - 1;
+                const float4 *tp = sc.tris + (size_t) (r.tg.x + i) * 3;
+                const float4 r0 = __ldg(tp), r1 = __ldg(tp + 1), r2 = __ldg(tp + 2);
+                cnt.add(C_TRIS);
+                // Mesh::moeller_trumbore (mesh.h:469-492)
+                const f3 e1(r1.x, r1.y, r1.z), e2(r2.x, r2.y, r2.z);
+                const f3 pvec = cross(r.d, e2);
+                const float inv_det = rcp(dot(e1, pvec));
+                const f3 tvec = r.o - f3(r0.x, r0.y, r0.z);
+                const float u = dot(tvec, pvec) * inv_det;
+                bool ok = u >= 0.f && u <= 1.f;
+                const f3 qvec = cross(tvec, e1);
+                const float v = dot(r.d, qvec) * inv_det;
+                ok = ok && v >= 0.f && u + v <= 1.f;
+                const float t = dot(e2, qvec) * inv_det;
+                ok = ok && t >= 0.f && t <= r.maxt;
+                if (ok) {
+                    const uint32_t face = __float_as_uint(r0.w);
+                    if (r.any) { r.found = true; r.tg.y = 0u; r.ng.y = 0u; r.sp = 0; break; }
+                    if (!r.found || t < r.t || (t == r.t && face < r.face)) {
+                        r.found = true; r.t = t; r.u = u; r.v = v; r.face = face; r.mesh = __float_as_uint(r1.w);
+                    }
+                }
+            }
+
+            if ((r.ng.y & 0xff000000u) == 0u) {
+                if (r.sp == 0) done = true;
+                else { --r.sp; r.ng = r.sp < kSmemStack ? s_stack[r.sp][tid] : l_stack[r.sp - kSmemStack]; }
+            }
+        }
+
+        if (done) {
+            if (r.any) {
+                if (!r.found) {         // the emitter sample arrives: L <- fma(a, b, L)
+                    if (r.tex) cnt.add(C_TEX);
+                    const float4 a = st.sh_a[r.slot], b = st.sh_b[r.slot]; float4 L = st.rad[r.slot];
+                    L.x = fma_(a.x, b.x, L.x); L.y = fma_(a.y, b.y, L.y); L.z = fma_(a.z, b.z, L.z);
+                    st.rad[r.slot] = L;
+                }
+            } else {
+                st.hit[r.slot] = make_float4(r.t, r.u, r.v, __uint_as_float(r.face));
+                st.hit_mesh[r.slot] = r.mesh;
+            }
+            have = false;
+        }
+    }
+    wf_flush_counters(cnt, counters);
+}
+
+// ------------------------------------------------------------------------------------------ shade
+template <int V, bool COUNT>
+__global__ void __launch_bounds__(256) k_wf_shade(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
+    __shared__ uint32_t s_cnt[2][8], s_base[2];
+    const WfState &st = w.st;
+    const uint32_t it = w.it, n = st.ctl->n_closest[it & 3u];
+    const uint32_t *qin = st.q[it & 1u]; uint32_t *qout = st.q[(it + 1u) & 1u], *qsh = st.q_shadow[0];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    Counters<COUNT> cnt; GradSink gs{ nullptr };
+    if (blockIdx.x == 0 && tid == 0) { const uint32_t z = (it + 2u) & 3u; st.ctl->n_closest[z] = 0u; st.ctl->n_shadow[z] = 0u; st.ctl->fetch[z] = 0u; }
+
+    for (uint32_t base = blockIdx.x * 256u; base < n; base += gridDim.x * 256u) {
+        const uint32_t i = base + tid;
+        bool alive = false, shadow = false; uint32_t slot = 0;
+        if (i < n) {
+            slot = qin[i];
+            Path s; wf_load_path(st, slot, s);
+            const float4 hh = st.hit[slot];
+            Hit h; h.t = hh.x; h.u = hh.y; h.v = hh.z; h.face = __float_as_uint(hh.w); h.mesh = st.hit_mesh[slot];
+            ShadowRec so; so.valid = false; so.tex = false; so.a = f3(0.f); so.b = f3(0.f);
+            alive = path_step<V, false, COUNT, true>(p, s, gs, cnt, &h, &so);
+            wf_store_path(st, slot, s, alive);
+            shadow = so.valid;
+            if (shadow) {
+                st.sh_o[slot] = make_float4(so.ray.o.x, so.ray.o.y, so.ray.o.z, so.ray.maxt);
+                st.sh_d[slot] = make_float4(so.ray.d.x, so.ray.d.y, so.ray.d.z, so.tex ? 1.f : 0.f);
+                st.sh_a[slot] = make_float4(so.a.x, so.a.y, so.a.z, 0.f);
+                st.sh_b[slot] = make_float4(so.b.x, so.b.y, so.b.z, 0.f);
+            }
+        }
+        // ---- compaction: warp ballot -> per-warp counts -> one atomic per block and queue
+        const uint32_t ma = __ballot_sync(0xffffffffu, alive), ms = __ballot_sync(0xffffffffu, shadow);
+        if (lane == 0) { s_cnt[0][warp] = __popc(ma); s_cnt[1][warp] = __popc(ms); }
+        __syncthreads();
+        if (tid < 2) {
+            uint32_t tot = 0;
+            for (int k = 0; k < 8; ++k) { const uint32_t c = s_cnt[tid][k]; s_cnt[tid][k] = tot; tot += c; }
+            s_base[tid] = tot ? atomicAdd(tid == 0 ? &st.ctl->n_closest[(it + 1u) & 3u] : &st.ctl->n_shadow[it & 3u], tot) : 0u;
+        }
+        __syncthreads();
+        const uint32_t lt = (1u << lane) - 1u;
+        if (alive) qout[s_base[0] + s_cnt[0][warp] + __popc(ma & lt)] = slot;
+        if (shadow) qsh[s_base[1] + s_cnt[1][warp] + __popc(ms & lt)] = slot;
+        __syncthreads();
+    }
+    wf_flush_counters(cnt, p.counters);
+}
+
+// ------------------------------------------------------------------------------------------ splat
+// Units (a run of pixels of one image row x all of its samples) are pulled from a global counter; the samples of a
+// unit are splatted into a shared-memory RGBW tile which is flushed with one 128-bit reduction per touched pixel.
+template <int V, bool COUNT, bool WEIGHTS_ONLY>
+__global__ void __launch_bounds__(256) k_wf_splat(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
+    extern __shared__ float4 s_tile[];
+    __shared__ uint32_t s_unit;
+    const DSensor &sn = p.sc.sensor; const WfState &st = w.st;
+    const int tid = threadIdx.x;
+    const uint32_t tile_cells = p.tile_rows * p.tile_cols;
+    const uint64_t c_lo = w.chunk_begin, c_hi = w.chunk_begin + w.n;
+    Counters<COUNT> cnt;
+    for (;;) {
+        if (tid == 0) s_unit = p.unit_begin + atomicAdd(p.unit_counter, 1u);
+        __syncthreads();
+        const uint32_t unit = s_unit;
+        if (unit >= p.unit_end) break;
+        const uint32_t row = unit / p.units_per_row, ux = unit - row * p.units_per_row;
+        const uint32_t x0 = ux * p.unit_pixels, x1 = min(x0 + p.unit_pixels, (uint32_t) sn.crop_width);
+        uint64_t lane_lo = ((uint64_t) row * sn.crop_width + x0) * p.spp_per_pass, lane_hi = ((uint64_t) row * sn.crop_width + x1) * p.spp_per_pass;
+        lane_lo = max(lane_lo, c_lo); lane_hi = min(lane_hi, c_hi);
+        const uint32_t n_lanes = lane_hi > lane_lo ? (uint32_t) (lane_hi - lane_lo) : 0u;
+        const int tx0 = (int) x0 - p.filter_n, ty0 = (int) row - p.filter_n;
+        for (uint32_t i = tid; i < tile_cells; i += 256) s_tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        __syncthreads();
+        for (uint32_t i = tid; i < n_lanes; i += 256) {
+            const uint32_t slot = (uint32_t) (lane_lo + i - c_lo);
+            const float2 ps = st.pos[slot];
+            f3 L(0.f);
+            if (!WEIGHTS_ONLY) {
+                const float4 l = st.rad[slot]; L = f3(l.x, l.y, l.z);
+                if (V == B2_VARIANT_PATH_MIS && !(__float_as_uint(l.w) & WF_FLAG_VALID_RAY)) L = f3(0.f);
+            }
+            const uint32_t taps = film_taps(p, f2{ ps.x, ps.y }, [&](int x, int y, float wgt) {
+                const int cx = x - tx0, cy = y - ty0;
+                float *c = ((unsigned) cx < p.tile_cols && (unsigned) cy < p.tile_rows) ? (float *) (s_tile + cy * p.tile_cols + cx)
+                                                                                        : p.film + 4 * ((size_t) y * sn.crop_width + x);
+                atomicAdd(c, L.x * wgt); atomicAdd(c + 1, L.y * wgt); atomicAdd(c + 2, L.z * wgt); atomicAdd(c + 3, 1.f * wgt);
+            });
+            cnt.add(C_TAPS, taps); cnt.add(C_SAMPLES);
+        }
+        __syncthreads();
+        for (uint32_t i = tid; i < tile_cells; i += 256) {
+            const float4 v = s_tile[i];
+            if (v.x == 0.f && v.y == 0.f && v.z == 0.f && v.w == 0.f) continue;
+            const int cy = i / p.tile_cols, cx = i - cy * p.tile_cols, x = tx0 + cx, y = ty0 + cy;
+            if ((unsigned) x < (unsigned) sn.crop_width && (unsigned) y < (unsigned) sn.crop_height)
+                atomicAdd((float4 *) (p.film + 4 * ((size_t) y * sn.crop_width + x)), v);
+        }
+        __syncthreads();
+    }
+    wf_flush_counters(cnt, p.counters);
+}
+
+// ------------------------------------------------------------------------------------------ host driver
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+size_t wf_state_bytes(uint32_t cap) {
+    const size_t c = cap;
+    return align_up(c * 16, 256) * 11 + align_up(c * 8, 256) + align_up(c * 4, 256) * 4 + 256;
+}
+
+void wf_bind(WfState &st, void *base, uint32_t cap) {
+    char *q = (char *) base; const size_t c = cap;
+    auto take = [&](size_t bytes) { void *r = q; q += align_up(bytes, 256); return r; };
+    st.ctl = (WfCtl *) take(256);
+    st.rng = (uint4 *) take(c * 16); st.ray_o = (float4 *) take(c * 16); st.ray_d = (float4 *) take(c * 16); st.thr = (float4 *) take(c * 16);
+    st.rad = (float4 *) take(c * 16); st.prev = (float4 *) take(c * 16); st.hit = (float4 *) take(c * 16);
+    st.sh_o = (float4 *) take(c * 16); st.sh_d = (float4 *) take(c * 16); st.sh_a = (float4 *) take(c * 16); st.sh_b = (float4 *) take(c * 16);
+    st.pos = (float2 *) take(c * 8);
+    st.hit_mesh = (uint32_t *) take(c * 4); st.q[0] = (uint32_t *) take(c * 4); st.q[1] = (uint32_t *) take(c * 4); st.q_shadow[0] = (uint32_t *) take(c * 4);
+    st.q_shadow[1] = st.q_shadow[0];
+    st.capacity = cap;
+}
+
+template <int V, bool COUNT>
+static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {
+    long launches = 0;
+    const DSensor &sn = p.sc.sensor;
+    const uint32_t W = (uint32_t) sn.crop_width, P = p.unit_pixels;
+    int occ_trace = 0, occ_shade = 0, occ_splat = 0;
+    const size_t smem_splat = sizeof(float4) * (size_t) p.tile_cols * p.tile_rows;
+    cudaFuncSetAttribute(k_wf_splat<V, COUNT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem_splat);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_trace, k_wf_trace<COUNT>, kTraceThreads, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<V, COUNT>, 256, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_splat, k_wf_splat<V, COUNT, false>, 256, smem_splat);
+    if (occ_trace <= 0 || occ_shade <= 0 || occ_splat <= 0) { *err = "wavefront: a kernel cannot be resident (occupancy 0)"; return -1; }
+    const uint64_t lane_lo = p.lane_begin, lane_hi = p.lane_end;
+    const bool skip_first_trace = V == B2_VARIANT_PATH && p.max_depth <= 1;
+    const bool bounded = p.max_depth <= 64;
+    const uint32_t n_iter = bounded ? (uint32_t) std::max(p.max_depth, 1) : 0u;
+    uint32_t it = 0;
+    for (uint64_t c0 = lane_lo; c0 < lane_hi; c0 += st.capacity) {
+        const uint32_t n = (uint32_t) std::min<uint64_t>(st.capacity, lane_hi - c0);
+        WfLaunch w; w.st = st; w.chunk_begin = c0; w.n = n;
+        const int g_gen = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) sm_count * 8);
+        const int g_trace = occ_trace * sm_count, g_shade = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_shade * sm_count);
+        for (uint32_t pass = 0; pass < p.n_passes; ++pass) {
+            w.pass = pass; w.it = it;
+            k_wf_generate<V><<<g_gen, 256, 0, stream>>>(p, w); launches++;
+            for (uint32_t k = 0;; ++k) {
+                if (bounded && k >= n_iter) break;
+                w.it = it;
+                if (!(k == 0 && skip_first_trace)) { k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); launches++; }
+                k_wf_shade<V, COUNT><<<g_shade, 256, 0, stream>>>(p, w); launches++;
+                ++it;
+                if (!bounded && (k & 3u) == 3u) {       // unbounded depth: Russian roulette ends the paths; poll the live count
+                    uint32_t live = 0;
+                    if (cudaMemcpyAsync(&live, &st.ctl->n_closest[it & 3u], 4, cudaMemcpyDeviceToHost, stream) != cudaSuccess ||
+                        cudaStreamSynchronize(stream) != cudaSuccess) { *err = "wavefront: polling the live-lane count failed"; return -1; }
+                    if (live == 0) break;
+                }
+            }
+            w.it = it;                                  // shadow rays of the last bounce
+            k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); launches++;
+            ++it;
+            // splat this chunk: units covering its pixels
+            RenderParams ps = p;
+            const uint64_t pix0 = c0 / p.spp_per_pass, pix1 = (c0 + n - 1) / p.spp_per_pass;
+            ps.unit_begin = (uint32_t) ((pix0 / W) * p.units_per_row + (pix0 % W) / P);
+            ps.unit_end = (uint32_t) ((pix1 / W) * p.units_per_row + (pix1 % W) / P) + 1;
+            cudaMemsetAsync(p.unit_counter, 0, 4, stream);
+            const int g_splat = (int) std::min<uint32_t>(ps.unit_end - ps.unit_begin, (uint32_t) (occ_splat * sm_count));
+            k_wf_splat<V, COUNT, false><<<g_splat, 256, smem_splat, stream>>>(ps, w); launches++;
+        }
+    }
+    if (cudaGetLastError() != cudaSuccess) { *err = "wavefront: kernel launch failed"; return -1; }
+    return launches;
+}
+
+long wf_render(int variant, bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {
+    switch (variant) {
+        case B2_VARIANT_PATH: return count ? wf_render_t<B2_VARIANT_PATH, true>(p, st, sm_count, stream, err) : wf_render_t<B2_VARIANT_PATH, false>(p, st, sm_count, stream, err);
+        case B2_VARIANT_PATH_MIS: return count ? wf_render_t<B2_VARIANT_PATH_MIS, true>(p, st, sm_count, stream, err) : wf_render_t<B2_VARIANT_PATH_MIS, false>(p, st, sm_count, stream, err);
+        default: return count ? wf_render_t<B2_VARIANT_PRB, true>(p, st, sm_count, stream, err) : wf_render_t<B2_VARIANT_PRB, false>(p, st, sm_count, stream, err);
+    }
+}
+
+}  // namespace b2

@@ -77,48 +77,75 @@ def test_bvh_stats_and_edge_cases():
     assert (c["prim"][c["prim"] != 0xffffffff] == 0).all()
 
 
+KERNELS = [pytest.param(0, id="wavefront"), pytest.param(1, id="megakernel")]
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
 @pytest.mark.parametrize("variant,max_depth,rr_depth", [(0, 8, 4), (1, 8, 2), (2, 6, 5), (0, 1, 4), (1, 1, 2), (0, 2, 1)])
-def test_cornell_render_parity(variant, max_depth, rr_depth):
+def test_cornell_render_parity(variant, max_depth, rr_depth, kernel):
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
     ds = DeviceScene(cornell_box(96, 96, spp=16)); orc = OracleScene(ds.desc)
     kw = dict(seed=0, spp=16, max_depth=max_depth, rr_depth=rr_depth, variant=variant)
-    img, cnt = ds.render(counters=True, **kw)
+    img, cnt = ds.render(counters=True, kernel=kernel, **kw)
     ref, rc = orc.render(**kw)
     check_image(img.cpu().numpy(), ref, 0.999, 1e-4)
     for k in ("samples", "closest_rays", "shadow_rays", "vertices", "nee_area", "splat_taps"):
         assert abs(cnt[k] - rc[k]) <= 1e-3 * max(rc[k], 1), (k, cnt[k], rc[k])
-    assert cnt["samples"] == 96 * 96 * 16 and cnt["launches"] == 1
+    assert cnt["samples"] == 96 * 96 * 16 and (cnt["launches"] == 1 if kernel == 1 else cnt["launches"] >= 3)
 
 
+@pytest.mark.parametrize("kernel", KERNELS)
 @pytest.mark.parametrize("variant", [0, 1, 2])
 @pytest.mark.parametrize("filt,envmap", [("gaussian", True), ("tent", False), ("box", True)])
-def test_materials_render_parity(variant, filt, envmap):
+def test_materials_render_parity(variant, filt, envmap, kernel):
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
     ds = DeviceScene(materials_scene(64, 48, 16, envmap=envmap, filter_type=filt)); orc = OracleScene(ds.desc)
     kw = dict(seed=3, spp=16, max_depth=7, rr_depth=3, variant=variant)
-    img, cnt = ds.render(counters=True, **kw)
+    img, cnt = ds.render(counters=True, kernel=kernel, **kw)
     ref, rc = orc.render(**kw)
     check_image(img.cpu().numpy(), ref, 0.99, 2e-3)
     for k in ("closest_rays", "shadow_rays", "vertices", "tex_evals", "nee_area", "nee_env", "env_escapes", "splat_taps"):
         assert abs(cnt[k] - rc[k]) <= 2e-3 * max(rc[k], 1) + 2, (k, cnt[k], rc[k])
 
 
-def test_triangle_soup_render_parity():
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_triangle_soup_render_parity(kernel):
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
     ds = DeviceScene(triangles_scene(20000, 64, 48, 8)); orc = OracleScene(ds.desc)
     kw = dict(seed=1, spp=8, max_depth=6, rr_depth=3, variant=1)
-    img, _ = ds.render(**kw)
+    img, _ = ds.render(kernel=kernel, **kw)
     ref, _ = orc.render(**kw)
     check_image(img.cpu().numpy(), ref, 0.99, 2e-3)
 
 
-def test_film_edge_cases_crop_multipass_shards():
+@pytest.mark.parametrize("variant", [0, 1, 2])
+def test_wavefront_equals_megakernel(variant):
+    """Both kernel organisations run the same per-lane arithmetic: images agree up to the film's fp32 summation order,
+    event counters agree exactly."""
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    ds = DeviceScene(materials_scene(64, 48, 16, envmap=True, filter_type="gaussian"))
+    kw = dict(seed=9, spp=16, max_depth=6, rr_depth=2, variant=variant)
+    a, ca = ds.render(counters=True, kernel=0, **kw)
+    b, cb = ds.render(counters=True, kernel=1, **kw)
+    np.testing.assert_allclose(a.cpu().numpy(), b.cpu().numpy(), rtol=2e-5, atol=1e-6)
+    for k in ca:
+        if k != "launches":
+            assert ca[k] == cb[k], (k, ca[k], cb[k])
+    # unbounded depth (max_depth = -1 -> 1 << 20): the wavefront polls the live-lane count instead of a fixed trip count
+    c, _ = ds.render(kernel=0, **dict(kw, max_depth=1 << 20))
+    d, _ = ds.render(kernel=1, **dict(kw, max_depth=1 << 20))
+    np.testing.assert_allclose(c.cpu().numpy(), d.cpu().numpy(), rtol=2e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_film_edge_cases_crop_multipass_shards(kernel):
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
     d = cornell_box(80, 60, spp=12)           # non power-of-two spp -> division path of integrator.cpp:293-300
     d["sensor"]["film"].update(crop_offset_x=17, crop_offset_y=9, crop_width=41, crop_height=23)
     ds = DeviceScene(d); orc = OracleScene(ds.desc)
     kw = dict(seed=5, spp=12, max_depth=5, rr_depth=2, variant=0)
     ref, _ = orc.render(**kw)
+    kw["kernel"] = kernel
     img, _ = ds.render(**kw)
     check_image(img.cpu().numpy(), ref, 0.999, 1e-4)
     # multi-pass: 3 passes x 4 spp continue each lane's stream (integrator.cpp:319-328)
