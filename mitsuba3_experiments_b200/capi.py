@@ -114,7 +114,7 @@ EXPORTS = ["b2_init", "b2_shutdown", "b2_scene_create", "b2_scene_destroy", "b2_
            "b2_render_host", "b2_last_error", "b2_abi_version"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libb2path.so")
+LIB_PATH = os.environ.get("B2PATH_LIB") or os.path.join(_HERE, "csrc", "libb2path.so")   # B2PATH_LIB: tuning builds only
 _lib = None
 
 

@@ -42,6 +42,7 @@ struct WfLaunch {
     uint32_t n;                      // lanes in this chunk
     uint32_t it;                     // global iteration counter (slot = it & 3)
     uint32_t pass;                   // > 0: continue each lane's PCG32 stream (integrator.cpp:319-328)
+    uint32_t slice;                  // trace: traversal steps between two refill points
 };
 
 // host entry points (wavefront.cu)

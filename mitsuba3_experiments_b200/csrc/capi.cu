@@ -289,9 +289,9 @@ int b2_render(b2_scene *s, const b2_render_args *a, float *film, uintptr_t strea
     if (count) CUDA_OK(cudaMemsetAsync(s->counters_dev, 0, sizeof(unsigned long long) * C_N, st));
     if (a->kernel != B2_KERNEL_WAVEFRONT && a->kernel != B2_KERNEL_MEGAKERNEL) return fail(-2, "render: unknown kernel");
     if (p.lane_end > p.lane_begin && a->kernel == B2_KERNEL_WAVEFRONT) {
-        // wavefront: lane state of one chunk lives in HBM (188 B per lane); default chunk = 8 Mi lanes (1.6 GB)
+        // wavefront: lane state of one chunk lives in HBM (188 B per lane); default chunk = 16 Mi lanes (3.2 GB)
         const uint64_t shard = p.lane_end - p.lane_begin;
-        const uint32_t want = (uint32_t) std::min<uint64_t>(shard, a->chunk_lanes ? std::max<uint32_t>(a->chunk_lanes, 256u) : (8u << 20));
+        const uint32_t want = (uint32_t) std::min<uint64_t>(shard, a->chunk_lanes ? std::max<uint32_t>(a->chunk_lanes, 256u) : (16u << 20));
         if (want > s->wf_capacity) {
             CUDA_OK(cudaStreamSynchronize(st));
             if (s->wf_mem) { cudaFree(s->wf_mem); s->wf_mem = nullptr; s->wf_capacity = 0; }

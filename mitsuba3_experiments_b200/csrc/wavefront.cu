@@ -13,6 +13,8 @@
 // deeper ones in local memory.  Node = five 128-bit loads, triangle = three.
 #include "b2_path.cuh"
 #include "b2_wavefront.cuh"
+#include <algorithm>
+#include <cstdlib>
 
 namespace b2 {
 
@@ -20,8 +22,14 @@ constexpr int kTraceThreads = 256;
 constexpr int kSmemStack = 8;          // stack entries per thread held in shared memory
 constexpr int kLocalStack = 40;        // overflow entries in local memory
 constexpr int kFetchBatch = 96;        // rays a warp takes from the global counter at a time
+#ifndef B2_TRACE_MINBLOCKS
+#define B2_TRACE_MINBLOCKS 4
+#endif
+#ifndef B2_SHADE_MINBLOCKS
+#define B2_SHADE_MINBLOCKS 3
+#endif
 #ifndef B2_TRACE_SLICE
-#define B2_TRACE_SLICE 8               // traversal steps between two refill points
+#define B2_TRACE_SLICE 4               // traversal steps between two refill points
 #endif
 
 // ------------------------------------------------------------------------------------------ state <-> registers
@@ -95,7 +103,7 @@ struct TraceRay {
 };
 
 template <bool COUNT>
-__global__ void __launch_bounds__(kTraceThreads, 3) k_wf_trace(const __grid_constant__ DScene sc, const __grid_constant__ WfLaunch w, unsigned long long *counters) {
+__global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(const __grid_constant__ DScene sc, const __grid_constant__ WfLaunch w, unsigned long long *counters) {
     __shared__ uint2 s_stack[kSmemStack][kTraceThreads];
     const WfState &st = w.st;
     const uint32_t slot_c = w.it & 3u, slot_s = (w.it + 3u) & 3u;
@@ -155,7 +163,7 @@ __global__ void __launch_bounds__(kTraceThreads, 3) k_wf_trace(const __grid_cons
         // ---- traverse for up to B2_TRACE_SLICE steps (same node / triangle arithmetic as bvh_trace, b2_bvh.cuh)
         bool done = false;
 #pragma unroll 1
-        for (int step = 0; step < B2_TRACE_SLICE && !done; ++step) {
+        for (uint32_t step = 0; step < w.slice && !done; ++step) {
             if (r.ng.y & 0xff000000u) {
                 const int bit = 31 - __clz(r.ng.y);
                 r.ng.y &= ~(1u << bit);
@@ -251,7 +259,7 @@ __global__ void __launch_bounds__(kTraceThreads, 3) k_wf_trace(const __grid_cons
 
 // ------------------------------------------------------------------------------------------ shade
 template <int V, bool COUNT>
-__global__ void __launch_bounds__(256) k_wf_shade(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
+__global__ void __launch_bounds__(256, B2_SHADE_MINBLOCKS) k_wf_shade(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
     __shared__ uint32_t s_cnt[2][8], s_base[2];
     const WfState &st = w.st;
     const uint32_t it = w.it, n = st.ctl->n_closest[it & 3u];
@@ -387,13 +395,15 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
     const uint64_t lane_lo = p.lane_begin, lane_hi = p.lane_end;
     const bool skip_first_trace = V == B2_VARIANT_PATH && p.max_depth <= 1;
     const bool bounded = p.max_depth <= 64;
+    static const uint32_t tune_slice = getenv("B2_TRACE_SLICE") ? (uint32_t) std::max(1, atoi(getenv("B2_TRACE_SLICE"))) : (uint32_t) B2_TRACE_SLICE;
+    static const int tune_trace_blocks = getenv("B2_TRACE_BLOCKS") ? atoi(getenv("B2_TRACE_BLOCKS")) : 0;
     const uint32_t n_iter = bounded ? (uint32_t) std::max(p.max_depth, 1) : 0u;
     uint32_t it = 0;
     for (uint64_t c0 = lane_lo; c0 < lane_hi; c0 += st.capacity) {
         const uint32_t n = (uint32_t) std::min<uint64_t>(st.capacity, lane_hi - c0);
-        WfLaunch w; w.st = st; w.chunk_begin = c0; w.n = n;
+        WfLaunch w; w.st = st; w.chunk_begin = c0; w.n = n; w.slice = tune_slice;
         const int g_gen = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) sm_count * 8);
-        const int g_trace = occ_trace * sm_count, g_shade = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_shade * sm_count);
+        const int g_trace = (tune_trace_blocks > 0 ? std::min(tune_trace_blocks, occ_trace) : occ_trace) * sm_count, g_shade = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_shade * sm_count);
         for (uint32_t pass = 0; pass < p.n_passes; ++pass) {
             w.pass = pass; w.it = it;
             k_wf_generate<V><<<g_gen, 256, 0, stream>>>(p, w); launches++;
