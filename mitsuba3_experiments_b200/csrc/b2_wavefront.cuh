@@ -42,7 +42,8 @@ struct WfLaunch {
     uint32_t n;                      // lanes in this chunk
     uint32_t it;                     // global iteration counter (slot = it & 3)
     uint32_t pass;                   // > 0: continue each lane's PCG32 stream (integrator.cpp:319-328)
-    uint32_t slice;                  // trace: traversal steps between two refill points
+    uint32_t slice;                  // trace: traversal micro-steps between two refill points
+    uint32_t tri_thresh;             // trace: lanes with pending leaf triangles that trigger a triangle step
 };
 
 // host entry points (wavefront.cu)

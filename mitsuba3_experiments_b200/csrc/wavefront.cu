@@ -21,6 +21,7 @@ namespace b2 {
 constexpr int kTraceThreads = 256;
 constexpr int kSmemStack = 8;          // stack entries per thread held in shared memory
 constexpr int kLocalStack = 40;        // overflow entries in local memory
+constexpr int kTriQueue = 4;           // parked leaf-triangle groups per thread (shared memory)
 constexpr int kFetchBatch = 96;        // rays a warp takes from the global counter at a time
 #ifndef B2_TRACE_MINBLOCKS
 #define B2_TRACE_MINBLOCKS 4
@@ -29,7 +30,7 @@ constexpr int kFetchBatch = 96;        // rays a warp takes from the global coun
 #define B2_SHADE_MINBLOCKS 3
 #endif
 #ifndef B2_TRACE_SLICE
-#define B2_TRACE_SLICE 4               // traversal steps between two refill points
+#define B2_TRACE_SLICE 5               // traversal steps between two refill points
 #endif
 
 // ------------------------------------------------------------------------------------------ state <-> registers
@@ -99,12 +100,13 @@ struct TraceRay {
     f3 o, d; float idx, idy, idz, maxt;
     uint32_t octinv, slot; bool any, tex;
     float t, u, v; uint32_t face, mesh; bool found;
-    uint2 ng, tg; int sp;
+    uint2 ng, tg; int sp, nq;
 };
 
 template <bool COUNT>
 __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(const __grid_constant__ DScene sc, const __grid_constant__ WfLaunch w, unsigned long long *counters) {
     __shared__ uint2 s_stack[kSmemStack][kTraceThreads];
+    __shared__ uint2 s_pend[kTriQueue][kTraceThreads];
     const WfState &st = w.st;
     const uint32_t slot_c = w.it & 3u, slot_s = (w.it + 3u) & 3u;
     const uint32_t nc = st.ctl->n_closest[slot_c], ns = st.ctl->n_shadow[slot_s], total = nc + ns;
@@ -119,7 +121,7 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
     bool exhausted = total == 0;
     bool have = false;
     TraceRay r;
-    r.sp = 0; r.any = false; r.tex = false; r.found = false; r.slot = 0; r.ng = make_uint2(0u, 0u); r.tg = make_uint2(0u, 0u);
+    r.sp = 0; r.nq = 0; r.any = false; r.tex = false; r.found = false; r.slot = 0; r.ng = make_uint2(0u, 0u); r.tg = make_uint2(0u, 0u);
 
     for (;;) {
         // ---- refill idle lanes (warp converged here)
@@ -152,19 +154,57 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
                 r.octinv = (r.d.x >= 0.f ? 1u : 0u) | (r.d.y >= 0.f ? 2u : 0u) | (r.d.z >= 0.f ? 4u : 0u);
                 r.t = r.maxt; r.u = 0.f; r.v = 0.f; r.face = 0xffffffffu; r.mesh = 0u; r.found = false;
                 r.ng = sc.n_nodes ? make_uint2(0u, (1u << (24 + r.octinv)) | 1u) : make_uint2(0u, 0u);
-                r.tg = make_uint2(0u, 0u); r.sp = 0;
+                r.tg = make_uint2(0u, 0u); r.sp = 0; r.nq = 0;
                 cnt.add(r.any ? C_SHADOW : C_CLOSEST);
                 have = true;
             }
         }
-        if (!__any_sync(0xffffffffu, have)) break;
+        const uint32_t smask = __ballot_sync(0xffffffffu, have);
+        if (smask == 0u) break;
         if (!have) continue;
 
-        // ---- traverse for up to B2_TRACE_SLICE steps (same node / triangle arithmetic as bvh_trace, b2_bvh.cuh)
+        // ---- traverse for up to `slice` micro-steps.  Every micro-step the lanes of this slice vote: a NODE step (pop a
+        // child, five 128-bit loads, eight branch-free slab tests) for the lanes that have node work, or a TRIANGLE step
+        // (one Moeller-Trumbore test per lane) once enough lanes hold pending leaf triangles.  Leaf hits found by a node
+        // step are parked in a per-lane queue (shared memory) instead of being tested on the spot, where only ~4 of
+        // 32 lanes had one (profiles/r01_v2_trace_*): the arithmetic per ray is that of bvh_trace (b2_bvh.cuh).
         bool done = false;
 #pragma unroll 1
-        for (uint32_t step = 0; step < w.slice && !done; ++step) {
-            if (r.ng.y & 0xff000000u) {
+        for (uint32_t step = 0; step < w.slice; ++step) {
+            const bool node_work = (r.ng.y & 0xff000000u) != 0u || r.sp > 0;
+            const bool can_node = node_work && (r.tg.y == 0u || r.nq < kTriQueue);
+            const uint32_t P = __ballot_sync(smask, r.tg.y != 0u), N = __ballot_sync(smask, can_node);
+            if ((P | N) == 0u) break;
+            if (N == 0u || (uint32_t) __popc(P) >= w.tri_thresh) {
+                if (r.tg.y) {
+                    const int i = __ffs(r.tg.y) - 1;
+                    r.tg.y &= r.tg.y - 1;
+                    const float4 *tp = sc.tris + (size_t) (r.tg.x + i) * 3;
+                    const float4 r0 = __ldg(tp), r1 = __ldg(tp + 1), r2 = __ldg(tp + 2);
+                    cnt.add(C_TRIS);
+                    // Mesh::moeller_trumbore (mesh.h:469-492)
+                    const f3 e1(r1.x, r1.y, r1.z), e2(r2.x, r2.y, r2.z);
+                    const f3 pvec = cross(r.d, e2);
+                    const float inv_det = rcp(dot(e1, pvec));
+                    const f3 tvec = r.o - f3(r0.x, r0.y, r0.z);
+                    const float u = dot(tvec, pvec) * inv_det;
+                    bool ok = u >= 0.f && u <= 1.f;
+                    const f3 qvec = cross(tvec, e1);
+                    const float v = dot(r.d, qvec) * inv_det;
+                    ok = ok && v >= 0.f && u + v <= 1.f;
+                    const float t = dot(e2, qvec) * inv_det;
+                    ok = ok && t >= 0.f && t <= r.maxt;
+                    if (ok) {
+                        const uint32_t face = __float_as_uint(r0.w);
+                        if (r.any) { r.found = true; r.tg.y = 0u; r.ng.y = 0u; r.sp = 0; r.nq = 0; }
+                        else if (!r.found || t < r.t || (t == r.t && face < r.face)) {
+                            r.found = true; r.t = t; r.u = u; r.v = v; r.face = face; r.mesh = __float_as_uint(r1.w);
+                        }
+                    }
+                    if (r.tg.y == 0u && r.nq > 0) r.tg = s_pend[--r.nq][tid];
+                }
+            } else if (can_node) {
+                if ((r.ng.y & 0xff000000u) == 0u) { --r.sp; r.ng = r.sp < kSmemStack ? s_stack[r.sp][tid] : l_stack[r.sp - kSmemStack]; }
                 const int bit = 31 - __clz(r.ng.y);
                 r.ng.y &= ~(1u << bit);
                 if (r.ng.y & 0xff000000u) {
@@ -183,61 +223,37 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
                 const float ax = sx * r.idx, ay = sy * r.idy, az = sz * r.idz;
                 const float bx = (__uint_as_float(w0.x) - r.o.x) * r.idx, by = (__uint_as_float(w0.y) - r.o.y) * r.idy,
                             bz = (__uint_as_float(w0.z) - r.o.z) * r.idz;
-                uint32_t nhits = 0, thits = 0;
+                // entry / exit plane bytes of the eight children, chosen once per node by the ray octant
+                const bool px = (r.octinv & 1u) != 0u, py = (r.octinv & 2u) != 0u, pz = (r.octinv & 4u) != 0u;
+                const uint32_t nx0 = px ? w2.x : w3.z, nx1 = px ? w2.y : w3.w, fx0 = px ? w3.z : w2.x, fx1 = px ? w3.w : w2.y;
+                const uint32_t ny0 = py ? w2.z : w4.x, ny1 = py ? w2.w : w4.y, fy0 = py ? w4.x : w2.z, fy1 = py ? w4.y : w2.w;
+                const uint32_t nz0 = pz ? w3.x : w4.z, nz1 = pz ? w3.y : w4.w, fz0 = pz ? w4.z : w3.x, fz1 = pz ? w4.w : w3.y;
+                uint32_t hitmask = 0;
 #pragma unroll
                 for (int s = 0; s < 8; ++s) {
                     const uint32_t meta = byte_of(w1.z, w1.w, s);
-                    if (meta == 0) continue;
-                    const float lx = (float) byte_of(w2.x, w2.y, s), ly = (float) byte_of(w2.z, w2.w, s), lz = (float) byte_of(w3.x, w3.y, s);
-                    const float hx = (float) byte_of(w3.z, w3.w, s), hy = (float) byte_of(w4.x, w4.y, s), hz = (float) byte_of(w4.z, w4.w, s);
-                    const float t0x = __fmaf_rn(r.octinv & 1u ? lx : hx, ax, bx), t1x = __fmaf_rn(r.octinv & 1u ? hx : lx, ax, bx);
-                    const float t0y = __fmaf_rn(r.octinv & 2u ? ly : hy, ay, by), t1y = __fmaf_rn(r.octinv & 2u ? hy : ly, ay, by);
-                    const float t0z = __fmaf_rn(r.octinv & 4u ? lz : hz, az, bz), t1z = __fmaf_rn(r.octinv & 4u ? hz : lz, az, bz);
+                    const float t0x = __fmaf_rn((float) byte_of(nx0, nx1, s), ax, bx), t1x = __fmaf_rn((float) byte_of(fx0, fx1, s), ax, bx);
+                    const float t0y = __fmaf_rn((float) byte_of(ny0, ny1, s), ay, by), t1y = __fmaf_rn((float) byte_of(fy0, fy1, s), ay, by);
+                    const float t0z = __fmaf_rn((float) byte_of(nz0, nz1, s), az, bz), t1z = __fmaf_rn((float) byte_of(fz0, fz1, s), az, bz);
                     const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
                     const float tf = fminf(fminf(t1x, t1y), t1z) * 1.0000005f;
-                    if (tn <= fminf(tf, r.t)) {
-                        if ((imask >> s) & 1u) nhits |= 1u << (24 + ((uint32_t) s ^ r.octinv));
-                        else thits |= (meta >> 5) << (meta & 31u);
-                    }
+                    // internal child: meta = 0x20 | (24 + s) -> bit 24 + s; leaf: unary count << offset; empty: 0
+                    hitmask |= (tn <= fminf(tf, r.t)) ? ((meta >> 5) << (meta & 31u)) : 0u;
                 }
-                r.ng = make_uint2(w1.x, nhits | imask);
-                r.tg = make_uint2(w1.y, thits);
-            } else {
-                r.tg = r.ng; r.ng = make_uint2(0u, 0u);
-            }
-
-            while (r.tg.y) {
-                const int i = __ffs(r.tg.y) - 1;
-                r.tg.y &= r.tg.y - 1;
-                const float4 *tp = sc.tris + (size_t) (r.tg.x + i) * 3;
-                const float4 r0 = __ldg(tp), r1 = __ldg(tp + 1), r2 = __ldg(tp + 2);
-                cnt.add(C_TRIS);
-                // Mesh::moeller_trumbore (mesh.h:469-492)
-                const f3 e1(r1.x, r1.y, r1.z), e2(r2.x, r2.y, r2.z);
-                const f3 pvec = cross(r.d, e2);
-                const float inv_det = rcp(dot(e1, pvec));
-                const f3 tvec = r.o - f3(r0.x, r0.y, r0.z);
-                const float u = dot(tvec, pvec) * inv_det;
-                bool ok = u >= 0.f && u <= 1.f;
-                const f3 qvec = cross(tvec, e1);
-                const float v = dot(r.d, qvec) * inv_det;
-                ok = ok && v >= 0.f && u + v <= 1.f;
-                const float t = dot(e2, qvec) * inv_det;
-                ok = ok && t >= 0.f && t <= r.maxt;
-                if (ok) {
-                    const uint32_t face = __float_as_uint(r0.w);
-                    if (r.any) { r.found = true; r.tg.y = 0u; r.ng.y = 0u; r.sp = 0; break; }
-                    if (!r.found || t < r.t || (t == r.t && face < r.face)) {
-                        r.found = true; r.t = t; r.u = u; r.v = v; r.face = face; r.mesh = __float_as_uint(r1.w);
-                    }
+                // child-slot bits (24 + s) -> traversal-order bits (24 + (s ^ octinv))
+                uint32_t nh = hitmask >> 24;
+                if (px) nh = ((nh & 0x55u) << 1) | ((nh & 0xaau) >> 1);
+                if (py) nh = ((nh & 0x33u) << 2) | ((nh & 0xccu) >> 2);
+                if (pz) nh = ((nh & 0x0fu) << 4) | ((nh & 0xf0u) >> 4);
+                r.ng = make_uint2(w1.x, (nh << 24) | imask);
+                const uint32_t thits = hitmask & 0x00ffffffu;
+                if (thits) {
+                    if (r.tg.y == 0u) r.tg = make_uint2(w1.y, thits);
+                    else s_pend[r.nq++][tid] = make_uint2(w1.y, thits);
                 }
-            }
-
-            if ((r.ng.y & 0xff000000u) == 0u) {
-                if (r.sp == 0) done = true;
-                else { --r.sp; r.ng = r.sp < kSmemStack ? s_stack[r.sp][tid] : l_stack[r.sp - kSmemStack]; }
             }
         }
+        done = (r.ng.y & 0xff000000u) == 0u && r.sp == 0 && r.tg.y == 0u && r.nq == 0;
 
         if (done) {
             if (r.any) {
@@ -396,12 +412,13 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
     const bool skip_first_trace = V == B2_VARIANT_PATH && p.max_depth <= 1;
     const bool bounded = p.max_depth <= 64;
     static const uint32_t tune_slice = getenv("B2_TRACE_SLICE") ? (uint32_t) std::max(1, atoi(getenv("B2_TRACE_SLICE"))) : (uint32_t) B2_TRACE_SLICE;
+    static const uint32_t tune_tri = getenv("B2_TRI_THRESH") ? (uint32_t) std::max(1, atoi(getenv("B2_TRI_THRESH"))) : 8u;
     static const int tune_trace_blocks = getenv("B2_TRACE_BLOCKS") ? atoi(getenv("B2_TRACE_BLOCKS")) : 0;
     const uint32_t n_iter = bounded ? (uint32_t) std::max(p.max_depth, 1) : 0u;
     uint32_t it = 0;
     for (uint64_t c0 = lane_lo; c0 < lane_hi; c0 += st.capacity) {
         const uint32_t n = (uint32_t) std::min<uint64_t>(st.capacity, lane_hi - c0);
-        WfLaunch w; w.st = st; w.chunk_begin = c0; w.n = n; w.slice = tune_slice;
+        WfLaunch w; w.st = st; w.chunk_begin = c0; w.n = n; w.slice = tune_slice; w.tri_thresh = tune_tri;
         const int g_gen = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) sm_count * 8);
         const int g_trace = (tune_trace_blocks > 0 ? std::min(tune_trace_blocks, occ_trace) : occ_trace) * sm_count, g_shade = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_shade * sm_count);
         for (uint32_t pass = 0; pass < p.n_passes; ++pass) {

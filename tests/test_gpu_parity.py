@@ -129,7 +129,9 @@ def test_wavefront_equals_megakernel(variant):
     b, cb = ds.render(counters=True, kernel=1, **kw)
     np.testing.assert_allclose(a.cpu().numpy(), b.cpu().numpy(), rtol=2e-5, atol=1e-6)
     for k in ca:
-        if k != "launches":
+        if k in ("node_fetches", "tri_fetches"):      # traversal work: the wavefront parks leaf triangles, so the
+            assert abs(ca[k] - cb[k]) <= 0.15 * cb[k], (k, ca[k], cb[k])   # closest-hit bound shrinks a little later
+        elif k != "launches":
             assert ca[k] == cb[k], (k, ca[k], cb[k])
     # unbounded depth (max_depth = -1 -> 1 << 20): the wavefront polls the live-lane count instead of a fixed trip count
     c, _ = ds.render(kernel=0, **dict(kw, max_depth=1 << 20))
