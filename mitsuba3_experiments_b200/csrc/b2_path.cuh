@@ -116,7 +116,8 @@ struct GradSink {               // shared-memory accumulators for constant-albed
 // reference consumes exactly 6 draws (2 emitter, 1 + 2 BSDF, 1 roulette), also on its last iteration.
 // Deferred next-event-estimation record of the wavefront formulation: the shadow ray and the two factors of the
 // contribution, L <- fma(a, b, L) once the ray is known to arrive (b = 1 where the reference writes a plain add).
-struct ShadowRec { bool valid, tex; Ray ray; f3 a, b; };   // tex: a texture evaluation is counted iff the ray arrives
+struct ShadowRec { bool valid, tex, vis; Ray ray; f3 a, b; };   // tex: a texture evaluation is counted iff the ray arrives
+                                                                // vis (adjoint replay, input): visibility found by the primal pass
 
 // path.py evaluates ray_intersect with `active &= depth < max_depth` (path.py:235): no first intersection at all when
 // max_depth <= 1.
@@ -129,7 +130,8 @@ B2_DEV bool first_trace_needed(const RenderParams &p, const Path &s) {
 // hit found by the wavefront trace kernel for s.ray, and the shadow ray is recorded in `so` instead of being traced.
 template <int V, bool ADJ, bool COUNT, bool WF = false>
 B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counters<COUNT> &cnt, const Hit *pre_hit = nullptr, ShadowRec *so = nullptr) {
-    static_assert(!(WF && ADJ), "the adjoint replay needs the visibility before the gradient: megakernel only");
+    // WF && ADJ: the adjoint pass replays the lane's sample stream; the visibility of each emitter sample was recorded
+    // by the primal pass of the same render_backward call (identical rays), so no shadow ray is traced again.
     const DScene &sc = p.sc;
     const uint32_t max_depth = (uint32_t) p.max_depth;
     Hit h; h.face = 0xffffffffu; h.t = s.ray.maxt; h.u = h.v = 0.f; h.mesh = 0;
@@ -185,6 +187,7 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
     bool active_em = (bsdf_lobes(bsdf) & LOBE_SMOOTH) != 0;
     DS ds; f3 em_weight;
     sample_emitter_direction(sc, si, s.rng.next_2d(), active_em, p.env_warp, ds, em_weight, cnt, [&](const Ray &sr) {
+        if (WF && ADJ) return !so->vis;
         if (WF) { so->valid = true; so->ray = sr; return false; }
         Hit hs; cnt.add(C_SHADOW);
         return bvh_trace<true>(sc, sr.o, sr.d, sr.maxt, hs, cnt);
@@ -193,7 +196,7 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
     const f3 wo = si.sh.to_local(ds.d);
     const float s1 = s.rng.next_1d(); const f2 s2 = s.rng.next_2d();
     f3 bsdf_val(0.f), bsdf_weight(0.f); float bsdf_pdf = 0.f; BS bs;
-    if (WF && V != B2_VARIANT_PATH_MIS) {
+    if (WF && !ADJ && V != B2_VARIANT_PATH_MIS) {
         // path.py / prb.py evaluate the BSDF only for unoccluded emitter samples; the wavefront evaluates it before
         // the visibility is known, so the texture-evaluation *event* is counted by the trace kernel on arrival
         Counters<false> quiet; bool tex = false;
@@ -218,7 +221,7 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
     } else {
         mis_em = ds.delta ? 1.f : mis_isfinite(ds.pdf, bsdf_pdf);
         const f3 Lr_dir = s.f * mis_em * bsdf_val * em_weight;                              // prb.py:149-162
-        if (WF) { s.L = s.L + Le; so->a = Lr_dir; so->b = f3(1.f); }
+        if (WF && !ADJ) { s.L = s.L + Le; so->a = Lr_dir; so->b = f3(1.f); }
         else s.L = ADJ ? (s.L - Le - Lr_dir) : (s.L + Le + Lr_dir);                         // prb.py:173
     }
     s.ray = spawn_ray(si.p, si.n, si.sh.to_world(bs.wo));

@@ -27,6 +27,8 @@ struct WfState {                     // all arrays have `capacity` entries, inde
     float2 *pos;                     // splat position
     float4 *hit;                     // t, u, v | face (bits)
     uint32_t *hit_mesh;
+    float4 *dl;                      // PRB adjoint: dL (adjoint radiance of the lane's splat), xyz
+    uint32_t *vis;                   // PRB: bit k = the emitter sample of bounce k arrived (primal pass -> adjoint replay)
     float4 *sh_o, *sh_d, *sh_a, *sh_b;   // deferred NEE: shadow ray o|maxt, d|-, factors a, b
     uint32_t *q[2];                  // closest-ray queues (lane slots), double buffered by iteration parity
     uint32_t *q_shadow[2];           // shadow-ray queues, by iteration parity
@@ -43,6 +45,7 @@ struct WfLaunch {
     uint32_t it;                     // global iteration counter (slot = it & 3)
     uint32_t pass;                   // > 0: continue each lane's PCG32 stream (integrator.cpp:319-328)
     uint32_t slice;                  // trace: traversal micro-steps between two refill points
+    uint32_t vis_bit;                // trace: bit to set in vis[] for arriving shadow rays; shade<ADJ>: bit to read; ~0u = off
     uint32_t tri_thresh;             // trace: lanes with pending leaf triangles that trigger a triangle step
 };
 
@@ -51,6 +54,9 @@ size_t wf_state_bytes(uint32_t capacity);
 void wf_bind(WfState &st, void *base, uint32_t capacity);
 // Renders lanes [p.lane_begin, p.lane_end) of every pass into p.film.  Returns the number of kernels launched, or -1
 // with `err` set.
+// PRB adjoint for lanes [p.lane_begin, p.lane_end): primal pass (records emitter-sample visibility), then the replay
+// with gradient scatter.  p.wfilm must hold the weight film of the sample set.  Needs max_depth <= 32.
+long wf_render_backward(bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err);
 long wf_render(int variant, bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err);
 
 }  // namespace b2

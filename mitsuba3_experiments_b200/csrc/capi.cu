@@ -219,6 +219,19 @@ int b2_scene_set_param(b2_scene *s, const char *key, const void *dev_ptr, size_t
     return fail(-2, std::string("b2_scene_set_param: unknown key '") + key + "'");
 }
 
+// wavefront: the lane state of one chunk lives in HBM (208 B per lane); default chunk = 16 Mi lanes (3.5 GB)
+static int wf_reserve(b2_scene *s, uint64_t shard_lanes, uint32_t chunk_lanes, cudaStream_t st) {
+    const uint32_t want = (uint32_t) std::min<uint64_t>(shard_lanes, chunk_lanes ? std::max<uint32_t>(chunk_lanes, 256u) : (16u << 20));
+    if (want > s->wf_capacity) {
+        CUDA_OK(cudaStreamSynchronize(st));
+        if (s->wf_mem) { cudaFree(s->wf_mem); s->wf_mem = nullptr; s->wf_capacity = 0; }
+        CUDA_OK(cudaMalloc(&s->wf_mem, wf_state_bytes(want)));
+        s->wf_capacity = want;
+    }
+    wf_bind(s->wf, s->wf_mem, want);
+    return 0;
+}
+
 // integrator.cpp:139-152,247-265
 static int derive_passes(const b2_scene *s, const b2_render_args *a, uint32_t &spp_per_pass, uint32_t &n_passes, uint64_t &wavefront) {
     if (a->spp == 0) return fail(-2, "render: spp must be > 0");
@@ -290,15 +303,7 @@ int b2_render(b2_scene *s, const b2_render_args *a, float *film, uintptr_t strea
     if (a->kernel != B2_KERNEL_WAVEFRONT && a->kernel != B2_KERNEL_MEGAKERNEL) return fail(-2, "render: unknown kernel");
     if (p.lane_end > p.lane_begin && a->kernel == B2_KERNEL_WAVEFRONT) {
         // wavefront: lane state of one chunk lives in HBM (188 B per lane); default chunk = 16 Mi lanes (3.2 GB)
-        const uint64_t shard = p.lane_end - p.lane_begin;
-        const uint32_t want = (uint32_t) std::min<uint64_t>(shard, a->chunk_lanes ? std::max<uint32_t>(a->chunk_lanes, 256u) : (16u << 20));
-        if (want > s->wf_capacity) {
-            CUDA_OK(cudaStreamSynchronize(st));
-            if (s->wf_mem) { cudaFree(s->wf_mem); s->wf_mem = nullptr; s->wf_capacity = 0; }
-            CUDA_OK(cudaMalloc(&s->wf_mem, wf_state_bytes(want)));
-            s->wf_capacity = want;
-        }
-        wf_bind(s->wf, s->wf_mem, want);
+        if (int rc = wf_reserve(s, p.lane_end - p.lane_begin, a->chunk_lanes, st)) return rc;
         const char *err = nullptr;
         const long n = wf_render(a->variant, count, p, s->wf, s->ctx->sm_count, st, &err);
         if (n < 0) return fail(-11, err ? err : "wavefront render failed");
@@ -362,7 +367,15 @@ int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_i
         }
         CUDA_OK(cudaMemsetAsync(s->unit_counter, 0, 16, st));
         if (count) CUDA_OK(cudaMemsetAsync(s->counters_dev, 0, sizeof(unsigned long long) * C_N, st));
-        if (p.unit_end > p.unit_begin) { launch_render(B2_VARIANT_PRB, MODE_BACKWARD, count, p, blocks, smem, st); launches++; }
+        if (a->kernel == B2_KERNEL_WAVEFRONT && a->max_depth <= 32) {
+            if (p.lane_end > p.lane_begin) {
+                if (int rc = wf_reserve(s, p.lane_end - p.lane_begin, a->chunk_lanes, st)) return rc;
+                const char *err = nullptr;
+                const long n = wf_render_backward(count, p, s->wf, s->ctx->sm_count, st, &err);
+                if (n < 0) return fail(-11, err ? err : "wavefront render_backward failed");
+                launches += (uint64_t) n;
+            }
+        } else if (p.unit_end > p.unit_begin) { launch_render(B2_VARIANT_PRB, MODE_BACKWARD, count, p, blocks, smem, st); launches++; }
         CUDA_OK(cudaGetLastError());
     }
     if (count) {

@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(256) k_wf_generate(const __grid_constant__ Ren
         wf_store_path(st, i, s, true);
         st.pos[i] = make_float2(s.pos.x, s.pos.y);
         st.hit[i] = make_float4(s.ray.maxt, 0.f, 0.f, __uint_as_float(0xffffffffu));     // a miss, unless trace(it) overwrites it
-        st.hit_mesh[i] = 0u;
+        st.hit_mesh[i] = 0u; st.vis[i] = 0u;
         q[i] = i;
     }
 }
@@ -259,6 +259,7 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
             if (r.any) {
                 if (!r.found) {         // the emitter sample arrives: L <- fma(a, b, L)
                     if (r.tex) cnt.add(C_TEX);
+                    if (w.vis_bit != 0xffffffffu) st.vis[r.slot] |= 1u << w.vis_bit;
                     const float4 a = st.sh_a[r.slot], b = st.sh_b[r.slot]; float4 L = st.rad[r.slot];
                     L.x = fma_(a.x, b.x, L.x); L.y = fma_(a.y, b.y, L.y); L.z = fma_(a.z, b.z, L.z);
                     st.rad[r.slot] = L;
@@ -274,14 +275,16 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
 }
 
 // ------------------------------------------------------------------------------------------ shade
-template <int V, bool COUNT>
+template <int V, bool COUNT, bool ADJ = false>
 __global__ void __launch_bounds__(256, B2_SHADE_MINBLOCKS) k_wf_shade(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
     __shared__ uint32_t s_cnt[2][8], s_base[2];
+    __shared__ float s_gconst[kMaxGradTargets * 3];     // adjoint: per-block sums of the constant-albedo gradients
     const WfState &st = w.st;
     const uint32_t it = w.it, n = st.ctl->n_closest[it & 3u];
     const uint32_t *qin = st.q[it & 1u]; uint32_t *qout = st.q[(it + 1u) & 1u], *qsh = st.q_shadow[0];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    Counters<COUNT> cnt; GradSink gs{ nullptr };
+    Counters<COUNT> cnt; GradSink gs{ s_gconst };
+    if (ADJ) { if (tid < kMaxGradTargets * 3) s_gconst[tid] = 0.f; __syncthreads(); }
     if (blockIdx.x == 0 && tid == 0) { const uint32_t z = (it + 2u) & 3u; st.ctl->n_closest[z] = 0u; st.ctl->n_shadow[z] = 0u; st.ctl->fetch[z] = 0u; }
 
     for (uint32_t base = blockIdx.x * 256u; base < n; base += gridDim.x * 256u) {
@@ -292,8 +295,13 @@ __global__ void __launch_bounds__(256, B2_SHADE_MINBLOCKS) k_wf_shade(const __gr
             Path s; wf_load_path(st, slot, s);
             const float4 hh = st.hit[slot];
             Hit h; h.t = hh.x; h.u = hh.y; h.v = hh.z; h.face = __float_as_uint(hh.w); h.mesh = st.hit_mesh[slot];
-            ShadowRec so; so.valid = false; so.tex = false; so.a = f3(0.f); so.b = f3(0.f);
-            alive = path_step<V, false, COUNT, true>(p, s, gs, cnt, &h, &so);
+            ShadowRec so; so.valid = false; so.tex = false; so.vis = false; so.a = f3(0.f); so.b = f3(0.f);
+            if (ADJ) {
+                const float4 g = st.dl[slot]; s.dL = f3(g.x, g.y, g.z); s.adjoint = true;
+                so.vis = ((st.vis[slot] >> w.vis_bit) & 1u) != 0u;
+            }
+            alive = path_step<V, ADJ, COUNT, true>(p, s, gs, cnt, &h, &so);
+            if (ADJ && !alive) cnt.add(C_SAMPLES);
             wf_store_path(st, slot, s, alive);
             shadow = so.valid;
             if (shadow) {
@@ -318,7 +326,43 @@ __global__ void __launch_bounds__(256, B2_SHADE_MINBLOCKS) k_wf_shade(const __gr
         if (shadow) qsh[s_base[1] + s_cnt[1][warp] + __popc(ms & lt)] = slot;
         __syncthreads();
     }
+    if (ADJ) {
+        __syncthreads();
+        if (tid < p.n_targets * 3 && p.targets[tid / 3].kind == 0) { const float v = s_gconst[tid]; if (v != 0.f) atomicAdd(p.targets[tid / 3].grad + tid % 3, v); }
+    }
     wf_flush_counters(cnt, p.counters);
+}
+
+// Adjoint pass set-up (RBIntegrator.render_backward, common.py:728-773): the lane keeps the radiance L of its primal
+// pass, reseeds its sampler to replay the identical stream, and gathers dL = sum_p grad_in[p] * w(p) / W[p], the
+// adjoint of splat + develop w.r.t. the splatted value.
+__global__ void __launch_bounds__(256) k_wf_generate_adj(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
+    const WfState &st = w.st; const DSensor &sn = p.sc.sensor;
+    if (blockIdx.x == 0 && threadIdx.x < 4) {
+        const uint32_t k = threadIdx.x;
+        st.ctl->n_closest[k] = (k == (w.it & 3u)) ? w.n : 0u; st.ctl->n_shadow[k] = 0u; st.ctl->fetch[k] = 0u;
+    }
+    uint32_t *q = st.q[w.it & 1u];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < w.n; i += gridDim.x * blockDim.x) {
+        Path s;
+        s.lane = (uint32_t) (w.chunk_begin + i); s.pass = 0; s.adjoint = true;
+        const float4 l = st.rad[i];
+        s.rng.seed_lane(p.seed, s.lane);
+        start_path<B2_VARIANT_PRB>(p, s);
+        s.L = f3(l.x, l.y, l.z);
+        f3 dL(0.f);
+        film_taps(p, s.pos, [&](int x, int y, float wgt) {
+            const size_t pix = (size_t) y * sn.crop_width + x;
+            float W = __ldg(p.wfilm + 4 * pix + 3); W = W == 0.f ? 1.f : W;
+            const float k = wgt / W;
+            dL += f3(__ldg(p.grad_in + 3 * pix) * k, __ldg(p.grad_in + 3 * pix + 1) * k, __ldg(p.grad_in + 3 * pix + 2) * k);
+        });
+        wf_store_path(st, i, s, true);
+        st.dl[i] = make_float4(dL.x, dL.y, dL.z, 0.f);
+        st.hit[i] = make_float4(s.ray.maxt, 0.f, 0.f, __uint_as_float(0xffffffffu));
+        st.hit_mesh[i] = 0u;
+        q[i] = i;
+    }
 }
 
 // ------------------------------------------------------------------------------------------ splat
@@ -380,7 +424,7 @@ static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 size_t wf_state_bytes(uint32_t cap) {
     const size_t c = cap;
-    return align_up(c * 16, 256) * 11 + align_up(c * 8, 256) + align_up(c * 4, 256) * 4 + 256;
+    return align_up(c * 16, 256) * 12 + align_up(c * 8, 256) + align_up(c * 4, 256) * 5 + 256;
 }
 
 void wf_bind(WfState &st, void *base, uint32_t cap) {
@@ -390,11 +434,18 @@ void wf_bind(WfState &st, void *base, uint32_t cap) {
     st.rng = (uint4 *) take(c * 16); st.ray_o = (float4 *) take(c * 16); st.ray_d = (float4 *) take(c * 16); st.thr = (float4 *) take(c * 16);
     st.rad = (float4 *) take(c * 16); st.prev = (float4 *) take(c * 16); st.hit = (float4 *) take(c * 16);
     st.sh_o = (float4 *) take(c * 16); st.sh_d = (float4 *) take(c * 16); st.sh_a = (float4 *) take(c * 16); st.sh_b = (float4 *) take(c * 16);
+    st.dl = (float4 *) take(c * 16); st.vis = (uint32_t *) take(c * 4);
     st.pos = (float2 *) take(c * 8);
     st.hit_mesh = (uint32_t *) take(c * 4); st.q[0] = (uint32_t *) take(c * 4); st.q[1] = (uint32_t *) take(c * 4); st.q_shadow[0] = (uint32_t *) take(c * 4);
     st.q_shadow[1] = st.q_shadow[0];
     st.capacity = cap;
 }
+
+// tuning knobs (environment overrides are for sweeps on the GPU box; the defaults are the measured optimum)
+static int env_int(const char *name, int def) { const char *v = getenv(name); return v ? std::max(1, atoi(v)) : def; }
+static const uint32_t tune_slice = (uint32_t) env_int("B2_TRACE_SLICE", B2_TRACE_SLICE);
+static const uint32_t tune_tri = (uint32_t) env_int("B2_TRI_THRESH", 8);
+static const int tune_trace_blocks = getenv("B2_TRACE_BLOCKS") ? atoi(getenv("B2_TRACE_BLOCKS")) : 0;
 
 template <int V, bool COUNT>
 static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {
@@ -411,14 +462,11 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
     const uint64_t lane_lo = p.lane_begin, lane_hi = p.lane_end;
     const bool skip_first_trace = V == B2_VARIANT_PATH && p.max_depth <= 1;
     const bool bounded = p.max_depth <= 64;
-    static const uint32_t tune_slice = getenv("B2_TRACE_SLICE") ? (uint32_t) std::max(1, atoi(getenv("B2_TRACE_SLICE"))) : (uint32_t) B2_TRACE_SLICE;
-    static const uint32_t tune_tri = getenv("B2_TRI_THRESH") ? (uint32_t) std::max(1, atoi(getenv("B2_TRI_THRESH"))) : 8u;
-    static const int tune_trace_blocks = getenv("B2_TRACE_BLOCKS") ? atoi(getenv("B2_TRACE_BLOCKS")) : 0;
     const uint32_t n_iter = bounded ? (uint32_t) std::max(p.max_depth, 1) : 0u;
     uint32_t it = 0;
     for (uint64_t c0 = lane_lo; c0 < lane_hi; c0 += st.capacity) {
         const uint32_t n = (uint32_t) std::min<uint64_t>(st.capacity, lane_hi - c0);
-        WfLaunch w; w.st = st; w.chunk_begin = c0; w.n = n; w.slice = tune_slice; w.tri_thresh = tune_tri;
+        WfLaunch w; w.st = st; w.chunk_begin = c0; w.n = n; w.slice = tune_slice; w.tri_thresh = tune_tri; w.vis_bit = 0xffffffffu;
         const int g_gen = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) sm_count * 8);
         const int g_trace = (tune_trace_blocks > 0 ? std::min(tune_trace_blocks, occ_trace) : occ_trace) * sm_count, g_shade = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_shade * sm_count);
         for (uint32_t pass = 0; pass < p.n_passes; ++pass) {
@@ -452,6 +500,56 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
     }
     if (cudaGetLastError() != cudaSuccess) { *err = "wavefront: kernel launch failed"; return -1; }
     return launches;
+}
+
+template <bool COUNT>
+static long wf_render_backward_t(RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {
+    constexpr int V = B2_VARIANT_PRB;
+    long launches = 0;
+    int occ_trace = 0, occ_shade = 0, occ_adj = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_trace, k_wf_trace<COUNT>, kTraceThreads, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<V, COUNT, false>, 256, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_adj, k_wf_shade<V, COUNT, true>, 256, 0);
+    if (occ_trace <= 0 || occ_shade <= 0 || occ_adj <= 0) { *err = "wavefront: a kernel cannot be resident (occupancy 0)"; return -1; }
+    if (p.max_depth > 32) { *err = "wavefront render_backward: max_depth > 32"; return -1; }
+    const uint32_t n_iter = (uint32_t) std::max(p.max_depth, 1);
+    uint32_t it = 0;
+    for (uint64_t c0 = p.lane_begin; c0 < p.lane_end; c0 += st.capacity) {
+        const uint32_t n = (uint32_t) std::min<uint64_t>(st.capacity, p.lane_end - c0);
+        WfLaunch w; w.st = st; w.chunk_begin = c0; w.n = n; w.slice = tune_slice; w.tri_thresh = tune_tri; w.pass = 0;
+        const int g_gen = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) sm_count * 8);
+        const int g_trace = (tune_trace_blocks > 0 ? std::min(tune_trace_blocks, occ_trace) : occ_trace) * sm_count;
+        const int g_shade = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_shade * sm_count);
+        const int g_adj = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_adj * sm_count);
+        // ---- primal pass (common.py:750-760): L per lane, and the visibility bit of every emitter sample
+        w.it = it; w.vis_bit = 0xffffffffu;
+        k_wf_generate<V><<<g_gen, 256, 0, stream>>>(p, w); launches++;
+        for (uint32_t k = 0; k < n_iter; ++k) {
+            w.it = it; w.vis_bit = k ? k - 1u : 0xffffffffu;
+            k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); launches++;
+            k_wf_shade<V, COUNT, false><<<g_shade, 256, 0, stream>>>(p, w); launches++;
+            ++it;
+        }
+        w.it = it; w.vis_bit = n_iter - 1u;
+        k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); launches++;
+        ++it;
+        // ---- adjoint pass (common.py:763-773): replay of the identical stream, closest-hit rays only
+        w.it = it; w.vis_bit = 0xffffffffu;
+        k_wf_generate_adj<<<g_gen, 256, 0, stream>>>(p, w); launches++;
+        for (uint32_t k = 0; k < n_iter; ++k) {
+            w.it = it; w.vis_bit = 0xffffffffu;
+            k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); launches++;
+            w.vis_bit = k;
+            k_wf_shade<V, COUNT, true><<<g_adj, 256, 0, stream>>>(p, w); launches++;
+            ++it;
+        }
+    }
+    if (cudaGetLastError() != cudaSuccess) { *err = "wavefront: kernel launch failed"; return -1; }
+    return launches;
+}
+
+long wf_render_backward(bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {
+    return count ? wf_render_backward_t<true>(p, st, sm_count, stream, err) : wf_render_backward_t<false>(p, st, sm_count, stream, err);
 }
 
 long wf_render(int variant, bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {

@@ -121,6 +121,7 @@ class B2Integrator:
         self.max_depth = int(get("max_depth", self.default_max_depth))
         self.rr_depth = int(get("rr_depth", self.default_rr_depth))
         self.samples_per_pass = int(get("samples_per_pass", 0) or 0)
+        self.kernel = {"wavefront": capi.KERNEL_WAVEFRONT, "megakernel": capi.KERNEL_MEGAKERNEL}[get("kernel", "wavefront")]
         self.env_warp = {"hierarchical": capi.ENV_WARP_HIERARCHICAL, "alias": capi.ENV_WARP_ALIAS}[get("env_warp", "hierarchical")]
         if self.max_depth < 0:
             if self.max_depth != -1:
@@ -159,7 +160,7 @@ class B2Integrator:
 
     def _args(self, scene: DeviceScene, seed, spp, **kw):
         return dict(seed=seed, spp=spp or scene.desc.spp, max_depth=self.max_depth, rr_depth=self.rr_depth,
-                    variant=self.variant, spp_per_pass=self.samples_per_pass, env_warp=self.env_warp, **kw)
+                    variant=self.variant, spp_per_pass=self.samples_per_pass, env_warp=self.env_warp, kernel=self.kernel, **kw)
 
     def render(self, scene, sensor=0, seed=0, spp=0, develop=True, evaluate=True, film=None, lane_begin=0, lane_end=0,
                counters=False):

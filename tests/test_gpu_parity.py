@@ -181,8 +181,9 @@ def test_render_host_and_errors():
         ds.set_param(0, "data", torch.zeros(3))               # constant reflectance has no .data
 
 
+@pytest.mark.parametrize("kernel", ["wavefront", "megakernel"])
 @pytest.mark.parametrize("textured", [False, True])
-def test_prb_backward_parity(textured):
+def test_prb_backward_parity(textured, kernel):
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
     from mitsuba3_experiments_b200.integrator import PRBIntegrator, traverse
     d = cornell_box(48, 48, spp=16)
@@ -195,7 +196,7 @@ def test_prb_backward_parity(textured):
     params = traverse(ds)
     keys = [k for k in params if k.startswith("white.") or k.startswith("red.")]
     params.keep(keys)
-    prb = PRBIntegrator({"max_depth": 6, "rr_depth": 3})
+    prb = PRBIntegrator({"max_depth": 6, "rr_depth": 3, "kernel": kernel})
     prb.render_backward(ds, params, torch.from_numpy(grad_in), seed=7, spp=16, counters=True)
     torch.cuda.synchronize()
     targets = []
@@ -215,6 +216,8 @@ def test_prb_backward_parity(textured):
         else:
             np.testing.assert_allclose(g, ref, rtol=1e-3)
     cnt = prb.last_counters
+    if kernel == "wavefront":        # the replay reuses the visibility bits recorded by the primal pass: half the shadow rays
+        cnt["shadow_rays"] *= 2
     for k in ("samples", "closest_rays", "shadow_rays", "grad_atomics"):
         assert abs(cnt[k] - rc[k]) <= 1e-3 * max(rc[k], 1), (k, cnt[k], rc[k])
 
