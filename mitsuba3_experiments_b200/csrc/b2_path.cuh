@@ -89,16 +89,62 @@ struct Path {
     uint32_t lane, pass;
 };
 
+// lane -> pixel (integrator.cpp:293-310) and the jittered film position (the first two draws of the lane's stream)
+B2_DEV f2 lane_sample_pos(const RenderParams &p, uint32_t lane, Pcg32 &rng, int &px, int &py) {
+    const DSensor &sn = p.sc.sensor;
+    uint32_t idx = lane;
+    idx = (p.spp_shift != 0xffffffffu) ? (idx >> p.spp_shift) : (idx / p.spp_per_pass);
+    const uint32_t y = idx / (uint32_t) sn.crop_width, x = idx - (uint32_t) sn.crop_width * y;
+    px = (int) x + sn.crop_offset_x; py = (int) y + sn.crop_offset_y;
+    const f2 j = rng.next_2d();
+    return f2{ (float) px + j.x, (float) py + j.y };
+}
+
+// ImageBlock::put for a group of `g` adjacent lanes (g a power of two <= 32) whose samples fall on the same pixel and
+// hence share one footprint: every tap value is summed over the group with xor-shuffles and the group's first lane
+// issues ONE add per tap and channel -- the warp-aggregated form of the per-sample atomics (the reference aggregates
+// the same way inside dr.scatter_reduce, drjit-core cuda_scatter.cpp:63-230).  All 32 lanes must call this together.
+// add(x, y, rgbw) receives crop-relative in-bounds coordinates.  Returns this lane's own in-bounds tap count.
+template <bool WEIGHTS_ONLY, class ADD>
+B2_DEV uint32_t film_taps_group(const RenderParams &p, f2 pos, f3 L, bool valid, uint32_t g, bool leader, ADD &&add) {
+    const DSensor &s = p.sc.sensor;
+    const bool box = s.rfilter == B2_RFILTER_BOX;
+    const int n = box ? 0 : p.filter_n, count = 2 * n + 1;
+    const int pix = (int) floorf(pos.x) - n, piy = (int) floorf(pos.y) - n;
+    const int lx = pix - s.crop_offset_x, ly = piy - s.crop_offset_y;
+    float relx = (float) pix + .5f - pos.x, rely = (float) piy + .5f - pos.y;
+    float wx[5], wy[5];
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+        if (i < count && valid) { wx[i] = box ? 1.f : rfilter_eval(s, relx); wy[i] = box ? 1.f : rfilter_eval(s, rely); relx += 1.f; rely += 1.f; }
+        else { wx[i] = 0.f; wy[i] = 0.f; }
+    }
+    uint32_t nx = 0, ny = 0;
+#pragma unroll
+    for (int ys = 0; ys < 5; ++ys) {
+        if (ys >= count) break;
+        const bool yin = (unsigned) (ly + ys) < (unsigned) s.crop_height; ny += yin;
+#pragma unroll
+        for (int xs = 0; xs < 5; ++xs) {
+            if (xs >= count) break;
+            const bool xin = (unsigned) (lx + xs) < (unsigned) s.crop_width; if (ys == 0) nx += xin;
+            const float wgt = wy[ys] * wx[xs];
+            float4 v = make_float4(L.x * wgt, L.y * wgt, L.z * wgt, 1.f * wgt);
+            for (uint32_t o = g >> 1; o; o >>= 1) {
+                if (!WEIGHTS_ONLY) { v.x += __shfl_xor_sync(0xffffffffu, v.x, o); v.y += __shfl_xor_sync(0xffffffffu, v.y, o); v.z += __shfl_xor_sync(0xffffffffu, v.z, o); }
+                v.w += __shfl_xor_sync(0xffffffffu, v.w, o);
+            }
+            if (leader && valid && yin && xin) add(lx + xs, ly + ys, v);
+        }
+    }
+    return valid ? nx * ny : 0u;
+}
+
 template <int V>
 B2_DEV void start_path(const RenderParams &p, Path &s) {
     const DSensor &sn = p.sc.sensor;
-    // lane -> pixel (integrator.cpp:293-310)
-    uint32_t idx = s.lane;
-    idx = (p.spp_shift != 0xffffffffu) ? (idx >> p.spp_shift) : (idx / p.spp_per_pass);
-    const uint32_t y = idx / (uint32_t) sn.crop_width, x = idx - (uint32_t) sn.crop_width * y;
-    const int px = (int) x + sn.crop_offset_x, py = (int) y + sn.crop_offset_y;
-    const f2 j = s.rng.next_2d();
-    const f2 sample_pos{ (float) px + j.x, (float) py + j.y };
+    int px, py;
+    const f2 sample_pos = lane_sample_pos(p, s.lane, s.rng, px, py);
     const f2 adjusted{ fma_(sample_pos.x, sn.scale_x, sn.offset_x), fma_(sample_pos.y, sn.scale_y, sn.offset_y) };
     s.ray = camera_ray(sn, adjusted);
     s.pos = sn.rfilter == B2_RFILTER_BOX ? f2{ (float) px, (float) py } : sample_pos;

@@ -57,6 +57,7 @@ void wf_bind(WfState &st, void *base, uint32_t capacity);
 // PRB adjoint for lanes [p.lane_begin, p.lane_end): primal pass (records emitter-sample visibility), then the replay
 // with gradient scatter.  p.wfilm must hold the weight film of the sample set.  Needs max_depth <= 32.
 long wf_render_backward(bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err);
+long wf_weights(RenderParams p, int sm_count, cudaStream_t stream, const char **err);
 long wf_render(int variant, bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err);
 
 }  // namespace b2

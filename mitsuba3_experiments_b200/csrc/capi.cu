@@ -219,9 +219,9 @@ int b2_scene_set_param(b2_scene *s, const char *key, const void *dev_ptr, size_t
     return fail(-2, std::string("b2_scene_set_param: unknown key '") + key + "'");
 }
 
-// wavefront: the lane state of one chunk lives in HBM (208 B per lane); default chunk = 16 Mi lanes (3.5 GB)
+// wavefront: the lane state of one chunk lives in HBM (208 B per lane); default chunk = 64 Mi lanes (14 GB of the 180 GB)
 static int wf_reserve(b2_scene *s, uint64_t shard_lanes, uint32_t chunk_lanes, cudaStream_t st) {
-    const uint32_t want = (uint32_t) std::min<uint64_t>(shard_lanes, chunk_lanes ? std::max<uint32_t>(chunk_lanes, 256u) : (16u << 20));
+    const uint32_t want = (uint32_t) std::min<uint64_t>(shard_lanes, chunk_lanes ? std::max<uint32_t>(chunk_lanes, 256u) : (64u << 20));
     if (want > s->wf_capacity) {
         CUDA_OK(cudaStreamSynchronize(st));
         if (s->wf_mem) { cudaFree(s->wf_mem); s->wf_mem = nullptr; s->wf_capacity = 0; }
@@ -349,7 +349,12 @@ int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_i
         p.film = s->wfilm;
         CUDA_OK(cudaMemsetAsync(s->wfilm, 0, film_bytes, st));
         CUDA_OK(cudaMemsetAsync(s->unit_counter, 0, 16, st));
-        launch_render(B2_VARIANT_PRB, MODE_WEIGHTS, false, p, blocks, smem, st); launches++;
+        if (a->kernel == B2_KERNEL_WAVEFRONT) {
+            const char *err = nullptr;
+            const long n = wf_weights(p, s->ctx->sm_count, st, &err);
+            if (n < 0) return fail(-11, err ? err : "wavefront weight splat failed");
+            launches += (uint64_t) n;
+        } else { launch_render(B2_VARIANT_PRB, MODE_WEIGHTS, false, p, blocks, smem, st); launches++; }
         CUDA_OK(cudaGetLastError());
     }
     // (2) primal pass + adjoint replay per lane (common.py:750-773)

@@ -390,21 +390,42 @@ __global__ void __launch_bounds__(256) k_wf_splat(const __grid_constant__ Render
         const int tx0 = (int) x0 - p.filter_n, ty0 = (int) row - p.filter_n;
         for (uint32_t i = tid; i < tile_cells; i += 256) s_tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         __syncthreads();
-        for (uint32_t i = tid; i < n_lanes; i += 256) {
-            const uint32_t slot = (uint32_t) (lane_lo + i - c_lo);
-            const float2 ps = st.pos[slot];
-            f3 L(0.f);
-            if (!WEIGHTS_ONLY) {
-                const float4 l = st.rad[slot]; L = f3(l.x, l.y, l.z);
-                if (V == B2_VARIANT_PATH_MIS && !(__float_as_uint(l.w) & WF_FLAG_VALID_RAY)) L = f3(0.f);
+        const uint32_t g = (p.spp_shift != 0xffffffffu) ? min(p.spp_per_pass, 32u) : 1u;     // lanes per pixel group in a warp
+        for (uint32_t base = 0; base < n_lanes; base += 256) {
+            const uint32_t i = base + tid; const bool valid = i < n_lanes;
+            f2 ps{ 0.f, 0.f }; f3 L(0.f);
+            if (valid) {
+                if (WEIGHTS_ONLY) {             // weight film of the sample set: positions re-derived from (seed, lane)
+                    Pcg32 rng; const uint32_t ln = (uint32_t) (lane_lo + i); rng.seed_lane(p.seed, ln);
+                    int px, py; ps = lane_sample_pos(p, ln, rng, px, py);
+                    if (sn.rfilter == B2_RFILTER_BOX) ps = f2{ (float) px, (float) py };
+                } else {
+                    const uint32_t slot = (uint32_t) (lane_lo + i - c_lo);
+                    const float2 q = st.pos[slot]; ps = f2{ q.x, q.y };
+                    const float4 l = st.rad[slot]; L = f3(l.x, l.y, l.z);
+                    if (V == B2_VARIANT_PATH_MIS && !(__float_as_uint(l.w) & WF_FLAG_VALID_RAY)) L = f3(0.f);
+                }
             }
-            const uint32_t taps = film_taps(p, f2{ ps.x, ps.y }, [&](int x, int y, float wgt) {
+            auto add = [&](int x, int y, float4 v) {
                 const int cx = x - tx0, cy = y - ty0;
                 float *c = ((unsigned) cx < p.tile_cols && (unsigned) cy < p.tile_rows) ? (float *) (s_tile + cy * p.tile_cols + cx)
                                                                                         : p.film + 4 * ((size_t) y * sn.crop_width + x);
-                atomicAdd(c, L.x * wgt); atomicAdd(c + 1, L.y * wgt); atomicAdd(c + 2, L.z * wgt); atomicAdd(c + 3, 1.f * wgt);
-            });
-            cnt.add(C_TAPS, taps); cnt.add(C_SAMPLES);
+                if (!WEIGHTS_ONLY) { atomicAdd(c, v.x); atomicAdd(c + 1, v.y); atomicAdd(c + 2, v.z); }
+                atomicAdd(c + 3, v.w);
+            };
+            // samples of one pixel sit in adjacent lanes: reduce each tap over the pixel's lanes, one add per group
+            bool fast = false; const uint32_t lid = tid & 31u, lead = lid & ~(g - 1u);
+            if (g > 1u) {
+                const uint32_t key = valid ? (uint32_t) ((lane_lo + i) >> p.spp_shift) : 0xffffffffu;
+                const int ax = (int) floorf(ps.x), ay = (int) floorf(ps.y);
+                const uint32_t lk = __shfl_sync(0xffffffffu, key, lead);
+                const int lax = __shfl_sync(0xffffffffu, ax, lead), lay = __shfl_sync(0xffffffffu, ay, lead);
+                fast = __all_sync(0xffffffffu, !valid || (key == lk && ax == lax && ay == lay));
+            }
+            uint32_t taps;
+            if (fast) taps = film_taps_group<WEIGHTS_ONLY>(p, ps, L, valid, g, lid == lead, add);
+            else taps = film_taps_group<WEIGHTS_ONLY>(p, ps, L, valid, 1u, true, add);
+            cnt.add(C_TAPS, taps); if (valid) cnt.add(C_SAMPLES);
         }
         __syncthreads();
         for (uint32_t i = tid; i < tile_cells; i += 256) {
@@ -546,6 +567,23 @@ static long wf_render_backward_t(RenderParams p, WfState &st, int sm_count, cuda
     }
     if (cudaGetLastError() != cudaSuccess) { *err = "wavefront: kernel launch failed"; return -1; }
     return launches;
+}
+
+// Weight film of a sample set (ADIntegrator: the dummy splat of common.py:728-741): every lane of the pass wavefront
+// splats weight 1 at its film position, which depends only on (seed, lane).  p.film = the weight film, units = all.
+long wf_weights(RenderParams p, int sm_count, cudaStream_t stream, const char **err) {
+    const size_t smem = sizeof(float4) * (size_t) p.tile_cols * p.tile_rows;
+    auto k = k_wf_splat<B2_VARIANT_PRB, false, true>;
+    int occ = 0;
+    cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k, 256, smem);
+    if (occ <= 0) { *err = "wavefront: the splat kernel cannot be resident"; return -1; }
+    if (p.unit_end <= p.unit_begin) return 0;
+    WfLaunch w{}; w.chunk_begin = p.lane_begin; w.n = (uint32_t) (p.lane_end - p.lane_begin);
+    cudaMemsetAsync(p.unit_counter, 0, 4, stream);
+    k<<<(int) std::min<uint32_t>(p.unit_end - p.unit_begin, (uint32_t) (occ * sm_count)), 256, smem, stream>>>(p, w);
+    if (cudaGetLastError() != cudaSuccess) { *err = "wavefront: kernel launch failed"; return -1; }
+    return 1;
 }
 
 long wf_render_backward(bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {
