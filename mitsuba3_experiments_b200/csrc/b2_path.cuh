@@ -174,14 +174,14 @@ B2_DEV bool first_trace_needed(const RenderParams &p, const Path &s) {
 
 // WF = false: the closest hit and the shadow ray are traced here (megakernel).  WF = true: `pre_hit` holds the closest
 // hit found by the wavefront trace kernel for s.ray, and the shadow ray is recorded in `so` instead of being traced.
-template <int V, bool ADJ, bool COUNT, bool WF = false>
+template <int V, bool ADJ, bool COUNT, bool WF = false, int CLS = CLS_GENERIC>
 B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counters<COUNT> &cnt, const Hit *pre_hit = nullptr, ShadowRec *so = nullptr) {
     // WF && ADJ: the adjoint pass replays the lane's sample stream; the visibility of each emitter sample was recorded
     // by the primal pass of the same render_backward call (identical rays), so no shadow ray is traced again.
     const DScene &sc = p.sc;
     const uint32_t max_depth = (uint32_t) p.max_depth;
     Hit h; h.face = 0xffffffffu; h.t = s.ray.maxt; h.u = h.v = 0.f; h.mesh = 0;
-    if (WF) h = *pre_hit;
+    if (WF) { h = *pre_hit; if (CLS == CLS_MISS) h.face = 0xffffffffu; }    // class known at compile time: the ray escaped
     else if (first_trace_needed<V>(p, s)) { cnt.add(C_CLOSEST); bvh_trace<false>(sc, s.ray.o, s.ray.d, s.ray.maxt, h, cnt); }
     SI si; make_si(sc, s.ray, h, si, cnt);
 
@@ -228,9 +228,9 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
     // ---- emitter sampling (NEE) + BSDF sampling.  si is valid from here on.
     const DBsdf &bsdf = sc.bsdfs[si.bsdf];
     ReflCache rc;
-    auto refl = [&]() { return reflectance(sc, bsdf, si, rc, cnt); };
+    auto refl = [&]() { return reflectance<CLS>(sc, bsdf, si, rc, cnt); };
     auto ones = []() { return f3(1.f); };
-    bool active_em = (bsdf_lobes(bsdf) & LOBE_SMOOTH) != 0;
+    bool active_em = (bsdf_lobes<CLS>(bsdf) & LOBE_SMOOTH) != 0;
     DS ds; f3 em_weight;
     sample_emitter_direction(sc, si, s.rng.next_2d(), active_em, p.env_warp, ds, em_weight, cnt, [&](const Ray &sr) {
         if (WF && ADJ) return !so->vis;
@@ -246,10 +246,10 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
         // path.py / prb.py evaluate the BSDF only for unoccluded emitter samples; the wavefront evaluates it before
         // the visibility is known, so the texture-evaluation *event* is counted by the trace kernel on arrival
         Counters<false> quiet; bool tex = false;
-        if (active_em) bsdf_eval_pdf(bsdf, si.wi, wo, [&]() { tex = bsdf.tex >= 0; return reflectance(sc, bsdf, si, rc, quiet); }, bsdf_val, bsdf_pdf);
+        if (active_em) bsdf_eval_pdf<CLS>(bsdf, si.wi, wo, [&]() { tex = cls_textured<CLS>(bsdf.tex); return reflectance<CLS>(sc, bsdf, si, rc, quiet); }, bsdf_val, bsdf_pdf);
         so->tex = tex;
-    } else if (active_em) bsdf_eval_pdf(bsdf, si.wi, wo, refl, bsdf_val, bsdf_pdf);
-    bsdf_sample(bsdf, si.wi, s1, s2, refl, bs, bsdf_weight);
+    } else if (active_em) bsdf_eval_pdf<CLS>(bsdf, si.wi, wo, refl, bsdf_val, bsdf_pdf);
+    bsdf_sample<CLS>(bsdf, si.wi, s1, s2, refl, bs, bsdf_weight);
     const f3 f_before = s.f;
     float mis_em;
     if (V == B2_VARIANT_PATH) {
@@ -298,12 +298,12 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
             // supported BSDF is linear in its reflectance, so the derivative is the value with reflectance := 1.
             f3 g(0.f);
             if (active_em) {
-                f3 unit; float dummy; bsdf_eval_pdf(bsdf, si.wi, wo, ones, unit, dummy);
+                f3 unit; float dummy; bsdf_eval_pdf<CLS>(bsdf, si.wi, wo, ones, unit, dummy);
                 g += s.dL * (f_before * mis_em * unit * em_weight);
             }
             if (active) {
                 const f3 wo2 = si.sh.to_local(s.ray.d);
-                f3 unit; float dummy; bsdf_eval_pdf(bsdf, si.wi, wo2, ones, unit, dummy);
+                f3 unit; float dummy; bsdf_eval_pdf<CLS>(bsdf, si.wi, wo2, ones, unit, dummy);
                 const f3 det = bsdf_weight * bs.pdf;
                 const f3 inv(det.x != 0.f ? rcp(det.x) : 0.f, det.y != 0.f ? rcp(det.y) : 0.f, det.z != 0.f ? rcp(det.z) : 0.f);
                 g += s.dL * (s.L * (inv * unit));

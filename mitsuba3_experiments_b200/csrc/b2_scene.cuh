@@ -26,7 +26,7 @@ struct alignas(16) DTexture {
     float to_uv[6];                  // first two rows of the 3x3 affine
 };
 
-struct alignas(16) DMesh { int32_t bsdf, emitter; uint32_t flags, first_face, n_faces, pad[3]; };
+struct alignas(16) DMesh { int32_t bsdf, emitter; uint32_t flags, first_face, n_faces, cls /* shading class, b2_shade.cuh */, pad[2]; };
 
 struct alignas(16) DEmitter {
     int32_t type, mesh, shape_kind; uint32_t cdf_offset;

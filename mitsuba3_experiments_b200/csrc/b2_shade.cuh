@@ -22,6 +22,16 @@ namespace b2 {
 enum { LOBE_DIFFUSE = 1, LOBE_GLOSSY = 2, LOBE_DELTA_R = 4, LOBE_DELTA_T = 8,
        LOBE_SMOOTH = LOBE_DIFFUSE | LOBE_GLOSSY, LOBE_DELTA = LOBE_DELTA_R | LOBE_DELTA_T };
 
+// Shading classes: the wavefront sorts the hits of a bounce by class and runs one specialised shade kernel per class
+// (CLS >= 0 turns the BSDF-type switch and the textured/constant test into compile-time constants); CLS_GENERIC keeps
+// both at run time (megakernel, adjoint replay).
+enum { CLS_GENERIC = -1, CLS_DIFFUSE = 0, CLS_DIFFUSE_TEX = 1, CLS_CONDUCTOR = 2, CLS_DIELECTRIC = 3, CLS_MISS = 4, CLS_COUNT = 5 };
+template <int CLS> B2_DEV int cls_type(int runtime_type) {
+    return (CLS == CLS_DIFFUSE || CLS == CLS_DIFFUSE_TEX) ? B2_BSDF_DIFFUSE : CLS == CLS_CONDUCTOR ? B2_BSDF_ROUGHCONDUCTOR
+           : CLS == CLS_DIELECTRIC ? B2_BSDF_DIELECTRIC : runtime_type;
+}
+template <int CLS> B2_DEV bool cls_textured(int tex) { return CLS == CLS_DIFFUSE ? false : CLS == CLS_DIFFUSE_TEX ? true : tex >= 0; }
+
 struct SI {
     bool valid;
     f3 p, n, wi;
@@ -134,9 +144,9 @@ B2_DEV f3 tex_eval(const DScene &sc, int ti, f2 uv_, uint32_t *idx, float *w, Co
 // Reflectance of a BSDF at a vertex.  The texture is fetched once per vertex and reused by eval_pdf / sample (the
 // reference's JIT merges the two identical lookups the same way); every logical evaluation is still counted.
 struct ReflCache { bool have = false; f3 v; };
-template <bool COUNT>
+template <int CLS = CLS_GENERIC, bool COUNT>
 B2_DEV f3 reflectance(const DScene &sc, const DBsdf &b, const SI &si, ReflCache &rc, Counters<COUNT> &cnt) {
-    if (b.tex < 0) return f3(b.refl[0], b.refl[1], b.refl[2]);
+    if (!cls_textured<CLS>(b.tex)) return f3(b.refl[0], b.refl[1], b.refl[2]);
     if (!rc.have) { uint32_t idx[4]; float w[4]; rc.v = tex_eval(sc, b.tex, si.uv, idx, w, cnt); rc.have = true; }
     else cnt.add(C_TEX);
     return rc.v;
@@ -256,8 +266,10 @@ struct Microfacet {
 };
 
 // -------------------------------------------------------------------------------- BSDFs
+template <int CLS = CLS_GENERIC>
 B2_DEV uint32_t bsdf_lobes(const DBsdf &b) {
-    return b.type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : (b.type == B2_BSDF_ROUGHCONDUCTOR ? LOBE_GLOSSY : LOBE_DELTA);
+    const int type = cls_type<CLS>(b.type);
+    return type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : (type == B2_BSDF_ROUGHCONDUCTOR ? LOBE_GLOSSY : LOBE_DELTA);
 }
 B2_DEV f3 fresnel_conductor3(float c, const DBsdf &b) {
     return f3(fresnel_conductor(c, b.eta[0], b.k[0]), fresnel_conductor(c, b.eta[1], b.k[1]), fresnel_conductor(c, b.eta[2], b.k[2]));
@@ -265,16 +277,17 @@ B2_DEV f3 fresnel_conductor3(float c, const DBsdf &b) {
 
 // eval_pdf.  `refl()` yields the (possibly textured) reflectance at si and is invoked exactly where the reference
 // evaluates it; pass a functor returning f3(1) to obtain the linear coefficient d value / d reflectance (PRB adjoint).
-template <class RF>
+template <int CLS = CLS_GENERIC, class RF>
 B2_DEV void bsdf_eval_pdf(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &val, float &pdf) {
     val = f3(0.f); pdf = 0.f;
     if (b.flags & B2_BSDF_FLAG_TWOSIDED) { wo.z = mulsign(wo.z, wi.z); wi.z = fabsf(wi.z); }
     const float ci = wi.z, co = wo.z;
-    if (b.type == B2_BSDF_DIFFUSE) {
+    const int type = cls_type<CLS>(b.type);
+    if (type == B2_BSDF_DIFFUSE) {
         if (!(ci > 0.f && co > 0.f)) return;
         val = refl() * kInvPi * co;
         pdf = kInvPi * co;
-    } else if (b.type == B2_BSDF_ROUGHCONDUCTOR) {
+    } else if (type == B2_BSDF_ROUGHCONDUCTOR) {
         const f3 H = normalize(wo + wi);
         if (!(ci > 0.f && co > 0.f && dot(wi, H) > 0.f && dot(wo, H) > 0.f)) return;
         const Microfacet distr(b.distribution, b.alpha_u, b.alpha_v, b.sample_visible != 0);
@@ -289,21 +302,22 @@ B2_DEV void bsdf_eval_pdf(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &val, floa
 }
 
 // sample.  Same lazy `refl()` convention as bsdf_eval_pdf.
-template <class RF>
+template <int CLS = CLS_GENERIC, class RF>
 B2_DEV void bsdf_sample(const DBsdf &b, f3 wi_in, float s1, f2 s2, RF &&refl, BS &bs, f3 &weight) {
+    const int type = cls_type<CLS>(b.type);
     f3 wi = wi_in;
     bs.wo = f3(); bs.pdf = 0.f; bs.eta = 0.f; bs.type = 0u; weight = f3(0.f);
     const bool two = (b.flags & B2_BSDF_FLAG_TWOSIDED) != 0;
     if (two) wi.z = fabsf(wi.z);
     const float ci = wi.z;
-    if (b.type == B2_BSDF_DIFFUSE) {
+    if (type == B2_BSDF_DIFFUSE) {
         if (ci > 0.f) {
             bs.wo = square_to_cosine_hemisphere(s2);
             bs.pdf = kInvPi * bs.wo.z;
             bs.eta = 1.f; bs.type = LOBE_DIFFUSE;
             if (bs.pdf > 0.f) weight = refl();
         }
-    } else if (b.type == B2_BSDF_ROUGHCONDUCTOR) {
+    } else if (type == B2_BSDF_ROUGHCONDUCTOR) {
         if (ci > 0.f) {
             const Microfacet distr(b.distribution, b.alpha_u, b.alpha_v, b.sample_visible != 0);
             const f3 m = distr.sample(wi, s2, bs.pdf);

@@ -4,9 +4,10 @@
 // (src/render/integrator.cpp:246-360); lanes that finish early idle inside dr.while_loop.  Here the wavefront is
 // explicit: per bounce one TRACE launch (closest rays of the live lanes and the shadow rays of the previous bounce,
 // persistent warps with dynamic ray fetch) and one SHADE launch (path_step<WF>), with the live lanes compacted into the
-// next queue by warp ballot + prefix sums.  Lane state lives in HBM as 16-byte SoA streams between launches.
+// next queue by warp ballot + prefix sums.  Lane state lives in HBM as streams of 32-byte elements between launches.
 #pragma once
 #include "b2_render.cuh"
+#include "b2_math.cuh"
 
 namespace b2 {
 
@@ -14,24 +15,41 @@ struct WfCtl {                       // device-side queue bookkeeping, slot = it
     uint32_t n_closest[4];           // live lanes entering iteration it (queue q[it & 1])
     uint32_t n_shadow[4];            // shadow rays emitted by shade(it)
     uint32_t fetch[4];               // persistent-warp work counter of trace(it)
-    uint32_t pad[4];
+    uint32_t n_class[4][8];          // hits of iteration it per shading class (queues qc[cls])
 };
 
-struct WfState {                     // all arrays have `capacity` entries, indexed by lane slot = lane - chunk_begin
-    uint4 *rng;                      // PCG32 state, inc
-    float4 *ray_o;                   // o.xyz | maxt
-    float4 *ray_d;                   // d.xyz | eta
-    float4 *thr;                     // f.xyz (throughput) | prev_bsdf_pdf
-    float4 *rad;                     // L.xyz | depth (bits 0..23), flags (bits 24..): prev_delta, first, valid_ray
-    float4 *prev;                    // prev_p.xyz | -
-    float2 *pos;                     // splat position
-    float4 *hit;                     // t, u, v | face (bits)
-    uint32_t *hit_mesh;
+struct WfState {                     // `capacity` lane slots (slot = lane - chunk_begin)
+    // Lane state = four streams of 32-byte elements (two 16-byte words each, grouped by which kernel touches them
+    // together).  A 32-byte element is exactly one DRAM/L2 sector, so a lane costs whole sectors however sparse or
+    // permuted the live lanes are (16-byte SoA streams moved 3x the useful bytes in late, class-sorted bounces), while
+    // dense warps still touch only 8 cache lines per request (a 128-byte record per lane touched 32: measured +30 % on
+    // the coherent Cornell / PRB workloads).
+    float4 *p0;                      // ray o.xyz | maxt          , ray d.xyz | eta                     (trace reads)
+    float4 *p1;                      // hit t, u, v | face        , hit mesh, vis bits, splat pos xy    (trace writes)
+    float4 *p2;                      // PCG32 state, inc          , throughput f.xyz | prev_bsdf_pdf
+    float4 *p3;                      // L.xyz | depth + flags     , prev_p.xyz | -
+    float4 *s0;                      // deferred NEE: shadow ray o | maxt , d | tex flag                (trace reads)
+    float4 *s1;                      //               factor a            , factor b   (L <- fma(a, b, L) on arrival)
     float4 *dl;                      // PRB adjoint: dL (adjoint radiance of the lane's splat), xyz
-    uint32_t *vis;                   // PRB: bit k = the emitter sample of bounce k arrived (primal pass -> adjoint replay)
-    float4 *sh_o, *sh_d, *sh_a, *sh_b;   // deferred NEE: shadow ray o|maxt, d|-, factors a, b
+    uint8_t *cls_q;                  // shading class of the hit of queue entry i of the current iteration (trace -> classify)
+    B2_DEV float4 &ray_o(uint32_t s) const { return p0[(size_t) s * 2]; }
+    B2_DEV float4 &ray_d(uint32_t s) const { return p0[(size_t) s * 2 + 1]; }
+    B2_DEV float4 &hit(uint32_t s) const { return p1[(size_t) s * 2]; }
+    B2_DEV uint32_t &hit_mesh(uint32_t s) const { return ((uint32_t *) (p1 + (size_t) s * 2 + 1))[0]; }
+    B2_DEV uint32_t &vis(uint32_t s) const { return ((uint32_t *) (p1 + (size_t) s * 2 + 1))[1]; }
+    B2_DEV float2 &pos(uint32_t s) const { return ((float2 *) (p1 + (size_t) s * 2 + 1))[1]; }
+    B2_DEV uint4 &rng(uint32_t s) const { return ((uint4 *) p2)[(size_t) s * 2]; }
+    B2_DEV float4 &thr(uint32_t s) const { return p2[(size_t) s * 2 + 1]; }
+    B2_DEV float4 &rad(uint32_t s) const { return p3[(size_t) s * 2]; }
+    B2_DEV float4 &prev(uint32_t s) const { return p3[(size_t) s * 2 + 1]; }
+    B2_DEV float4 &sh_o(uint32_t s) const { return s0[(size_t) s * 2]; }
+    B2_DEV float4 &sh_d(uint32_t s) const { return s0[(size_t) s * 2 + 1]; }
+    B2_DEV float4 &sh_a(uint32_t s) const { return s1[(size_t) s * 2]; }
+    B2_DEV float4 &sh_b(uint32_t s) const { return s1[(size_t) s * 2 + 1]; }
     uint32_t *q[2];                  // closest-ray queues (lane slots), double buffered by iteration parity
     uint32_t *q_shadow[2];           // shadow-ray queues, by iteration parity
+    uint32_t *qc[5];                 // closest hits of the current iteration sorted by shading class (CLS_*)
+    uint32_t class_mask;             // classes present in the scene
     WfCtl *ctl;
     uint32_t capacity;
 };

@@ -32,6 +32,7 @@ struct b2_scene {
     uint32_t *unit_counter = nullptr;
     unsigned long long *counters_dev = nullptr;
     float *wfilm = nullptr;                     // weight film of the PRB sample set
+    uint32_t class_mask = 0;                    // shading classes present in the scene (bit = CLS_*)
     void *wf_mem = nullptr; uint32_t wf_capacity = 0; WfState wf{};   // wavefront lane state (grown on demand)
     uint64_t launches = 0;
 
@@ -84,7 +85,10 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
         const b2_mesh &m = desc->meshes[i];
         if (m.bsdf < 0 || (uint32_t) m.bsdf >= desc->n_bsdfs) return fail(-2, "b2_scene_create: mesh references a missing BSDF");
         if ((uint64_t) m.first_face + m.n_faces > desc->n_faces) return fail(-2, "b2_scene_create: mesh face range out of bounds");
-        meshes[i] = DMesh{ m.bsdf, m.emitter, m.flags, m.first_face, m.n_faces, { 0, 0, 0 } };
+        const b2_bsdf &mb = desc->bsdfs[m.bsdf];
+        const uint32_t cls = mb.type == B2_BSDF_DIFFUSE ? (mb.reflectance_tex >= 0 ? 1u : 0u) : (mb.type == B2_BSDF_ROUGHCONDUCTOR ? 2u : 3u);   // CLS_* of b2_shade.cuh
+        s->class_mask |= 1u << cls;
+        meshes[i] = DMesh{ m.bsdf, m.emitter, m.flags, m.first_face, m.n_faces, cls, { 0, 0 } };
         for (uint32_t f = 0; f < m.n_faces; ++f) face_mesh[m.first_face + f] = i;
     }
     for (size_t i = 0; i < (size_t) desc->n_faces * 3; ++i)
@@ -229,6 +233,7 @@ static int wf_reserve(b2_scene *s, uint64_t shard_lanes, uint32_t chunk_lanes, c
         s->wf_capacity = want;
     }
     wf_bind(s->wf, s->wf_mem, want);
+    s->wf.class_mask = s->class_mask;
     return 0;
 }
 

@@ -35,20 +35,20 @@ constexpr int kFetchBatch = 96;        // rays a warp takes from the global coun
 
 // ------------------------------------------------------------------------------------------ state <-> registers
 B2_DEV void wf_store_path(const WfState &st, uint32_t slot, const Path &s, bool with_ray) {
-    st.rng[slot] = make_uint4((uint32_t) s.rng.state, (uint32_t) (s.rng.state >> 32), (uint32_t) s.rng.inc, (uint32_t) (s.rng.inc >> 32));
+    st.rng(slot) = make_uint4((uint32_t) s.rng.state, (uint32_t) (s.rng.state >> 32), (uint32_t) s.rng.inc, (uint32_t) (s.rng.inc >> 32));
     uint32_t bits = (s.depth & WF_DEPTH_MASK) | (s.prev_delta ? WF_FLAG_PREV_DELTA : 0u) | (s.first ? WF_FLAG_FIRST : 0u) | (s.valid_ray ? WF_FLAG_VALID_RAY : 0u);
-    st.rad[slot] = make_float4(s.L.x, s.L.y, s.L.z, __uint_as_float(bits));
+    st.rad(slot) = make_float4(s.L.x, s.L.y, s.L.z, __uint_as_float(bits));
     if (with_ray) {
-        st.ray_o[slot] = make_float4(s.ray.o.x, s.ray.o.y, s.ray.o.z, s.ray.maxt);
-        st.ray_d[slot] = make_float4(s.ray.d.x, s.ray.d.y, s.ray.d.z, s.eta);
-        st.thr[slot] = make_float4(s.f.x, s.f.y, s.f.z, s.prev_pdf);
-        st.prev[slot] = make_float4(s.prev_p.x, s.prev_p.y, s.prev_p.z, 0.f);
+        st.ray_o(slot) = make_float4(s.ray.o.x, s.ray.o.y, s.ray.o.z, s.ray.maxt);
+        st.ray_d(slot) = make_float4(s.ray.d.x, s.ray.d.y, s.ray.d.z, s.eta);
+        st.thr(slot) = make_float4(s.f.x, s.f.y, s.f.z, s.prev_pdf);
+        st.prev(slot) = make_float4(s.prev_p.x, s.prev_p.y, s.prev_p.z, 0.f);
     }
 }
 B2_DEV void wf_load_path(const WfState &st, uint32_t slot, Path &s) {
-    const uint4 r = st.rng[slot];
+    const uint4 r = st.rng(slot);
     s.rng.state = (uint64_t) r.x | ((uint64_t) r.y << 32); s.rng.inc = (uint64_t) r.z | ((uint64_t) r.w << 32);
-    const float4 o = st.ray_o[slot], d = st.ray_d[slot], t = st.thr[slot], l = st.rad[slot], pv = st.prev[slot];
+    const float4 o = st.ray_o(slot), d = st.ray_d(slot), t = st.thr(slot), l = st.rad(slot), pv = st.prev(slot);
     s.ray.o = f3(o.x, o.y, o.z); s.ray.maxt = o.w; s.ray.d = f3(d.x, d.y, d.z); s.eta = d.w;
     s.f = f3(t.x, t.y, t.z); s.prev_pdf = t.w; s.L = f3(l.x, l.y, l.z);
     const uint32_t bits = __float_as_uint(l.w);
@@ -79,18 +79,19 @@ __global__ void __launch_bounds__(256) k_wf_generate(const __grid_constant__ Ren
     if (blockIdx.x == 0 && threadIdx.x < 4) {       // nothing else is in flight: reset the queue bookkeeping
         const uint32_t k = threadIdx.x;
         st.ctl->n_closest[k] = (k == (w.it & 3u)) ? w.n : 0u; st.ctl->n_shadow[k] = 0u; st.ctl->fetch[k] = 0u;
+        for (int c = 0; c < 8; ++c) st.ctl->n_class[k][c] = 0u;
     }
     uint32_t *q = st.q[w.it & 1u];
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < w.n; i += gridDim.x * blockDim.x) {
         Path s;
         s.lane = (uint32_t) (w.chunk_begin + i); s.pass = w.pass; s.adjoint = false; s.dL = f3(0.f);
         if (w.pass == 0) s.rng.seed_lane(p.seed, s.lane);
-        else { const uint4 r = st.rng[i]; s.rng.state = (uint64_t) r.x | ((uint64_t) r.y << 32); s.rng.inc = (uint64_t) r.z | ((uint64_t) r.w << 32); }
+        else { const uint4 r = st.rng(i); s.rng.state = (uint64_t) r.x | ((uint64_t) r.y << 32); s.rng.inc = (uint64_t) r.z | ((uint64_t) r.w << 32); }
         start_path<V>(p, s);
         wf_store_path(st, i, s, true);
-        st.pos[i] = make_float2(s.pos.x, s.pos.y);
-        st.hit[i] = make_float4(s.ray.maxt, 0.f, 0.f, __uint_as_float(0xffffffffu));     // a miss, unless trace(it) overwrites it
-        st.hit_mesh[i] = 0u; st.vis[i] = 0u;
+        st.pos(i) = make_float2(s.pos.x, s.pos.y);
+        st.hit(i) = make_float4(s.ray.maxt, 0.f, 0.f, __uint_as_float(0xffffffffu));     // a miss, unless trace(it) overwrites it
+        st.hit_mesh(i) = 0xffffffffu; st.vis(i) = 0u;
         q[i] = i;
     }
 }
@@ -98,7 +99,7 @@ __global__ void __launch_bounds__(256) k_wf_generate(const __grid_constant__ Ren
 // ------------------------------------------------------------------------------------------ trace
 struct TraceRay {
     f3 o, d; float idx, idy, idz, maxt;
-    uint32_t octinv, slot; bool any, tex;
+    uint32_t octinv, slot, qi; bool any, tex;
     float t, u, v; uint32_t face, mesh; bool found;
     uint2 ng, tg; int sp, nq;
 };
@@ -143,9 +144,9 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
                 if (nb == 0u) exhausted = true;
             }
             if (my != 0xffffffffu) {
-                r.any = my >= nc;
+                r.any = my >= nc; r.qi = my;
                 r.slot = r.any ? qs[my - nc] : qc[my];
-                const float4 o = r.any ? st.sh_o[r.slot] : st.ray_o[r.slot], d = r.any ? st.sh_d[r.slot] : st.ray_d[r.slot];
+                const float4 o = r.any ? st.sh_o(r.slot) : st.ray_o(r.slot), d = r.any ? st.sh_d(r.slot) : st.ray_d(r.slot);
                 r.o = f3(o.x, o.y, o.z); r.d = f3(d.x, d.y, d.z); r.maxt = o.w; r.tex = r.any && d.w != 0.f;
                 const float tiny = 1e-30f;
                 r.idx = 1.f / (fabsf(r.d.x) > tiny ? r.d.x : copysignf(tiny, r.d.x));
@@ -259,14 +260,15 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
             if (r.any) {
                 if (!r.found) {         // the emitter sample arrives: L <- fma(a, b, L)
                     if (r.tex) cnt.add(C_TEX);
-                    if (w.vis_bit != 0xffffffffu) st.vis[r.slot] |= 1u << w.vis_bit;
-                    const float4 a = st.sh_a[r.slot], b = st.sh_b[r.slot]; float4 L = st.rad[r.slot];
+                    if (w.vis_bit != 0xffffffffu) st.vis(r.slot) |= 1u << w.vis_bit;
+                    const float4 a = st.sh_a(r.slot), b = st.sh_b(r.slot); float4 L = st.rad(r.slot);
                     L.x = fma_(a.x, b.x, L.x); L.y = fma_(a.y, b.y, L.y); L.z = fma_(a.z, b.z, L.z);
-                    st.rad[r.slot] = L;
+                    st.rad(r.slot) = L;
                 }
             } else {
-                st.hit[r.slot] = make_float4(r.t, r.u, r.v, __uint_as_float(r.face));
-                st.hit_mesh[r.slot] = r.mesh;
+                st.hit(r.slot) = make_float4(r.t, r.u, r.v, __uint_as_float(r.face));
+                st.hit_mesh(r.slot) = r.found ? r.mesh : 0xffffffffu;
+                st.cls_q[r.qi] = r.found ? (uint8_t) __ldg(&sc.meshes[r.mesh].cls) : (uint8_t) CLS_MISS;   // for classify(it)
             }
             have = false;
         }
@@ -275,17 +277,58 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
 }
 
 // ------------------------------------------------------------------------------------------ shade
-template <int V, bool COUNT, bool ADJ = false>
-__global__ void __launch_bounds__(256, B2_SHADE_MINBLOCKS) k_wf_shade(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
+// ------------------------------------------------------------------------------------------ classify
+// Sorts the closest hits of iteration `it` by shading class (miss / diffuse / textured diffuse / rough conductor /
+// dielectric) into per-class queues, so that every warp of a shade kernel runs one BSDF and the kernels can be
+// specialised: block-wide counting sort step = five ballots, one atomic per block and class.
+__global__ void __launch_bounds__(256) k_wf_classify(const __grid_constant__ WfLaunch w) {
+    __shared__ uint32_t s_cnt[CLS_COUNT][8], s_base[CLS_COUNT];
+    const WfState &st = w.st;
+    const uint32_t it = w.it, n = st.ctl->n_closest[it & 3u];
+    const uint32_t *qin = st.q[it & 1u];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (blockIdx.x == 0 && tid < 8) {
+        const uint32_t z = (it + 2u) & 3u;
+        if (tid == 0) { st.ctl->n_closest[z] = 0u; st.ctl->n_shadow[z] = 0u; st.ctl->fetch[z] = 0u; }
+        st.ctl->n_class[z][tid] = 0u;
+    }
+    for (uint32_t base = blockIdx.x * 256u; base < n; base += gridDim.x * 256u) {
+        const uint32_t i = base + tid;
+        uint32_t slot = 0; int cls = -1;
+        if (i < n) { slot = qin[i]; cls = (int) st.cls_q[i]; }       // class by queue position, written by trace(it)
+        uint32_t mine = 0;
+#pragma unroll
+        for (int k = 0; k < CLS_COUNT; ++k) {
+            const uint32_t m = __ballot_sync(0xffffffffu, cls == k);
+            if (lane == 0) s_cnt[k][warp] = __popc(m);
+            if (cls == k) mine = m;
+        }
+        __syncthreads();
+        if (tid < CLS_COUNT) {
+            uint32_t tot = 0;
+            for (int k = 0; k < 8; ++k) { const uint32_t c = s_cnt[tid][k]; s_cnt[tid][k] = tot; tot += c; }
+            s_base[tid] = tot ? atomicAdd(&st.ctl->n_class[it & 3u][tid], tot) : 0u;
+        }
+        __syncthreads();
+        if (cls >= 0) st.qc[cls][s_base[cls] + s_cnt[cls][warp] + __popc(mine & ((1u << lane) - 1u))] = slot;
+        __syncthreads();
+    }
+}
+
+// SORTED: the input is the class queue qc[CLS] filled by k_wf_classify; otherwise the whole live queue (CLS then only
+// states what every BSDF of the scene is -- single-class scenes such as the Cornell box skip the sort).
+template <int V, bool COUNT, bool ADJ = false, int CLS = CLS_GENERIC, bool SORTED = (CLS != CLS_GENERIC)>
+__global__ void __launch_bounds__(256, (CLS == CLS_DIFFUSE || CLS == CLS_MISS) ? 4 : B2_SHADE_MINBLOCKS) k_wf_shade(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
     __shared__ uint32_t s_cnt[2][8], s_base[2];
     __shared__ float s_gconst[kMaxGradTargets * 3];     // adjoint: per-block sums of the constant-albedo gradients
     const WfState &st = w.st;
-    const uint32_t it = w.it, n = st.ctl->n_closest[it & 3u];
-    const uint32_t *qin = st.q[it & 1u]; uint32_t *qout = st.q[(it + 1u) & 1u], *qsh = st.q_shadow[0];
+    const uint32_t it = w.it, n = !SORTED ? st.ctl->n_closest[it & 3u] : st.ctl->n_class[it & 3u][SORTED ? CLS : 0];
+    const uint32_t *qin = !SORTED ? st.q[it & 1u] : st.qc[SORTED ? CLS : 0];
+    uint32_t *qout = st.q[(it + 1u) & 1u], *qsh = st.q_shadow[0];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     Counters<COUNT> cnt; GradSink gs{ s_gconst };
     if (ADJ) { if (tid < kMaxGradTargets * 3) s_gconst[tid] = 0.f; __syncthreads(); }
-    if (blockIdx.x == 0 && tid == 0) { const uint32_t z = (it + 2u) & 3u; st.ctl->n_closest[z] = 0u; st.ctl->n_shadow[z] = 0u; st.ctl->fetch[z] = 0u; }
+    if (!SORTED && blockIdx.x == 0 && tid == 0) { const uint32_t z = (it + 2u) & 3u; st.ctl->n_closest[z] = 0u; st.ctl->n_shadow[z] = 0u; st.ctl->fetch[z] = 0u; }
 
     for (uint32_t base = blockIdx.x * 256u; base < n; base += gridDim.x * 256u) {
         const uint32_t i = base + tid;
@@ -293,25 +336,26 @@ __global__ void __launch_bounds__(256, B2_SHADE_MINBLOCKS) k_wf_shade(const __gr
         if (i < n) {
             slot = qin[i];
             Path s; wf_load_path(st, slot, s);
-            const float4 hh = st.hit[slot];
-            Hit h; h.t = hh.x; h.u = hh.y; h.v = hh.z; h.face = __float_as_uint(hh.w); h.mesh = st.hit_mesh[slot];
+            const float4 hh = st.hit(slot);
+            Hit h; h.t = hh.x; h.u = hh.y; h.v = hh.z; h.face = __float_as_uint(hh.w); h.mesh = st.hit_mesh(slot);
             ShadowRec so; so.valid = false; so.tex = false; so.vis = false; so.a = f3(0.f); so.b = f3(0.f);
             if (ADJ) {
                 const float4 g = st.dl[slot]; s.dL = f3(g.x, g.y, g.z); s.adjoint = true;
-                so.vis = ((st.vis[slot] >> w.vis_bit) & 1u) != 0u;
+                so.vis = ((st.vis(slot) >> w.vis_bit) & 1u) != 0u;
             }
-            alive = path_step<V, ADJ, COUNT, true>(p, s, gs, cnt, &h, &so);
+            alive = path_step<V, ADJ, COUNT, true, CLS>(p, s, gs, cnt, &h, &so);
             if (ADJ && !alive) cnt.add(C_SAMPLES);
             wf_store_path(st, slot, s, alive);
             shadow = so.valid;
             if (shadow) {
-                st.sh_o[slot] = make_float4(so.ray.o.x, so.ray.o.y, so.ray.o.z, so.ray.maxt);
-                st.sh_d[slot] = make_float4(so.ray.d.x, so.ray.d.y, so.ray.d.z, so.tex ? 1.f : 0.f);
-                st.sh_a[slot] = make_float4(so.a.x, so.a.y, so.a.z, 0.f);
-                st.sh_b[slot] = make_float4(so.b.x, so.b.y, so.b.z, 0.f);
+                st.sh_o(slot) = make_float4(so.ray.o.x, so.ray.o.y, so.ray.o.z, so.ray.maxt);
+                st.sh_d(slot) = make_float4(so.ray.d.x, so.ray.d.y, so.ray.d.z, so.tex ? 1.f : 0.f);
+                st.sh_a(slot) = make_float4(so.a.x, so.a.y, so.a.z, 0.f);
+                st.sh_b(slot) = make_float4(so.b.x, so.b.y, so.b.z, 0.f);
             }
         }
-        // ---- compaction: warp ballot -> per-warp counts -> one atomic per block and queue
+        // ---- compaction: warp ballot -> per-warp counts -> one atomic per block and queue (keeps the queue in lane
+        // order within a block, which the next trace launch rewards with coherent rays; per-warp atomics measured 10 % slower)
         const uint32_t ma = __ballot_sync(0xffffffffu, alive), ms = __ballot_sync(0xffffffffu, shadow);
         if (lane == 0) { s_cnt[0][warp] = __popc(ma); s_cnt[1][warp] = __popc(ms); }
         __syncthreads();
@@ -341,12 +385,13 @@ __global__ void __launch_bounds__(256) k_wf_generate_adj(const __grid_constant__
     if (blockIdx.x == 0 && threadIdx.x < 4) {
         const uint32_t k = threadIdx.x;
         st.ctl->n_closest[k] = (k == (w.it & 3u)) ? w.n : 0u; st.ctl->n_shadow[k] = 0u; st.ctl->fetch[k] = 0u;
+        for (int c = 0; c < 8; ++c) st.ctl->n_class[k][c] = 0u;
     }
     uint32_t *q = st.q[w.it & 1u];
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < w.n; i += gridDim.x * blockDim.x) {
         Path s;
         s.lane = (uint32_t) (w.chunk_begin + i); s.pass = 0; s.adjoint = true;
-        const float4 l = st.rad[i];
+        const float4 l = st.rad(i);
         s.rng.seed_lane(p.seed, s.lane);
         start_path<B2_VARIANT_PRB>(p, s);
         s.L = f3(l.x, l.y, l.z);
@@ -359,8 +404,8 @@ __global__ void __launch_bounds__(256) k_wf_generate_adj(const __grid_constant__
         });
         wf_store_path(st, i, s, true);
         st.dl[i] = make_float4(dL.x, dL.y, dL.z, 0.f);
-        st.hit[i] = make_float4(s.ray.maxt, 0.f, 0.f, __uint_as_float(0xffffffffu));
-        st.hit_mesh[i] = 0u;
+        st.hit(i) = make_float4(s.ray.maxt, 0.f, 0.f, __uint_as_float(0xffffffffu));
+        st.hit_mesh(i) = 0xffffffffu;
         q[i] = i;
     }
 }
@@ -401,8 +446,8 @@ __global__ void __launch_bounds__(256) k_wf_splat(const __grid_constant__ Render
                     if (sn.rfilter == B2_RFILTER_BOX) ps = f2{ (float) px, (float) py };
                 } else {
                     const uint32_t slot = (uint32_t) (lane_lo + i - c_lo);
-                    const float2 q = st.pos[slot]; ps = f2{ q.x, q.y };
-                    const float4 l = st.rad[slot]; L = f3(l.x, l.y, l.z);
+                    const float2 q = st.pos(slot); ps = f2{ q.x, q.y };
+                    const float4 l = st.rad(slot); L = f3(l.x, l.y, l.z);
                     if (V == B2_VARIANT_PATH_MIS && !(__float_as_uint(l.w) & WF_FLAG_VALID_RAY)) L = f3(0.f);
                 }
             }
@@ -445,20 +490,19 @@ static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 size_t wf_state_bytes(uint32_t cap) {
     const size_t c = cap;
-    return align_up(c * 16, 256) * 12 + align_up(c * 8, 256) + align_up(c * 4, 256) * 5 + 256;
+    return align_up(c * 32, 256) * 6 + align_up(c * 16, 256) + align_up(c, 256) + align_up(c * 4, 256) * (3 + CLS_COUNT) + 256;
 }
 
 void wf_bind(WfState &st, void *base, uint32_t cap) {
     char *q = (char *) base; const size_t c = cap;
     auto take = [&](size_t bytes) { void *r = q; q += align_up(bytes, 256); return r; };
     st.ctl = (WfCtl *) take(256);
-    st.rng = (uint4 *) take(c * 16); st.ray_o = (float4 *) take(c * 16); st.ray_d = (float4 *) take(c * 16); st.thr = (float4 *) take(c * 16);
-    st.rad = (float4 *) take(c * 16); st.prev = (float4 *) take(c * 16); st.hit = (float4 *) take(c * 16);
-    st.sh_o = (float4 *) take(c * 16); st.sh_d = (float4 *) take(c * 16); st.sh_a = (float4 *) take(c * 16); st.sh_b = (float4 *) take(c * 16);
-    st.dl = (float4 *) take(c * 16); st.vis = (uint32_t *) take(c * 4);
-    st.pos = (float2 *) take(c * 8);
-    st.hit_mesh = (uint32_t *) take(c * 4); st.q[0] = (uint32_t *) take(c * 4); st.q[1] = (uint32_t *) take(c * 4); st.q_shadow[0] = (uint32_t *) take(c * 4);
+    st.p0 = (float4 *) take(c * 32); st.p1 = (float4 *) take(c * 32); st.p2 = (float4 *) take(c * 32); st.p3 = (float4 *) take(c * 32);
+    st.s0 = (float4 *) take(c * 32); st.s1 = (float4 *) take(c * 32);
+    st.dl = (float4 *) take(c * 16); st.cls_q = (uint8_t *) take(c);
+    st.q[0] = (uint32_t *) take(c * 4); st.q[1] = (uint32_t *) take(c * 4); st.q_shadow[0] = (uint32_t *) take(c * 4);
     st.q_shadow[1] = st.q_shadow[0];
+    for (int k = 0; k < CLS_COUNT; ++k) st.qc[k] = (uint32_t *) take(c * 4);
     st.capacity = cap;
 }
 
@@ -467,6 +511,7 @@ static int env_int(const char *name, int def) { const char *v = getenv(name); re
 static const uint32_t tune_slice = (uint32_t) env_int("B2_TRACE_SLICE", B2_TRACE_SLICE);
 static const uint32_t tune_tri = (uint32_t) env_int("B2_TRI_THRESH", 8);
 static const int tune_trace_blocks = getenv("B2_TRACE_BLOCKS") ? atoi(getenv("B2_TRACE_BLOCKS")) : 0;
+static const int tune_sort = getenv("B2_SHADE_SORT") ? atoi(getenv("B2_SHADE_SORT")) : -1;   // 0/1 force, -1 = by scene content
 
 template <int V, bool COUNT>
 static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {
@@ -497,7 +542,19 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
                 if (bounded && k >= n_iter) break;
                 w.it = it;
                 if (!(k == 0 && skip_first_trace)) { k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); launches++; }
-                k_wf_shade<V, COUNT><<<g_shade, 256, 0, stream>>>(p, w); launches++;
+                const uint32_t cmask = st.class_mask;
+                const bool sort = tune_sort >= 0 ? tune_sort != 0     // default: sort when the BSDFs differ enough to diverge
+                                                 : (__builtin_popcount(cmask) >= 2 && (cmask & ((1u << CLS_CONDUCTOR) | (1u << CLS_DIELECTRIC))) != 0);
+                if (!sort && cmask == (1u << CLS_DIFFUSE)) { k_wf_shade<V, COUNT, false, CLS_DIFFUSE, false><<<g_shade, 256, 0, stream>>>(p, w); launches++; }
+                else if (sort) {
+                    k_wf_classify<<<g_shade, 256, 0, stream>>>(w); launches++;
+                    const uint32_t cm = st.class_mask;
+                    if (cm & (1u << CLS_DIFFUSE)) { k_wf_shade<V, COUNT, false, CLS_DIFFUSE><<<g_shade, 256, 0, stream>>>(p, w); launches++; }
+                    if (cm & (1u << CLS_DIFFUSE_TEX)) { k_wf_shade<V, COUNT, false, CLS_DIFFUSE_TEX><<<g_shade, 256, 0, stream>>>(p, w); launches++; }
+                    if (cm & (1u << CLS_CONDUCTOR)) { k_wf_shade<V, COUNT, false, CLS_CONDUCTOR><<<g_shade, 256, 0, stream>>>(p, w); launches++; }
+                    if (cm & (1u << CLS_DIELECTRIC)) { k_wf_shade<V, COUNT, false, CLS_DIELECTRIC><<<g_shade, 256, 0, stream>>>(p, w); launches++; }
+                    k_wf_shade<V, COUNT, false, CLS_MISS><<<g_shade, 256, 0, stream>>>(p, w); launches++;
+                } else { k_wf_shade<V, COUNT><<<g_shade, 256, 0, stream>>>(p, w); launches++; }
                 ++it;
                 if (!bounded && (k & 3u) == 3u) {       // unbounded depth: Russian roulette ends the paths; poll the live count
                     uint32_t live = 0;
