@@ -25,6 +25,7 @@
  *                             / PRBIntegrator.sample primal (prb.py:63-265)
  *   b2_develop             <- HDRFilm::develop (mi3/src/films/hdrfilm.cpp:304-405)
  *   b2_render_backward     <- RBIntegrator.render_backward (mi3/src/python/python/ad/integrators/common.py:623-781)
+ *   b2_kernel_times        <- dr.kernel_history() as printed by path.py:332-351
  *   b2_trace               <- Scene::ray_intersect_preliminary / ray_test (mi3/src/render/scene.cpp:191-235)
  */
 #ifndef B2PATH_H
@@ -211,6 +212,12 @@ int  b2_trace(b2_scene *scene, const float *rays_dev, uint64_t n, int any_hit, b
 /* host-buffer convenience entry points (what a reference-side binding with host arrays calls):
    upload/download happen inside; film_rgbw_host is accumulated into */
 int  b2_render_host(b2_scene *scene, const b2_render_args *args, float *film_rgbw_host, float *image_rgb_host, b2_counters *counters);
+/* Kernel history (the reference prints dr.kernel_history() with per-kernel execution times, path.py:332-351):
+   when enabled, CUDA events bracket every wavefront launch; b2_kernel_times synchronises the device and returns the
+   milliseconds and launch counts accumulated since the previous call, per kernel kind
+   [0] trace  [1] shade (+ classify)  [2] splat  [3] other (ray generation). */
+int  b2_set_kernel_timing(b2_scene *scene, int enabled);
+int  b2_kernel_times(b2_scene *scene, double ms[4], uint64_t launches[4]);
 const char *b2_last_error(void);
 int  b2_abi_version(void);
 

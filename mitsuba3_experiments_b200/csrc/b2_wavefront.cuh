@@ -8,6 +8,7 @@
 #pragma once
 #include "b2_render.cuh"
 #include "b2_math.cuh"
+#include <vector>
 
 namespace b2 {
 
@@ -66,6 +67,12 @@ struct WfLaunch {
     uint32_t vis_bit;                // trace: bit to set in vis[] for arriving shadow rays; shade<ADJ>: bit to read; ~0u = off
     uint32_t tri_thresh;             // trace: lanes with pending leaf triangles that trigger a triangle step
 };
+
+// per-kernel-kind timing (host side)
+enum { WF_K_TRACE = 0, WF_K_SHADE = 1, WF_K_SPLAT = 2, WF_K_OTHER = 3, WF_K_COUNT = 4 };
+struct WfTiming { std::vector<cudaEvent_t> ev; std::vector<int> kind; size_t used = 0; };
+void wf_set_timing(WfTiming *t);          // nullptr = off (default)
+void wf_collect_timing(WfTiming &t, double ms[WF_K_COUNT], uint64_t n[WF_K_COUNT]);   // after the stream has been synchronised
 
 // host entry points (wavefront.cu)
 size_t wf_state_bytes(uint32_t capacity);

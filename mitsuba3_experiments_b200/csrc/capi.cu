@@ -32,6 +32,7 @@ struct b2_scene {
     uint32_t *unit_counter = nullptr;
     unsigned long long *counters_dev = nullptr;
     float *wfilm = nullptr;                     // weight film of the PRB sample set
+    WfTiming timing; bool timing_on = false;     // kernel history (b2_kernel_times)
     uint32_t class_mask = 0;                    // shading classes present in the scene (bit = CLS_*)
     void *wf_mem = nullptr; uint32_t wf_capacity = 0; WfState wf{};   // wavefront lane state (grown on demand)
     uint64_t launches = 0;
@@ -42,7 +43,7 @@ struct b2_scene {
         if (n && host) e = cudaMemcpy(q, host, n * sizeof(T), cudaMemcpyHostToDevice);
         return e;
     }
-    ~b2_scene() { for (void *q : allocs) cudaFree(q); if (wf_mem) cudaFree(wf_mem); bvh_free(bvh); }
+    ~b2_scene() { for (cudaEvent_t e : timing.ev) cudaEventDestroy(e); for (void *q : allocs) cudaFree(q); if (wf_mem) cudaFree(wf_mem); bvh_free(bvh); }
 };
 
 extern "C" {
@@ -310,7 +311,9 @@ int b2_render(b2_scene *s, const b2_render_args *a, float *film, uintptr_t strea
         // wavefront: lane state of one chunk lives in HBM (188 B per lane); default chunk = 16 Mi lanes (3.2 GB)
         if (int rc = wf_reserve(s, p.lane_end - p.lane_begin, a->chunk_lanes, st)) return rc;
         const char *err = nullptr;
+        wf_set_timing(s->timing_on ? &s->timing : nullptr);
         const long n = wf_render(a->variant, count, p, s->wf, s->ctx->sm_count, st, &err);
+        wf_set_timing(nullptr);
         if (n < 0) return fail(-11, err ? err : "wavefront render failed");
         launches += (uint64_t) n;
     } else if (p.unit_end > p.unit_begin) { launch_render(a->variant, MODE_RENDER, count, p, blocks, smem, st); launches++; }
@@ -381,7 +384,9 @@ int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_i
             if (p.lane_end > p.lane_begin) {
                 if (int rc = wf_reserve(s, p.lane_end - p.lane_begin, a->chunk_lanes, st)) return rc;
                 const char *err = nullptr;
+                wf_set_timing(s->timing_on ? &s->timing : nullptr);
                 const long n = wf_render_backward(count, p, s->wf, s->ctx->sm_count, st, &err);
+                wf_set_timing(nullptr);
                 if (n < 0) return fail(-11, err ? err : "wavefront render_backward failed");
                 launches += (uint64_t) n;
             }
@@ -395,6 +400,20 @@ int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_i
         export_counters(h, launches, counters);
     }
     s->launches += launches;
+    return 0;
+}
+
+int b2_set_kernel_timing(b2_scene *s, int enabled) {
+    if (!s) return fail(-1, "b2_set_kernel_timing: null argument");
+    s->timing_on = enabled != 0;
+    return 0;
+}
+
+int b2_kernel_times(b2_scene *s, double ms[4], uint64_t launches[4]) {
+    if (!s || !ms || !launches) return fail(-1, "b2_kernel_times: null argument");
+    CUDA_OK(cudaSetDevice(s->ctx->device));
+    CUDA_OK(cudaDeviceSynchronize());
+    wf_collect_timing(s->timing, ms, launches);
     return 0;
 }
 

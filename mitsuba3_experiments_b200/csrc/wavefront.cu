@@ -506,6 +506,25 @@ void wf_bind(WfState &st, void *base, uint32_t cap) {
     st.capacity = cap;
 }
 
+// optional per-kernel-kind device timing (bench.py's roofline): CUDA events around every launch, summed after the render
+static thread_local WfTiming *g_tm = nullptr;
+void wf_set_timing(WfTiming *t) { g_tm = t; }
+static void tm_begin(int kind, cudaStream_t st) {
+    WfTiming *t = g_tm; if (!t) return;
+    if (t->used + 2 > t->ev.size()) { cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b); t->ev.push_back(a); t->ev.push_back(b); }
+    t->kind.push_back(kind);
+    cudaEventRecord(t->ev[t->used], st);
+}
+static void tm_end(cudaStream_t st) { WfTiming *t = g_tm; if (!t) return; cudaEventRecord(t->ev[t->used + 1], st); t->used += 2; }
+void wf_collect_timing(WfTiming &t, double ms[WF_K_COUNT], uint64_t n[WF_K_COUNT]) {
+    for (int k = 0; k < WF_K_COUNT; ++k) { ms[k] = 0.0; n[k] = 0; }
+    for (size_t i = 0; i < t.kind.size(); ++i) {
+        float e = 0.f; cudaEventElapsedTime(&e, t.ev[2 * i], t.ev[2 * i + 1]);
+        ms[t.kind[i]] += e; n[t.kind[i]]++;
+    }
+    t.kind.clear(); t.used = 0;
+}
+
 // tuning knobs (environment overrides are for sweeps on the GPU box; the defaults are the measured optimum)
 static int env_int(const char *name, int def) { const char *v = getenv(name); return v ? std::max(1, atoi(v)) : def; }
 static const uint32_t tune_slice = (uint32_t) env_int("B2_TRACE_SLICE", B2_TRACE_SLICE);
@@ -537,24 +556,24 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
         const int g_trace = (tune_trace_blocks > 0 ? std::min(tune_trace_blocks, occ_trace) : occ_trace) * sm_count, g_shade = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_shade * sm_count);
         for (uint32_t pass = 0; pass < p.n_passes; ++pass) {
             w.pass = pass; w.it = it;
-            k_wf_generate<V><<<g_gen, 256, 0, stream>>>(p, w); launches++;
+            tm_begin(WF_K_OTHER, stream); k_wf_generate<V><<<g_gen, 256, 0, stream>>>(p, w); tm_end(stream); launches++;
             for (uint32_t k = 0;; ++k) {
                 if (bounded && k >= n_iter) break;
                 w.it = it;
-                if (!(k == 0 && skip_first_trace)) { k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); launches++; }
+                if (!(k == 0 && skip_first_trace)) { tm_begin(WF_K_TRACE, stream); k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); tm_end(stream); launches++; }
                 const uint32_t cmask = st.class_mask;
                 const bool sort = tune_sort >= 0 ? tune_sort != 0     // default: sort when the BSDFs differ enough to diverge
                                                  : (__builtin_popcount(cmask) >= 2 && (cmask & ((1u << CLS_CONDUCTOR) | (1u << CLS_DIELECTRIC))) != 0);
-                if (!sort && cmask == (1u << CLS_DIFFUSE)) { k_wf_shade<V, COUNT, false, CLS_DIFFUSE, false><<<g_shade, 256, 0, stream>>>(p, w); launches++; }
+                if (!sort && cmask == (1u << CLS_DIFFUSE)) { tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false, CLS_DIFFUSE, false><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++; }
                 else if (sort) {
-                    k_wf_classify<<<g_shade, 256, 0, stream>>>(w); launches++;
+                    tm_begin(WF_K_SHADE, stream); k_wf_classify<<<g_shade, 256, 0, stream>>>(w); tm_end(stream); launches++;
                     const uint32_t cm = st.class_mask;
-                    if (cm & (1u << CLS_DIFFUSE)) { k_wf_shade<V, COUNT, false, CLS_DIFFUSE><<<g_shade, 256, 0, stream>>>(p, w); launches++; }
-                    if (cm & (1u << CLS_DIFFUSE_TEX)) { k_wf_shade<V, COUNT, false, CLS_DIFFUSE_TEX><<<g_shade, 256, 0, stream>>>(p, w); launches++; }
-                    if (cm & (1u << CLS_CONDUCTOR)) { k_wf_shade<V, COUNT, false, CLS_CONDUCTOR><<<g_shade, 256, 0, stream>>>(p, w); launches++; }
-                    if (cm & (1u << CLS_DIELECTRIC)) { k_wf_shade<V, COUNT, false, CLS_DIELECTRIC><<<g_shade, 256, 0, stream>>>(p, w); launches++; }
-                    k_wf_shade<V, COUNT, false, CLS_MISS><<<g_shade, 256, 0, stream>>>(p, w); launches++;
-                } else { k_wf_shade<V, COUNT><<<g_shade, 256, 0, stream>>>(p, w); launches++; }
+                    if (cm & (1u << CLS_DIFFUSE)) { tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false, CLS_DIFFUSE><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++; }
+                    if (cm & (1u << CLS_DIFFUSE_TEX)) { tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false, CLS_DIFFUSE_TEX><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++; }
+                    if (cm & (1u << CLS_CONDUCTOR)) { tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false, CLS_CONDUCTOR><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++; }
+                    if (cm & (1u << CLS_DIELECTRIC)) { tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false, CLS_DIELECTRIC><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++; }
+                    tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false, CLS_MISS><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++;
+                } else { tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++; }
                 ++it;
                 if (!bounded && (k & 3u) == 3u) {       // unbounded depth: Russian roulette ends the paths; poll the live count
                     uint32_t live = 0;
@@ -564,7 +583,7 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
                 }
             }
             w.it = it;                                  // shadow rays of the last bounce
-            k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); launches++;
+            tm_begin(WF_K_TRACE, stream); k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); tm_end(stream); launches++;
             ++it;
             // splat this chunk: units covering its pixels
             RenderParams ps = p;
@@ -573,7 +592,7 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
             ps.unit_end = (uint32_t) ((pix1 / W) * p.units_per_row + (pix1 % W) / P) + 1;
             cudaMemsetAsync(p.unit_counter, 0, 4, stream);
             const int g_splat = (int) std::min<uint32_t>(ps.unit_end - ps.unit_begin, (uint32_t) (occ_splat * sm_count));
-            k_wf_splat<V, COUNT, false><<<g_splat, 256, smem_splat, stream>>>(ps, w); launches++;
+            tm_begin(WF_K_SPLAT, stream); k_wf_splat<V, COUNT, false><<<g_splat, 256, smem_splat, stream>>>(ps, w); tm_end(stream); launches++;
         }
     }
     if (cudaGetLastError() != cudaSuccess) { *err = "wavefront: kernel launch failed"; return -1; }
@@ -601,24 +620,24 @@ static long wf_render_backward_t(RenderParams p, WfState &st, int sm_count, cuda
         const int g_adj = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_adj * sm_count);
         // ---- primal pass (common.py:750-760): L per lane, and the visibility bit of every emitter sample
         w.it = it; w.vis_bit = 0xffffffffu;
-        k_wf_generate<V><<<g_gen, 256, 0, stream>>>(p, w); launches++;
+        tm_begin(WF_K_OTHER, stream); k_wf_generate<V><<<g_gen, 256, 0, stream>>>(p, w); tm_end(stream); launches++;
         for (uint32_t k = 0; k < n_iter; ++k) {
             w.it = it; w.vis_bit = k ? k - 1u : 0xffffffffu;
-            k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); launches++;
-            k_wf_shade<V, COUNT, false><<<g_shade, 256, 0, stream>>>(p, w); launches++;
+            tm_begin(WF_K_TRACE, stream); k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); tm_end(stream); launches++;
+            tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++;
             ++it;
         }
         w.it = it; w.vis_bit = n_iter - 1u;
-        k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); launches++;
+        tm_begin(WF_K_TRACE, stream); k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); tm_end(stream); launches++;
         ++it;
         // ---- adjoint pass (common.py:763-773): replay of the identical stream, closest-hit rays only
         w.it = it; w.vis_bit = 0xffffffffu;
-        k_wf_generate_adj<<<g_gen, 256, 0, stream>>>(p, w); launches++;
+        tm_begin(WF_K_OTHER, stream); k_wf_generate_adj<<<g_gen, 256, 0, stream>>>(p, w); tm_end(stream); launches++;
         for (uint32_t k = 0; k < n_iter; ++k) {
             w.it = it; w.vis_bit = 0xffffffffu;
-            k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); launches++;
+            tm_begin(WF_K_TRACE, stream); k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); tm_end(stream); launches++;
             w.vis_bit = k;
-            k_wf_shade<V, COUNT, true><<<g_adj, 256, 0, stream>>>(p, w); launches++;
+            tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, true><<<g_adj, 256, 0, stream>>>(p, w); tm_end(stream); launches++;
             ++it;
         }
     }

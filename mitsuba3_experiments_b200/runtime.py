@@ -149,6 +149,16 @@ class DeviceScene:
         out = hits.cpu().numpy()
         return out.view(np.dtype([("t", "f4"), ("u", "f4"), ("v", "f4"), ("prim", "u4")])).reshape(-1)
 
+    def set_kernel_timing(self, enabled: bool):
+        """Kernel history (``dr.kernel_history`` analogue): bracket every wavefront launch with CUDA events."""
+        capi.check(self.lib.b2_set_kernel_timing(self.handle, int(bool(enabled))))
+
+    def kernel_times(self):
+        """-> {kind: (milliseconds, launches)} accumulated since the previous call (synchronises the device)."""
+        ms = (C.c_double * 4)(); n = (C.c_uint64 * 4)()
+        capi.check(self.lib.b2_kernel_times(self.handle, ms, n))
+        return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(("trace", "shade", "splat", "other"))}
+
     def set_param(self, bsdf_index: int, what: str, value):
         """what = 'value' (3 floats) | 'data' ([H, W, 3] fp32 texture)."""
         t = as_device_tensor(value, self.device, _torch().float32)

@@ -7,6 +7,8 @@ because the reference's bedroom meshes/textures are git-LFS pointers (SURVEY.md 
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 
 from .scene import T
@@ -269,3 +271,24 @@ def random_triangles(n_tris=10_000_000, width=1920, height=1080, spp=128, seed=3
         d[f"soup{k}"] = {"type": "mesh", "positions": v.reshape(-1, 3), "faces": np.arange(3 * n, dtype=np.uint32).reshape(-1, 3),
                          "bsdf": {"type": "twosided", "nested": {"type": "diffuse", "reflectance": {"type": "rgb", "value": albedos[k].tolist()}}}}
     return d
+
+
+def woodfloor_texture() -> np.ndarray:
+    """The reference's ``WoodFloor.jpg`` (960 x 870) as the fp32 linear-RGB tensor Mitsuba would hold for an optimised
+    ``bitmap`` parameter (sRGB -> linear, bitmap.cpp:286-294; fp32 because it is a differentiable tensor, :208-218).
+    The pixels come from the committed fixture ``tests/golden/woodfloor_u8.npz`` (decoded from the reference checkout by
+    ``tests/golden/make_woodfloor.py``); without the fixture a procedural stand-in of the same shape is returned."""
+    from .scene import srgb_to_linear
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "woodfloor_u8.npz")
+    if os.path.exists(path):
+        rgb = np.load(path)["rgb"]
+        return np.ascontiguousarray(srgb_to_linear(rgb.astype(np.float32) / np.float32(255.0)))
+    return np.ascontiguousarray(value_noise_rgb(960, 7, [0.6, 0.45, 0.3]).astype(np.float32)[:870])
+
+
+def cornell_prb_scene(width=512, height=512, spp=32) -> dict:
+    """BASELINE config 3: the Cornell box whose ``white`` BSDF carries the WoodFloor texture as its reflectance."""
+    d = cornell_box(width, height, spp)
+    d["white"] = {"type": "diffuse", "reflectance": {"type": "bitmap", "data": woodfloor_texture(), "raw": True}}
+    return d
+

@@ -6,9 +6,7 @@ from mitsuba3_experiments_b200 import scenes
 from mitsuba3_experiments_b200.integrator import PRBIntegrator, traverse
 from mitsuba3_experiments_b200.runtime import DeviceScene
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 3
-d = scenes.cornell_box(512, 512, 32)
-tex = scenes.value_noise_rgb(960, 7, [0.6, 0.45, 0.3]).astype(np.float32)[:870]
-d["white"] = {"type": "diffuse", "reflectance": {"type": "bitmap", "data": np.ascontiguousarray(tex), "raw": True}}
+d = scenes.cornell_prb_scene(512, 512, 32)
 ds = DeviceScene(d)
 prb = PRBIntegrator({"max_depth": 8, "rr_depth": 5})
 params = traverse(ds); params.keep(["white.reflectance.data"])
