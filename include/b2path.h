@@ -160,7 +160,9 @@ typedef struct b2_render_args {
     int32_t env_warp;       /* B2_ENV_WARP_* */
     uint64_t lane_begin, lane_end; /* shard: global lane range within one pass wavefront; 0,0 = all */
     uint32_t chunk_lanes;   /* wavefront chunk capacity (CUDA only), 0 = default */
-    uint32_t reserved;      /* bit 0 (render_backward only): reuse the weight film of the previous call with the same (seed, spp) */
+    uint32_t reserved;      /* bit 0 (render_backward only): reuse the weight film of the previous call with the same (seed, spp);
+                               bit 1 (render): trace every shadow ray, also those of emitter samples whose value is exactly zero
+                               (the reference does; the image is identical either way, only b2_counters.shadow_rays differs) */
 } b2_render_args;
 
 typedef struct b2_counters {

@@ -270,6 +270,12 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
         if (WF && !ADJ) { s.L = s.L + Le; so->a = Lr_dir; so->b = f3(1.f); }
         else s.L = ADJ ? (s.L - Le - Lr_dir) : (s.L + Le + Lr_dir);                         // prb.py:173
     }
+    if (WF && !ADJ && p.cull_nee && so->valid) {
+        // an emitter sample whose contribution is exactly zero (light behind the surface, back side of the emitter, ...)
+        // cannot change L whether or not it arrives: drop the shadow ray (NaN products compare false and are kept)
+        const f3 c = so->a * so->b;
+        if (c.x == 0.f && c.y == 0.f && c.z == 0.f) so->valid = false;
+    }
     s.ray = spawn_ray(si.p, si.n, si.sh.to_world(bs.wo));
     s.f *= bsdf_weight; s.eta *= bs.eta;
     s.prev_p = si.p; s.prev_pdf = bs.pdf; s.prev_delta = (bs.type & LOBE_DELTA) != 0;

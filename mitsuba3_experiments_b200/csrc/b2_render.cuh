@@ -14,6 +14,7 @@ struct GradTargetDev { int32_t bsdf, kind; float *grad; };
 struct RenderParams {
     DScene sc;
     uint32_t seed, spp_per_pass, n_passes, spp_shift;   // spp_shift: log2(spp_per_pass) or 0xffffffff (integrator.cpp:293-300)
+    int32_t cull_nee;                                    // wavefront: skip shadow rays of zero-valued emitter samples
     int32_t max_depth, rr_depth, env_warp, filter_n;     // filter_n = ceil(radius - 0.5) (imageblock.cpp:438-441); box: 0
     uint64_t lane_begin, lane_end;                       // shard of the per-pass wavefront
     uint32_t unit_pixels, units_per_row, unit_begin, unit_end, tile_cols, tile_rows;

@@ -261,6 +261,7 @@ static int setup_params(b2_scene *s, const b2_render_args *a, int mode, bool cou
     p.spp_shift = 0xffffffffu;
     for (uint32_t k = 0; k < 32; ++k) if ((1u << k) == spp_per_pass) p.spp_shift = k;
     p.max_depth = a->max_depth; p.rr_depth = a->rr_depth; p.env_warp = a->env_warp;
+    p.cull_nee = (mode == MODE_RENDER && !(a->reserved & 2u)) ? 1 : 0;   // never in render_backward: a zero albedo still has a gradient
     p.filter_n = sn.rfilter == B2_RFILTER_BOX ? 0 : (int) std::ceil(sn.rfilter_radius - .5f);
     p.lane_begin = lane_begin; p.lane_end = lane_end ? std::min(lane_end, wavefront) : wavefront;
     if (p.lane_begin > p.lane_end) return fail(-2, "render: lane_begin > lane_end");

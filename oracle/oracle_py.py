@@ -78,7 +78,7 @@ class OracleScene:
         if getattr(self, "h", None):
             lib().orc_scene_destroy(self.h); self.h = None
 
-    def make_args(self, seed=0, spp=None, max_depth=8, rr_depth=4, variant=0, spp_per_pass=0, lane_begin=0, lane_end=0, kernel=0):
+    def make_args(self, seed=0, spp=None, max_depth=8, rr_depth=4, variant=0, spp_per_pass=0, lane_begin=0, lane_end=0, kernel=0, all_shadow_rays=False):
         from mitsuba3_experiments_b200 import capi
         a = capi.RenderArgs()
         a.seed, a.spp, a.spp_per_pass = seed, spp or self.desc.spp, spp_per_pass

@@ -86,7 +86,7 @@ def test_cornell_render_parity(variant, max_depth, rr_depth, kernel):
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
     ds = DeviceScene(cornell_box(96, 96, spp=16)); orc = OracleScene(ds.desc)
     kw = dict(seed=0, spp=16, max_depth=max_depth, rr_depth=rr_depth, variant=variant)
-    img, cnt = ds.render(counters=True, kernel=kernel, **kw)
+    img, cnt = ds.render(counters=True, kernel=kernel, all_shadow_rays=True, **kw)    # counter parity: trace what the reference traces
     ref, rc = orc.render(**kw)
     check_image(img.cpu().numpy(), ref, 0.999, 1e-4)
     for k in ("samples", "closest_rays", "shadow_rays", "vertices", "nee_area", "splat_taps"):
@@ -101,7 +101,7 @@ def test_materials_render_parity(variant, filt, envmap, kernel):
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
     ds = DeviceScene(materials_scene(64, 48, 16, envmap=envmap, filter_type=filt)); orc = OracleScene(ds.desc)
     kw = dict(seed=3, spp=16, max_depth=7, rr_depth=3, variant=variant)
-    img, cnt = ds.render(counters=True, kernel=kernel, **kw)
+    img, cnt = ds.render(counters=True, kernel=kernel, all_shadow_rays=True, **kw)    # counter parity: trace what the reference traces
     ref, rc = orc.render(**kw)
     check_image(img.cpu().numpy(), ref, 0.99, 2e-3)
     for k in ("closest_rays", "shadow_rays", "vertices", "tex_evals", "nee_area", "nee_env", "env_escapes", "splat_taps"):
@@ -125,9 +125,13 @@ def test_wavefront_equals_megakernel(variant):
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
     ds = DeviceScene(materials_scene(64, 48, 16, envmap=True, filter_type="gaussian"))
     kw = dict(seed=9, spp=16, max_depth=6, rr_depth=2, variant=variant)
-    a, ca = ds.render(counters=True, kernel=0, **kw)
+    a, ca = ds.render(counters=True, kernel=0, all_shadow_rays=True, **kw)
     b, cb = ds.render(counters=True, kernel=1, **kw)
     np.testing.assert_allclose(a.cpu().numpy(), b.cpu().numpy(), rtol=2e-5, atol=1e-6)
+    # default product path: shadow rays of emitter samples whose value is exactly zero are not traced -- same image
+    e, ce = ds.render(counters=True, kernel=0, **kw)
+    np.testing.assert_allclose(e.cpu().numpy(), a.cpu().numpy(), rtol=2e-5, atol=1e-6)
+    assert ce["shadow_rays"] < ca["shadow_rays"] and ce["closest_rays"] == ca["closest_rays"] and ce["vertices"] == ca["vertices"]
     for k in ca:
         if k in ("node_fetches", "tri_fetches"):      # traversal work: the wavefront parks leaf triangles, so the
             assert abs(ca[k] - cb[k]) <= 0.15 * cb[k], (k, ca[k], cb[k])   # closest-hit bound shrinks a little later
