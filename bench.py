@@ -151,6 +151,7 @@ def main():
     ap.add_argument("--workload", default="bedroom", choices=["bedroom", "cornell"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-prb", action="store_true")
+    ap.add_argument("--bands", type=int, default=2, help="image bands per rank (N > 1); bands are interleaved across ranks")
     args = ap.parse_args()
     rank_env = int(os.environ.get("RANK", "0"))
     if args.impl == "reference":
@@ -171,7 +172,7 @@ def main():
     ds = DeviceScene(scene_dict, device=local)
     H, W = ds.film_shape
     n_total = ds.wavefront_size(spp)
-    plan = b2dist.shard_plan(n_total, spp, W, world, rank, bands_per_rank=8 if world > 1 else 1)
+    plan = b2dist.shard_plan(n_total, spp, W, world, rank, bands_per_rank=args.bands if world > 1 else 1)
     n_local = sum(b - a for a, b in plan)
     film = ds.new_film()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -242,6 +243,8 @@ def main():
         tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
     e2e_value = n_total / float(t[0]) / 1e6
 
+    if world > 1:
+        tdist.barrier(); tdist.destroy_process_group()
     if rank != 0:
         return
     peak, peak_kind = measured_peak()
