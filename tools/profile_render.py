@@ -15,7 +15,7 @@ elif wl == "cornell":
     spp = spp or 16; d = scenes.cornell_box(256, 256, spp); kw = dict(variant=0, max_depth=8, rr_depth=4)
 elif wl == "tris":
     spp = spp or 8; d = scenes.random_triangles(10_000_000, 1920, 1080, spp); kw = dict(variant=0, max_depth=8, rr_depth=4)
-kw.update(kernel=kernel, chunk_lanes=chunk)
+kw.update(kernel=kernel, chunk_lanes=chunk, env_warp=int(os.environ.get('B2_ENV_WARP', '0')))
 ds = DeviceScene(d)
 print("build", ds.build_stats.as_dict())
 film = ds.new_film()
