@@ -61,6 +61,7 @@ struct DScene {
     const uint4 *nodes;              // 5 x uint4 per wide node
     const float4 *tris;              // 3 x float4 per triangle, leaf order
     uint32_t n_emitters, n_faces, n_nodes; int32_t env_emitter;
+    uint32_t qmagic;                 // = 0x47: exponent byte of 32768 + q, read from the constant bank (b2_bvh.cuh, qbyte_biased)
     DEnvmap env;
     DSensor sensor;
 };

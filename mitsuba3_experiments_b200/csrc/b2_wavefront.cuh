@@ -66,6 +66,7 @@ struct WfLaunch {
     uint32_t slice;                  // trace: traversal micro-steps between two refill points
     uint32_t vis_bit;                // trace: bit to set in vis[] for arriving shadow rays; shade<ADJ>: bit to read; ~0u = off
     uint32_t tri_thresh;             // trace: lanes with pending leaf triangles that trigger a triangle step
+    uint32_t prefetch;               // trace: bit 0 = prefetch parked leaf triangles into L1
 };
 
 // per-kernel-kind timing (host side)

@@ -9,6 +9,8 @@
 #include "b2_bvh.cuh"
 #include <cub/device/device_radix_sort.cuh>
 #include <cfloat>
+#include <cstdlib>
+#include <string>
 
 namespace b2 {
 
@@ -16,6 +18,7 @@ namespace b2 {
 
 constexpr uint32_t kLeafFlag = 0x80000000u;
 constexpr uint32_t kLeafMax = 3;       // triangles per leaf child (unary count in 3 meta bits)
+constexpr float kQMargin = 1.f / 64.f;  // quantisation margin in grid cells
 
 struct Box { float lo[3], hi[3]; };
 
@@ -107,10 +110,22 @@ __global__ void k_karras(const uint64_t *__restrict__ keys, int n, uint32_t *__r
     if (i == 0) parent[0] = 0xffffffffu;
 }
 
-// ---- 4. bottom-up refit; the second thread to arrive at a node merges its children
+// ---- 4. bottom-up refit + collapse DP; the second thread to arrive at a node merges its children.
+// DP (Ylitie, Karras, Laine 2017, "Efficient incoherent ray traversal on GPUs through compressed wide BVHs", sec. 4.1):
+// cost[x][i-1], i = 1..7, is the least SAH cost of representing the binary subtree x by at most i children of a wide
+// node (each a leaf of <= 3 triangles or a wide node of its own):
+//   dist(x, j)  = min_{0<k<j} cost[left][k] + cost[right][j-k]                 (j = 2..8)
+//   cost[x][1]  = min(A_x P_x c_prim  if P_x <= 3,   A_x c_node + dist(x, 8))
+//   cost[x][i]  = min(dist(x, i), cost[x][i-1])
+// dec[x][j-1] records the choice: j = 1: 0 = leaf, else internal; j = 2..7: 0 = "as j-1", else the left budget k;
+// dec[x][7] = the left budget of dist(x, 8).  A single triangle costs A c_prim for every i.
+struct DpCost { float c[7]; };
+B2_DEV float half_area(const float4 &lo, const float4 &hi) { float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z; return dx * dy + dy * dz + dz * dx; }
+
 __global__ void k_refit(const float4 *__restrict__ blo, const float4 *__restrict__ bhi, const uint32_t *__restrict__ sorted, int n,
                         const uint32_t *__restrict__ left, const uint32_t *__restrict__ right, const uint32_t *__restrict__ parent,
-                        float4 *__restrict__ nlo, float4 *__restrict__ nhi, uint32_t *__restrict__ flags) {
+                        const uint2 *__restrict__ range, float4 *__restrict__ nlo, float4 *__restrict__ nhi, uint32_t *__restrict__ flags,
+                        float *__restrict__ cost, uint2 *__restrict__ dec, float c_node, float c_prim) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     uint32_t tri = sorted[i];
@@ -129,6 +144,31 @@ __global__ void k_refit(const float4 *__restrict__ blo, const float4 *__restrict
         lo = make_float4(fminf(a.x, c.x), fminf(a.y, c.y), fminf(a.z, c.z), 0.f);
         hi = make_float4(fmaxf(b.x, e.x), fmaxf(b.y, e.y), fmaxf(b.z, e.z), 0.f);
         nlo[p] = lo; nhi[p] = hi;
+        // collapse DP of node p
+        float cl[7], cr[7];
+        volatile const float *vc = cost;
+        if (L & kLeafFlag) { float v = half_area(a, b) * c_prim; for (int k = 0; k < 7; ++k) cl[k] = v; }
+        else for (int k = 0; k < 7; ++k) cl[k] = vc[(size_t) L * 7 + k];
+        if (R & kLeafFlag) { float v = half_area(c, e) * c_prim; for (int k = 0; k < 7; ++k) cr[k] = v; }
+        else for (int k = 0; k < 7; ++k) cr[k] = vc[(size_t) R * 7 + k];
+        float dist[9]; uint32_t dk[9];
+        for (int j = 2; j <= 8; ++j) {
+            float best = FLT_MAX; uint32_t bk = 1;
+            for (int k = 1; k < j; ++k) { float v = cl[k - 1] + cr[j - k - 1]; if (v < best) { best = v; bk = (uint32_t) k; } }
+            dist[j] = best; dk[j] = bk;
+        }
+        const uint2 rg = range[p];
+        const uint32_t cnt = rg.y - rg.x + 1u;
+        const float A = half_area(lo, hi);
+        const float c_int = A * c_node + dist[8], c_leaf = cnt <= kLeafMax ? A * (float) cnt * c_prim : FLT_MAX;
+        float out[7]; uint32_t d[8];
+        out[0] = fminf(c_leaf, c_int); d[0] = c_leaf <= c_int ? 0u : 1u;
+        for (int j = 2; j <= 7; ++j) {
+            if (dist[j] < out[j - 2]) { out[j - 1] = dist[j]; d[j - 1] = dk[j]; } else { out[j - 1] = out[j - 2]; d[j - 1] = 0u; }
+        }
+        d[7] = dk[8];
+        for (int k = 0; k < 7; ++k) cost[(size_t) p * 7 + k] = out[k];
+        dec[p] = make_uint2(d[0] | (d[1] << 8) | (d[2] << 16) | (d[3] << 24), d[4] | (d[5] << 8) | (d[6] << 16) | (d[7] << 24));
         p = parent[p];
     }
 }
@@ -136,7 +176,7 @@ __global__ void k_refit(const float4 *__restrict__ blo, const float4 *__restrict
 // ---- 5. collapse one level: wide node w <- binary subtree wide_to_binary[w]
 struct CollapseArgs {
     const float *pos; const uint32_t *faces; const uint32_t *face_mesh; const uint32_t *sorted;
-    const uint32_t *left, *right; const uint2 *range; const float4 *nlo, *nhi;
+    const uint32_t *left, *right; const uint2 *range; const float4 *nlo, *nhi; const uint2 *dec;   // dec == nullptr: greedy collapse
     uint32_t *wide_to_binary; uint4 *nodes; float4 *tris; uint32_t *counters;   // [0] nodes, [1] tris
     uint32_t n, max_nodes;
 };
@@ -159,29 +199,53 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
     if (w >= end) return;
     const uint32_t n = a.n;
     uint32_t root = a.wide_to_binary[w];
-    uint32_t ch[8]; int nc = 1; ch[0] = root;
-    // open the child with the largest surface area until 8 children
-    while (nc < 8) {
-        int best = -1; float best_area = -1.f;
-        for (int i = 0; i < nc; ++i) {
-            if (ref_count(a, ch[i]) <= kLeafMax) continue;
-            uint32_t bi = ref_index(ch[i], n);
-            float4 l = a.nlo[bi], h = a.nhi[bi];
-            float dx = h.x - l.x, dy = h.y - l.y, dz = h.z - l.z, area = dx * dy + dy * dz + dz * dx;
-            if (area > best_area) { best_area = area; best = i; }
+    uint32_t ch[8]; int nc = 0; uint32_t leaf_bits = 0;       // leaf_bits: child i is a leaf (<= kLeafMax triangles)
+    auto dec_of = [&](uint32_t x, int j) { uint2 d = a.dec[x]; return ((j <= 4 ? d.x : d.y) >> (((j - 1) & 3) * 8)) & 0xffu; };
+    if (a.dec && !(root & kLeafFlag)) {
+        // follow the DP decisions: (binary node, child budget) pairs; the root is forced to distribute 8
+        uint32_t sx[8]; int sj[8]; int sp = 0;
+        sx[sp] = root; sj[sp++] = 8; bool forced = true;
+        while (sp) {
+            uint32_t x = sx[--sp]; int j = sj[sp];
+            if (x & kLeafFlag) { leaf_bits |= 1u << nc; ch[nc++] = x; continue; }
+            uint32_t k;
+            if (forced) { k = dec_of(x, 8); forced = false; }
+            else {
+                while (j > 1 && dec_of(x, j) == 0u) --j;
+                if (j == 1) { if (dec_of(x, 1) == 0u) leaf_bits |= 1u << nc; ch[nc++] = x; continue; }
+                k = dec_of(x, j);
+            }
+            sx[sp] = a.right[x]; sj[sp++] = j - (int) k;
+            sx[sp] = a.left[x]; sj[sp++] = (int) k;
         }
-        if (best < 0) break;
-        uint32_t b = ch[best];
-        ch[best] = a.left[b]; ch[nc++] = a.right[b];
+    } else {
+        nc = 1; ch[0] = root;
+        // greedy: open the child with the largest surface area until 8 children
+        while (nc < 8) {
+            int best = -1; float best_area = -1.f;
+            for (int i = 0; i < nc; ++i) {
+                if (ref_count(a, ch[i]) <= kLeafMax) continue;
+                uint32_t bi = ref_index(ch[i], n);
+                float4 l = a.nlo[bi], h = a.nhi[bi];
+                float dx = h.x - l.x, dy = h.y - l.y, dz = h.z - l.z, area = dx * dy + dy * dz + dz * dx;
+                if (area > best_area) { best_area = area; best = i; }
+            }
+            if (best < 0) break;
+            uint32_t b = ch[best];
+            ch[best] = a.left[b]; ch[nc++] = a.right[b];
+        }
+        for (int i = 0; i < nc; ++i) if (ref_count(a, ch[i]) <= kLeafMax) leaf_bits |= 1u << i;
     }
     // node frame
     uint32_t rbi = ref_index(root, n);
     float4 nl = a.nlo[rbi], nh = a.nhi[rbi];
     float lo[3] = { nl.x, nl.y, nl.z }, hi[3] = { nh.x, nh.y, nh.z };
     float ext_max = fmaxf(fmaxf(hi[0] - lo[0], hi[1] - lo[1]), hi[2] - lo[2]);
-    float origin[3], scale[3]; uint32_t eb[3];
+    float origin[3], scale[3], padabs[3]; uint32_t eb[3];
     for (int k = 0; k < 3; ++k) {
-        float pad = fmaxf(fmaxf(fabsf(lo[k]), fabsf(hi[k])), ext_max) * 2e-6f + 1e-30f;
+        // padabs covers fp32 rounding of ray-origin-relative positions; pad >= padabs + the quantisation margin of the children
+        padabs[k] = fmaxf(fmaxf(fabsf(lo[k]), fabsf(hi[k])), ext_max) * 2e-6f + 1e-30f;
+        float pad = 1.1f * padabs[k] + (hi[k] - lo[k]) * (1.f / 3000.f);
         origin[k] = lo[k] - pad;
         eb[k] = exp_byte_for((hi[k] + pad) - origin[k]);
         scale[k] = __uint_as_float(eb[k] << 23);
@@ -209,7 +273,7 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
     }
     // allocate children
     uint32_t k_int = 0, k_tri = 0;
-    for (int i = 0; i < nc; ++i) { uint32_t c = ref_count(a, ch[i]); if (c > kLeafMax) k_int++; else k_tri += c; }
+    for (int i = 0; i < nc; ++i) { if (leaf_bits >> i & 1u) k_tri += ref_count(a, ch[i]); else k_int++; }
     uint32_t child_base = k_int ? atomicAdd(&a.counters[0], k_int) : 0u;
     uint32_t tri_base = k_tri ? atomicAdd(&a.counters[1], k_tri) : 0u;
     if (k_int && child_base + k_int > a.max_nodes) { a.counters[2] = 1u; return; }   // cannot happen (max_nodes bound), flagged anyway
@@ -221,13 +285,16 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
         float4 l = a.nlo[bi], h = a.nhi[bi];
         float cl[3] = { l.x, l.y, l.z }, chh[3] = { h.x, h.y, h.z };
         for (int k = 0; k < 3; ++k) {
-            float ql = floorf((cl[k] - origin[k]) / scale[k]), qh = ceilf((chh[k] - origin[k]) / scale[k]);
+            // planes sit padabs + kQMargin cells outside the child box: covers position rounding (as the node frame does)
+            // and the <= 2^-9-cell plane shift of the biased-byte slab test (b2_bvh.cuh, qbyte_biased)
+            const float m = kQMargin * scale[k] + padabs[k];
+            float ql = floorf((cl[k] - m - origin[k]) / scale[k]), qh = ceilf((chh[k] + m - origin[k]) / scale[k]);
             ql = fminf(fmaxf(ql, 0.f), 255.f); qh = fminf(fmaxf(qh, 0.f), 255.f);
-            while (ql > 0.f && origin[k] + ql * scale[k] > cl[k]) ql -= 1.f;
-            while (qh < 255.f && origin[k] + qh * scale[k] <= chh[k]) qh += 1.f;
+            while (ql > 0.f && origin[k] + ql * scale[k] > cl[k] - m) ql -= 1.f;
+            while (qh < 255.f && origin[k] + qh * scale[k] < chh[k] + m) qh += 1.f;
             qlo[k][s] = (uint32_t) ql; qhi[k][s] = (uint32_t) qh;
         }
-        if (cnt > kLeafMax) {
+        if (!(leaf_bits >> i & 1u)) {
             imask |= 1u << s; meta[s] = 0x20u | (24u + (uint32_t) s);
             a.wide_to_binary[child_base + ni] = ref; ni++;
         } else {
@@ -285,7 +352,12 @@ bool bvh_build(const float *pos, const uint32_t *faces, const uint32_t *face_mes
     float4 *blo, *bhi, *nlo, *nhi, *tris;
     uint32_t *scene_bounds, *vals, *vals2, *left, *right, *parent, *flags, *w2b, *counters;
     uint64_t *keys, *keys2; uint2 *range; uint4 *nodes, *nodes_final; void *tmp; size_t tmp_bytes = 0;
-    const uint32_t max_nodes = n / 2 + 2;
+    const uint32_t max_nodes = n + 2;     // a wide node per binary internal node at most
+    float *cost; uint2 *dec;
+    // collapse policy knobs (tuning only; defaults are the measured optimum, profiles/README.md)
+    const char *e_mode = getenv("B2_BVH_COLLAPSE"), *e_cn = getenv("B2_BVH_CNODE"), *e_cp = getenv("B2_BVH_CPRIM");
+    const bool use_dp = !(e_mode && std::string(e_mode) == "greedy");
+    const float c_node = e_cn ? (float) atof(e_cn) : 1.f, c_prim = e_cp ? (float) atof(e_cp) : 0.3f;
     uint32_t level_begin = 0, level_end = 1, depth = 0, host_counters[3] = { 1, 0, 0 };
     for (auto &e : S.ev) CK(cudaEventCreate(&e));
     CK(S.alloc(blo, sizeof(float4) * n)); CK(S.alloc(bhi, sizeof(float4) * n));
@@ -312,7 +384,8 @@ bool bvh_build(const float *pos, const uint32_t *faces, const uint32_t *face_mes
     CK(S.alloc(nlo, sizeof(float4) * 2 * (size_t) n)); CK(S.alloc(nhi, sizeof(float4) * 2 * (size_t) n));
     if (n > 1) k_karras<<<G, T, 0, st>>>(keys, (int) n, left, right, parent, range);
     else { CK(cudaMemsetAsync(parent, 0xff, 4, st)); }
-    k_refit<<<G, T, 0, st>>>(blo, bhi, vals, (int) n, left, right, parent, nlo, nhi, flags);
+    CK(S.alloc(cost, sizeof(float) * 7 * (size_t) n)); CK(S.alloc(dec, sizeof(uint2) * (size_t) n));
+    k_refit<<<G, T, 0, st>>>(blo, bhi, vals, (int) n, left, right, parent, range, nlo, nhi, flags, cost, dec, c_node, c_prim);
     CK(cudaEventRecord(S.ev[2], st));
     // collapse, one launch per level of the wide tree
     CK(S.alloc(nodes, sizeof(uint4) * 5 * (size_t) max_nodes)); CK(S.alloc(tris, sizeof(float4) * 3 * (size_t) n));
@@ -320,7 +393,7 @@ bool bvh_build(const float *pos, const uint32_t *faces, const uint32_t *face_mes
     CK(cudaMemcpyAsync(counters, host_counters, sizeof(host_counters), cudaMemcpyHostToDevice, st));
     { uint32_t root_ref = n > 1 ? 0u : (0u | kLeafFlag); CK(cudaMemcpyAsync(w2b, &root_ref, 4, cudaMemcpyHostToDevice, st)); CK(cudaStreamSynchronize(st)); }
     {
-        CollapseArgs ca{ pos, faces, face_mesh, vals, left, right, range, nlo, nhi, w2b, nodes, tris, counters, n, max_nodes };
+        CollapseArgs ca{ pos, faces, face_mesh, vals, left, right, range, nlo, nhi, use_dp ? dec : nullptr, w2b, nodes, tris, counters, n, max_nodes };
         while (level_begin < level_end) {
             uint32_t cnt = level_end - level_begin;
             k_collapse<<<(cnt + 127) / 128, 128, 0, st>>>(ca, level_begin, level_end);

@@ -174,7 +174,7 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
     }
     CUDA_OK(cudaMalloc((void **) &s->unit_counter, 16)); s->allocs.push_back(s->unit_counter);
     CUDA_OK(cudaMalloc((void **) &s->counters_dev, sizeof(unsigned long long) * C_N)); s->allocs.push_back(s->counters_dev);
-    d.nodes = nullptr; d.tris = nullptr; d.n_nodes = 0;
+    d.nodes = nullptr; d.tris = nullptr; d.n_nodes = 0; d.qmagic = 0x47u;
     *out = s.release();
     return 0;
 }

@@ -97,6 +97,8 @@ __global__ void __launch_bounds__(256) k_wf_generate(const __grid_constant__ Ren
 }
 
 // ------------------------------------------------------------------------------------------ trace
+B2_DEV void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
+
 struct TraceRay {
     f3 o, d; float idx, idy, idz, maxt;
     uint32_t octinv, slot, qi; bool any, tex;
@@ -148,7 +150,7 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
                 r.slot = r.any ? qs[my - nc] : qc[my];
                 const float4 o = r.any ? st.sh_o(r.slot) : st.ray_o(r.slot), d = r.any ? st.sh_d(r.slot) : st.ray_d(r.slot);
                 r.o = f3(o.x, o.y, o.z); r.d = f3(d.x, d.y, d.z); r.maxt = o.w; r.tex = r.any && d.w != 0.f;
-                const float tiny = 1e-30f;
+                const float tiny = kTinyDir;
                 r.idx = 1.f / (fabsf(r.d.x) > tiny ? r.d.x : copysignf(tiny, r.d.x));
                 r.idy = 1.f / (fabsf(r.d.y) > tiny ? r.d.y : copysignf(tiny, r.d.y));
                 r.idz = 1.f / (fabsf(r.d.z) > tiny ? r.d.z : copysignf(tiny, r.d.z));
@@ -218,37 +220,14 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
                 const uint4 *np = sc.nodes + (size_t) (r.ng.x + rel) * 5;
                 const uint4 w0 = __ldg(np), w1 = __ldg(np + 1), w2 = __ldg(np + 2), w3 = __ldg(np + 3), w4 = __ldg(np + 4);
                 cnt.add(C_NODES);
-                const float sx = __uint_as_float((w0.w & 0xffu) << 23), sy = __uint_as_float(((w0.w >> 8) & 0xffu) << 23),
-                            sz = __uint_as_float(((w0.w >> 16) & 0xffu) << 23);
                 const uint32_t imask = w0.w >> 24;
-                const float ax = sx * r.idx, ay = sy * r.idy, az = sz * r.idz;
-                const float bx = (__uint_as_float(w0.x) - r.o.x) * r.idx, by = (__uint_as_float(w0.y) - r.o.y) * r.idy,
-                            bz = (__uint_as_float(w0.z) - r.o.z) * r.idz;
-                // entry / exit plane bytes of the eight children, chosen once per node by the ray octant
-                const bool px = (r.octinv & 1u) != 0u, py = (r.octinv & 2u) != 0u, pz = (r.octinv & 4u) != 0u;
-                const uint32_t nx0 = px ? w2.x : w3.z, nx1 = px ? w2.y : w3.w, fx0 = px ? w3.z : w2.x, fx1 = px ? w3.w : w2.y;
-                const uint32_t ny0 = py ? w2.z : w4.x, ny1 = py ? w2.w : w4.y, fy0 = py ? w4.x : w2.z, fy1 = py ? w4.y : w2.w;
-                const uint32_t nz0 = pz ? w3.x : w4.z, nz1 = pz ? w3.y : w4.w, fz0 = pz ? w4.z : w3.x, fz1 = pz ? w4.w : w3.y;
-                uint32_t hitmask = 0;
-#pragma unroll
-                for (int s = 0; s < 8; ++s) {
-                    const uint32_t meta = byte_of(w1.z, w1.w, s);
-                    const float t0x = __fmaf_rn((float) byte_of(nx0, nx1, s), ax, bx), t1x = __fmaf_rn((float) byte_of(fx0, fx1, s), ax, bx);
-                    const float t0y = __fmaf_rn((float) byte_of(ny0, ny1, s), ay, by), t1y = __fmaf_rn((float) byte_of(fy0, fy1, s), ay, by);
-                    const float t0z = __fmaf_rn((float) byte_of(nz0, nz1, s), az, bz), t1z = __fmaf_rn((float) byte_of(fz0, fz1, s), az, bz);
-                    const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
-                    const float tf = fminf(fminf(t1x, t1y), t1z) * 1.0000005f;
-                    // internal child: meta = 0x20 | (24 + s) -> bit 24 + s; leaf: unary count << offset; empty: 0
-                    hitmask |= (tn <= fminf(tf, r.t)) ? ((meta >> 5) << (meta & 31u)) : 0u;
-                }
-                // child-slot bits (24 + s) -> traversal-order bits (24 + (s ^ octinv))
-                uint32_t nh = hitmask >> 24;
-                if (px) nh = ((nh & 0x55u) << 1) | ((nh & 0xaau) >> 1);
-                if (py) nh = ((nh & 0x33u) << 2) | ((nh & 0xccu) >> 2);
-                if (pz) nh = ((nh & 0x0fu) << 4) | ((nh & 0xf0u) >> 4);
-                r.ng = make_uint2(w1.x, (nh << 24) | imask);
+                const uint32_t hitmask = node_slab_hits(w0, w1, w2, w3, w4, r.o, r.idx, r.idy, r.idz, r.octinv, r.t, sc.qmagic);
+                r.ng = make_uint2(w1.x, (permute_octant(hitmask, r.octinv) << 24) | imask);
                 const uint32_t thits = hitmask & 0x00ffffffu;
                 if (thits) {
+                    // the parked triangles are tested a few micro-steps from now: start their L2 -> L1 transfer here
+                    // (ncu r01_v4: the first use of the triangle words was the largest long-scoreboard stall, 14 % of samples)
+                    if (w.prefetch & 1u) prefetch_l1(sc.tris + (size_t) (w1.y + (uint32_t) (__ffs(thits) - 1)) * 3);
                     if (r.tg.y == 0u) r.tg = make_uint2(w1.y, thits);
                     else s_pend[r.nq++][tid] = make_uint2(w1.y, thits);
                 }
@@ -529,6 +508,7 @@ void wf_collect_timing(WfTiming &t, double ms[WF_K_COUNT], uint64_t n[WF_K_COUNT
 static int env_int(const char *name, int def) { const char *v = getenv(name); return v ? std::max(1, atoi(v)) : def; }
 static const uint32_t tune_slice = (uint32_t) env_int("B2_TRACE_SLICE", B2_TRACE_SLICE);
 static const uint32_t tune_tri = (uint32_t) env_int("B2_TRI_THRESH", 8);
+static const uint32_t tune_prefetch = (uint32_t) env_int("B2_PREFETCH", 1);
 static const int tune_trace_blocks = getenv("B2_TRACE_BLOCKS") ? atoi(getenv("B2_TRACE_BLOCKS")) : 0;
 static const int tune_sort = getenv("B2_SHADE_SORT") ? atoi(getenv("B2_SHADE_SORT")) : -1;   // 0/1 force, -1 = by scene content
 
@@ -551,7 +531,7 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
     uint32_t it = 0;
     for (uint64_t c0 = lane_lo; c0 < lane_hi; c0 += st.capacity) {
         const uint32_t n = (uint32_t) std::min<uint64_t>(st.capacity, lane_hi - c0);
-        WfLaunch w; w.st = st; w.chunk_begin = c0; w.n = n; w.slice = tune_slice; w.tri_thresh = tune_tri; w.vis_bit = 0xffffffffu;
+        WfLaunch w; w.st = st; w.chunk_begin = c0; w.n = n; w.slice = tune_slice; w.tri_thresh = tune_tri; w.prefetch = tune_prefetch; w.vis_bit = 0xffffffffu;
         const int g_gen = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) sm_count * 8);
         const int g_trace = (tune_trace_blocks > 0 ? std::min(tune_trace_blocks, occ_trace) : occ_trace) * sm_count, g_shade = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_shade * sm_count);
         for (uint32_t pass = 0; pass < p.n_passes; ++pass) {
@@ -613,7 +593,7 @@ static long wf_render_backward_t(RenderParams p, WfState &st, int sm_count, cuda
     uint32_t it = 0;
     for (uint64_t c0 = p.lane_begin; c0 < p.lane_end; c0 += st.capacity) {
         const uint32_t n = (uint32_t) std::min<uint64_t>(st.capacity, p.lane_end - c0);
-        WfLaunch w; w.st = st; w.chunk_begin = c0; w.n = n; w.slice = tune_slice; w.tri_thresh = tune_tri; w.pass = 0;
+        WfLaunch w; w.st = st; w.chunk_begin = c0; w.n = n; w.slice = tune_slice; w.tri_thresh = tune_tri; w.prefetch = tune_prefetch; w.pass = 0;
         const int g_gen = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) sm_count * 8);
         const int g_trace = (tune_trace_blocks > 0 ? std::min(tune_trace_blocks, occ_trace) : occ_trace) * sm_count;
         const int g_shade = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_shade * sm_count);
