@@ -226,7 +226,8 @@ def main():
     film_h = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory()
     img_h = torch.zeros((H, W, 3), dtype=torch.float32).pin_memory()
     e2e_times = []
-    for i in range(2 + args.steps):
+    e2e_warm = 3
+    for i in range(e2e_warm + args.steps):
         film_h.zero_()
         barrier(); t0 = time.perf_counter()
         if world == 1:
@@ -236,7 +237,7 @@ def main():
             render_bands(); b2dist.merge_sum(film)
             img_h.copy_(ds.develop(film), non_blocking=True); film_h.copy_(film, non_blocking=True)
         barrier(); dt = time.perf_counter() - t0
-        if i >= 2:
+        if i >= e2e_warm:
             e2e_times.append(dt)
     t = torch.tensor([float(np.mean(e2e_times))], device=dev, dtype=torch.float64)
     if world > 1:
@@ -270,7 +271,8 @@ def main():
                    "bvh_nodes": ds.build_stats.n_nodes8, "triangles": ds.build_stats.n_tris,
                    "rays_per_step_rank0": cnt["closest_rays"] + cnt["shadow_rays"], "Mrays_per_s_rank0": (cnt["closest_rays"] + cnt["shadow_rays"]) / (kernel_ms * 1e-3) / 1e6},
         "clocks": clk,
-        "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": H * W * 16, "d2h_bytes_per_step": H * W * 16 + H * W * 12},
+        "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": H * W * 16, "d2h_bytes_per_step": H * W * 16 + H * W * 12,
+                "ms_each_rank0": [round(x * 1e3, 2) for x in e2e_times]},
         "gpu_launches": launches_per_step * args.steps,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "kernel": "k_wf_trace", "kernel_ms_per_launch": tr_ms_launch, "launches_per_step": tr_n // max(args.steps, 1),

@@ -180,7 +180,10 @@ typedef struct b2_counters {
 typedef struct b2_build_stats {
     float ms_morton_sort, ms_lbvh, ms_collapse, ms_total;
     uint32_t n_nodes8, n_tris, max_depth;
+    uint32_t builder;        /* B2_BUILDER_* that produced the tree */
     uint64_t node_bytes, tri_bytes;
+    float sah_cost;          /* SAH cost of the wide tree / root area, c_node = 1, c_prim = 0.3 */
+    float reserved;
 } b2_build_stats;
 
 typedef struct b2_hit { float t, u, v; uint32_t prim; /* original face index, 0xffffffff = miss */ } b2_hit;
@@ -200,6 +203,14 @@ int  b2_init(int device, b2_ctx **out);
 void b2_shutdown(b2_ctx *ctx);
 int  b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out);
 void b2_scene_destroy(b2_scene *scene);
+/* builder: binary tree over the Morton-sorted triangles that is then collapsed (SAH-optimal DP) into the compressed 8-wide BVH.
+   LBVH = Karras radix tree; PLOC = parallel locally-ordered clustering (better SAH, ~1.5x the build time); AUTO builds both
+   and keeps PLOC when its SAH cost is below 0.9x the radix tree's; DEFAULT = AUTO unless the environment variable
+   B2_BVH_BUILDER (0 | 1 | 2) overrides it. */
+#define B2_BUILDER_DEFAULT (-1)
+#define B2_BUILDER_LBVH    0
+#define B2_BUILDER_PLOC    1
+#define B2_BUILDER_AUTO    2
 int  b2_scene_build_accel(b2_scene *scene, int builder, uintptr_t stream, b2_build_stats *stats);
 /* key = "<bsdf index>.reflectance.value" | "<bsdf index>.reflectance.data"; data is a DEVICE pointer */
 int  b2_scene_set_param(b2_scene *scene, const char *key, const void *dev_ptr, size_t bytes, uintptr_t stream);

@@ -94,7 +94,8 @@ class Counters(C.Structure):
 
 class BuildStats(C.Structure):
     _fields_ = [("ms_morton_sort", f32), ("ms_lbvh", f32), ("ms_collapse", f32), ("ms_total", f32),
-                ("n_nodes8", u32), ("n_tris", u32), ("max_depth", u32), ("node_bytes", u64), ("tri_bytes", u64)]
+                ("n_nodes8", u32), ("n_tris", u32), ("max_depth", u32), ("builder", u32), ("node_bytes", u64), ("tri_bytes", u64),
+                ("sah_cost", f32), ("reserved", f32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -13,10 +13,13 @@ struct Bvh {
     uint32_t n_nodes = 0, n_tris = 0, depth = 0;
     size_t node_bytes = 0, tri_bytes = 0;
     float ms_morton_sort = 0, ms_lbvh = 0, ms_collapse = 0, ms_total = 0;
+    float sah_cost = 0;         // SAH cost of the wide tree / root area (c_node = 1)
+    int builder = 0;            // builder that produced this tree
 };
 
 // pos / faces / face_mesh are DEVICE pointers (Mesh buffer layout: fp32 xyz, u32 triangle indices, u32 mesh id per face)
-bool bvh_build(const float *pos, const uint32_t *faces, const uint32_t *face_mesh, uint32_t n_faces, cudaStream_t stream, Bvh &out, std::string &err);
+// builder: 0 = Karras LBVH, 1 = PLOC (both over the Morton order, both collapsed to the compressed 8-wide BVH by the SAH DP)
+bool bvh_build(const float *pos, const uint32_t *faces, const uint32_t *face_mesh, uint32_t n_faces, int builder, cudaStream_t stream, Bvh &out, std::string &err);
 void bvh_free(Bvh &b);
 
 }  // namespace b2

@@ -8,6 +8,7 @@
 #include "b2_build.h"
 #include "b2_bvh.cuh"
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_select.cuh>
 #include <cfloat>
 #include <cstdlib>
 #include <string>
@@ -86,7 +87,7 @@ B2_DEV int delta(const uint64_t *__restrict__ keys, int n, int i, int j) {
     return __clzll((long long) (a ^ b));
 }
 __global__ void k_karras(const uint64_t *__restrict__ keys, int n, uint32_t *__restrict__ left, uint32_t *__restrict__ right,
-                         uint32_t *__restrict__ parent, uint2 *__restrict__ range) {
+                         uint32_t *__restrict__ parent, uint32_t *__restrict__ cnt) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
     int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
@@ -103,12 +104,14 @@ __global__ void k_karras(const uint64_t *__restrict__ keys, int n, uint32_t *__r
     int lo = min(i, j), hi = max(i, j);
     uint32_t L = (lo == g) ? ((uint32_t) g | kLeafFlag) : (uint32_t) g;
     uint32_t R = (hi == g + 1) ? ((uint32_t) (g + 1) | kLeafFlag) : (uint32_t) (g + 1);
-    left[i] = L; right[i] = R; range[i] = make_uint2((uint32_t) lo, (uint32_t) hi);
+    left[i] = L; right[i] = R; cnt[i] = (uint32_t) (hi - lo + 1);
     // parents: internal nodes index [0, n-1), leaves index (n-1) + leaf
     if (L & kLeafFlag) parent[(n - 1) + (L & ~kLeafFlag)] = (uint32_t) i; else parent[L] = (uint32_t) i;
     if (R & kLeafFlag) parent[(n - 1) + (R & ~kLeafFlag)] = (uint32_t) i; else parent[R] = (uint32_t) i;
     if (i == 0) parent[0] = 0xffffffffu;
 }
+
+B2_DEV uint32_t ref_index(uint32_t ref, uint32_t n) { return (ref & kLeafFlag) ? (n - 1) + (ref & ~kLeafFlag) : ref; }
 
 // ---- 4. bottom-up refit + collapse DP; the second thread to arrive at a node merges its children.
 // DP (Ylitie, Karras, Laine 2017, "Efficient incoherent ray traversal on GPUs through compressed wide BVHs", sec. 4.1):
@@ -119,12 +122,38 @@ __global__ void k_karras(const uint64_t *__restrict__ keys, int n, uint32_t *__r
 //   cost[x][i]  = min(dist(x, i), cost[x][i-1])
 // dec[x][j-1] records the choice: j = 1: 0 = leaf, else internal; j = 2..7: 0 = "as j-1", else the left budget k;
 // dec[x][7] = the left budget of dist(x, 8).  A single triangle costs A c_prim for every i.
-struct DpCost { float c[7]; };
 B2_DEV float half_area(const float4 &lo, const float4 &hi) { float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z; return dx * dy + dy * dz + dz * dx; }
+
+// DP step of binary node p with children L, R (boxes a..b and c..e, node box lo..hi, `count` triangles below p)
+B2_DEV void dp_node(uint32_t p, uint32_t L, uint32_t R, const float4 &a, const float4 &b, const float4 &c, const float4 &e,
+                    const float4 &lo, const float4 &hi, uint32_t count, float *cost, uint2 *dec, float c_node, float c_prim) {
+    float cl[7], cr[7];
+    volatile const float *vc = cost;
+    if (L & kLeafFlag) { float v = half_area(a, b) * c_prim; for (int k = 0; k < 7; ++k) cl[k] = v; }
+    else for (int k = 0; k < 7; ++k) cl[k] = vc[(size_t) L * 7 + k];
+    if (R & kLeafFlag) { float v = half_area(c, e) * c_prim; for (int k = 0; k < 7; ++k) cr[k] = v; }
+    else for (int k = 0; k < 7; ++k) cr[k] = vc[(size_t) R * 7 + k];
+    float dist[9]; uint32_t dk[9];
+    for (int j = 2; j <= 8; ++j) {
+        float best = FLT_MAX; uint32_t bk = 1;
+        for (int k = 1; k < j; ++k) { float v = cl[k - 1] + cr[j - k - 1]; if (v < best) { best = v; bk = (uint32_t) k; } }
+        dist[j] = best; dk[j] = bk;
+    }
+    const float A = half_area(lo, hi);
+    const float c_int = A * c_node + dist[8], c_leaf = count <= kLeafMax ? A * (float) count * c_prim : FLT_MAX;
+    float out[7]; uint32_t d[8];
+    out[0] = fminf(c_leaf, c_int); d[0] = c_leaf <= c_int ? 0u : 1u;
+    for (int j = 2; j <= 7; ++j) {
+        if (dist[j] < out[j - 2]) { out[j - 1] = dist[j]; d[j - 1] = dk[j]; } else { out[j - 1] = out[j - 2]; d[j - 1] = 0u; }
+    }
+    d[7] = dk[8];
+    for (int k = 0; k < 7; ++k) cost[(size_t) p * 7 + k] = out[k];
+    dec[p] = make_uint2(d[0] | (d[1] << 8) | (d[2] << 16) | (d[3] << 24), d[4] | (d[5] << 8) | (d[6] << 16) | (d[7] << 24));
+}
 
 __global__ void k_refit(const float4 *__restrict__ blo, const float4 *__restrict__ bhi, const uint32_t *__restrict__ sorted, int n,
                         const uint32_t *__restrict__ left, const uint32_t *__restrict__ right, const uint32_t *__restrict__ parent,
-                        const uint2 *__restrict__ range, float4 *__restrict__ nlo, float4 *__restrict__ nhi, uint32_t *__restrict__ flags,
+                        const uint32_t *__restrict__ cnt, float4 *__restrict__ nlo, float4 *__restrict__ nhi, uint32_t *__restrict__ flags,
                         float *__restrict__ cost, uint2 *__restrict__ dec, float c_node, float c_prim) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -144,47 +173,79 @@ __global__ void k_refit(const float4 *__restrict__ blo, const float4 *__restrict
         lo = make_float4(fminf(a.x, c.x), fminf(a.y, c.y), fminf(a.z, c.z), 0.f);
         hi = make_float4(fmaxf(b.x, e.x), fmaxf(b.y, e.y), fmaxf(b.z, e.z), 0.f);
         nlo[p] = lo; nhi[p] = hi;
-        // collapse DP of node p
-        float cl[7], cr[7];
-        volatile const float *vc = cost;
-        if (L & kLeafFlag) { float v = half_area(a, b) * c_prim; for (int k = 0; k < 7; ++k) cl[k] = v; }
-        else for (int k = 0; k < 7; ++k) cl[k] = vc[(size_t) L * 7 + k];
-        if (R & kLeafFlag) { float v = half_area(c, e) * c_prim; for (int k = 0; k < 7; ++k) cr[k] = v; }
-        else for (int k = 0; k < 7; ++k) cr[k] = vc[(size_t) R * 7 + k];
-        float dist[9]; uint32_t dk[9];
-        for (int j = 2; j <= 8; ++j) {
-            float best = FLT_MAX; uint32_t bk = 1;
-            for (int k = 1; k < j; ++k) { float v = cl[k - 1] + cr[j - k - 1]; if (v < best) { best = v; bk = (uint32_t) k; } }
-            dist[j] = best; dk[j] = bk;
-        }
-        const uint2 rg = range[p];
-        const uint32_t cnt = rg.y - rg.x + 1u;
-        const float A = half_area(lo, hi);
-        const float c_int = A * c_node + dist[8], c_leaf = cnt <= kLeafMax ? A * (float) cnt * c_prim : FLT_MAX;
-        float out[7]; uint32_t d[8];
-        out[0] = fminf(c_leaf, c_int); d[0] = c_leaf <= c_int ? 0u : 1u;
-        for (int j = 2; j <= 7; ++j) {
-            if (dist[j] < out[j - 2]) { out[j - 1] = dist[j]; d[j - 1] = dk[j]; } else { out[j - 1] = out[j - 2]; d[j - 1] = 0u; }
-        }
-        d[7] = dk[8];
-        for (int k = 0; k < 7; ++k) cost[(size_t) p * 7 + k] = out[k];
-        dec[p] = make_uint2(d[0] | (d[1] << 8) | (d[2] << 16) | (d[3] << 24), d[4] | (d[5] << 8) | (d[6] << 16) | (d[7] << 24));
+        dp_node(p, L, R, a, b, c, e, lo, hi, cnt[p], cost, dec, c_node, c_prim);
         p = parent[p];
     }
 }
 
+// ---- 4b. PLOC (Meister & Bittner 2018, "Parallel locally-ordered clustering for BVH construction"): the clusters stay
+// in Morton order; every iteration each cluster finds the neighbour within +-radius whose union with it has the least
+// surface area, mutual pairs merge into a new binary node, and the cluster array is compacted.  Ties are broken by a
+// symmetric hash of the pair, so regular meshes (equal areas everywhere) still merge a constant fraction per iteration.
+// Internal node indices are handed out downwards, the last merge (the root) gets index 0 as in the Karras tree.
+B2_DEV uint32_t pair_hash(uint32_t a, uint32_t b) {
+    uint32_t lo = min(a, b), hi = max(a, b), h = lo * 0x9E3779B1u ^ (hi + 0x7F4A7C15u) * 0x85EBCA6Bu;
+    h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 12; return h;
+}
+__global__ void k_ploc_init(const float4 *__restrict__ blo, const float4 *__restrict__ bhi, const uint32_t *__restrict__ sorted, uint32_t n,
+                            float4 *__restrict__ nlo, float4 *__restrict__ nhi, uint32_t *__restrict__ cid) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t tri = sorted[i];
+    nlo[(n - 1) + i] = blo[tri]; nhi[(n - 1) + i] = bhi[tri];
+    cid[i] = i | kLeafFlag;
+}
+__global__ void k_ploc_nn(const uint32_t *__restrict__ cid, uint32_t nc, uint32_t n, const float4 *__restrict__ nlo, const float4 *__restrict__ nhi,
+                          int radius, uint32_t *__restrict__ nn) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nc) return;
+    const uint32_t ci = cid[i], bi = ref_index(ci, n);
+    const float4 l = nlo[bi], h = nhi[bi];
+    unsigned long long best = ~0ull; uint32_t bj = i;
+    const int j0 = max(0, (int) i - radius), j1 = min((int) nc - 1, (int) i + radius);
+    for (int j = j0; j <= j1; ++j) {
+        if (j == (int) i) continue;
+        const uint32_t cj = cid[j], bjx = ref_index(cj, n);
+        const float4 l2 = nlo[bjx], h2 = nhi[bjx];
+        const float dx = fmaxf(h.x, h2.x) - fminf(l.x, l2.x), dy = fmaxf(h.y, h2.y) - fminf(l.y, l2.y), dz = fmaxf(h.z, h2.z) - fminf(l.z, l2.z);
+        const float area = dx * dy + dy * dz + dz * dx;
+        const unsigned long long key = ((unsigned long long) __float_as_uint(area) << 32) | pair_hash(ci, cj);
+        if (key < best) { best = key; bj = (uint32_t) j; }
+    }
+    nn[i] = bj;
+}
+__global__ void k_ploc_merge(uint32_t *__restrict__ cid, uint32_t nc, uint32_t n, const uint32_t *__restrict__ nn,
+                             uint32_t *__restrict__ left, uint32_t *__restrict__ right, uint32_t *__restrict__ cnt,
+                             float4 *__restrict__ nlo, float4 *__restrict__ nhi, uint32_t *__restrict__ merge_counter,
+                             float *__restrict__ cost, uint2 *__restrict__ dec, float c_node, float c_prim, uint32_t *__restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nc) return;
+    const uint32_t j = nn[i];
+    const bool mutual = j != i && nn[j] == i;
+    if (!mutual) { out[i] = cid[i]; return; }
+    if (i > j) { out[i] = 0xffffffffu; return; }
+    const uint32_t L = cid[i], R = cid[j], li = ref_index(L, n), ri = ref_index(R, n);
+    const uint32_t p = (n - 2u) - atomicAdd(merge_counter, 1u);
+    const float4 a = nlo[li], b = nhi[li], c = nlo[ri], e = nhi[ri];
+    const float4 lo = make_float4(fminf(a.x, c.x), fminf(a.y, c.y), fminf(a.z, c.z), 0.f), hi = make_float4(fmaxf(b.x, e.x), fmaxf(b.y, e.y), fmaxf(b.z, e.z), 0.f);
+    const uint32_t count = ((L & kLeafFlag) ? 1u : cnt[L]) + ((R & kLeafFlag) ? 1u : cnt[R]);
+    left[p] = L; right[p] = R; cnt[p] = count; nlo[p] = lo; nhi[p] = hi;
+    dp_node(p, L, R, a, b, c, e, lo, hi, count, cost, dec, c_node, c_prim);
+    out[i] = p;
+}
+struct NotRemoved { __device__ bool operator()(uint32_t v) const { return v != 0xffffffffu; } };
+
 // ---- 5. collapse one level: wide node w <- binary subtree wide_to_binary[w]
 struct CollapseArgs {
     const float *pos; const uint32_t *faces; const uint32_t *face_mesh; const uint32_t *sorted;
-    const uint32_t *left, *right; const uint2 *range; const float4 *nlo, *nhi; const uint2 *dec;   // dec == nullptr: greedy collapse
+    const uint32_t *left, *right, *cnt; const float4 *nlo, *nhi; const uint2 *dec;   // dec == nullptr: greedy collapse
     uint32_t *wide_to_binary; uint4 *nodes; float4 *tris; uint32_t *counters;   // [0] nodes, [1] tris
     uint32_t n, max_nodes;
 };
 
-B2_DEV uint32_t ref_index(uint32_t ref, uint32_t n) { return (ref & kLeafFlag) ? (n - 1) + (ref & ~kLeafFlag) : ref; }
 B2_DEV uint32_t ref_count(const CollapseArgs &a, uint32_t ref) {
     if (ref & kLeafFlag) return 1u;
-    uint2 r = a.range[ref]; return r.y - r.x + 1u;
+    return a.cnt[ref];
 }
 B2_DEV uint32_t exp_byte_for(float extent) {
     // smallest e with 2^(e-127) * 254 >= extent
@@ -299,9 +360,11 @@ __global__ void k_collapse(CollapseArgs a, uint32_t begin, uint32_t end) {
             a.wide_to_binary[child_base + ni] = ref; ni++;
         } else {
             meta[s] = (((1u << cnt) - 1u) << 5) | nt;
-            uint32_t first = (ref & kLeafFlag) ? (ref & ~kLeafFlag) : a.range[ref].x;
+            // the <= kLeafMax triangles below ref, left to right (= Morton order for the Karras tree)
+            uint32_t lpos[kLeafMax], lst[kLeafMax]; int lsp = 0; uint32_t ln = 0; lst[lsp++] = ref;
+            while (lsp) { uint32_t x = lst[--lsp]; if (x & kLeafFlag) lpos[ln++] = x & ~kLeafFlag; else { lst[lsp++] = a.right[x]; lst[lsp++] = a.left[x]; } }
             for (uint32_t j = 0; j < cnt; ++j) {
-                uint32_t face = a.sorted[first + j];
+                uint32_t face = a.sorted[lpos[j]];
                 uint32_t i0 = a.faces[3 * (size_t) face], i1 = a.faces[3 * (size_t) face + 1], i2 = a.faces[3 * (size_t) face + 2];
                 f3 p0(a.pos[3 * (size_t) i0], a.pos[3 * (size_t) i0 + 1], a.pos[3 * (size_t) i0 + 2]);
                 f3 p1(a.pos[3 * (size_t) i1], a.pos[3 * (size_t) i1 + 1], a.pos[3 * (size_t) i1 + 2]);
@@ -344,14 +407,14 @@ struct Scratch {
 };
 }  // namespace
 
-bool bvh_build(const float *pos, const uint32_t *faces, const uint32_t *face_mesh, uint32_t n, cudaStream_t st, Bvh &out, std::string &err) {
+bool bvh_build(const float *pos, const uint32_t *faces, const uint32_t *face_mesh, uint32_t n, int builder, cudaStream_t st, Bvh &out, std::string &err) {
     out = Bvh();
     if (n == 0) return true;
     Scratch S;
     const int T = 256; const uint32_t G = (n + T - 1) / T;
     float4 *blo, *bhi, *nlo, *nhi, *tris;
     uint32_t *scene_bounds, *vals, *vals2, *left, *right, *parent, *flags, *w2b, *counters;
-    uint64_t *keys, *keys2; uint2 *range; uint4 *nodes, *nodes_final; void *tmp; size_t tmp_bytes = 0;
+    uint64_t *keys, *keys2; uint32_t *cnt; uint4 *nodes, *nodes_final; void *tmp; size_t tmp_bytes = 0;
     const uint32_t max_nodes = n + 2;     // a wide node per binary internal node at most
     float *cost; uint2 *dec;
     // collapse policy knobs (tuning only; defaults are the measured optimum, profiles/README.md)
@@ -377,15 +440,40 @@ bool bvh_build(const float *pos, const uint32_t *faces, const uint32_t *face_mes
         if (dv.Current() != vals) std::swap(vals, vals2);
     }
     CK(cudaEventRecord(S.ev[1], st));
-    // binary radix tree + refit
-    CK(S.alloc(left, sizeof(uint32_t) * n)); CK(S.alloc(right, sizeof(uint32_t) * n));
-    CK(S.alloc(parent, sizeof(uint32_t) * 2 * (size_t) n)); CK(S.alloc(range, sizeof(uint2) * n));
-    CK(S.alloc(flags, sizeof(uint32_t) * n)); CK(cudaMemsetAsync(flags, 0, sizeof(uint32_t) * n, st));
+    // binary tree (Karras radix tree + refit, or PLOC) with the collapse DP
+    CK(S.alloc(left, sizeof(uint32_t) * n)); CK(S.alloc(right, sizeof(uint32_t) * n)); CK(S.alloc(cnt, sizeof(uint32_t) * n));
     CK(S.alloc(nlo, sizeof(float4) * 2 * (size_t) n)); CK(S.alloc(nhi, sizeof(float4) * 2 * (size_t) n));
-    if (n > 1) k_karras<<<G, T, 0, st>>>(keys, (int) n, left, right, parent, range);
-    else { CK(cudaMemsetAsync(parent, 0xff, 4, st)); }
     CK(S.alloc(cost, sizeof(float) * 7 * (size_t) n)); CK(S.alloc(dec, sizeof(uint2) * (size_t) n));
-    k_refit<<<G, T, 0, st>>>(blo, bhi, vals, (int) n, left, right, parent, range, nlo, nhi, flags, cost, dec, c_node, c_prim);
+    if (builder == 0 || n < 2) {
+        CK(S.alloc(parent, sizeof(uint32_t) * 2 * (size_t) n));
+        CK(S.alloc(flags, sizeof(uint32_t) * n)); CK(cudaMemsetAsync(flags, 0, sizeof(uint32_t) * n, st));
+        if (n > 1) k_karras<<<G, T, 0, st>>>(keys, (int) n, left, right, parent, cnt);
+        else { CK(cudaMemsetAsync(parent, 0xff, 4, st)); }
+        k_refit<<<G, T, 0, st>>>(blo, bhi, vals, (int) n, left, right, parent, cnt, nlo, nhi, flags, cost, dec, c_node, c_prim);
+    } else {
+        const char *e_r = getenv("B2_PLOC_RADIUS");
+        const int radius = std::max(1, e_r ? atoi(e_r) : 10);
+        uint32_t *cid, *cid2, *nn, *merged, *d_sel; void *sel_tmp; size_t sel_bytes = 0;
+        CK(S.alloc(cid, sizeof(uint32_t) * n)); CK(S.alloc(cid2, sizeof(uint32_t) * n)); CK(S.alloc(nn, sizeof(uint32_t) * n));
+        CK(S.alloc(merged, sizeof(uint32_t) * n)); CK(S.alloc(d_sel, 2 * sizeof(uint32_t)));
+        CK(cub::DeviceSelect::If(nullptr, sel_bytes, merged, cid2, d_sel, (int) n, NotRemoved(), st));
+        CK(S.alloc(sel_tmp, sel_bytes));
+        CK(cudaMemsetAsync(d_sel, 0, 2 * sizeof(uint32_t), st));
+        k_ploc_init<<<G, T, 0, st>>>(blo, bhi, vals, n, nlo, nhi, cid);
+        uint32_t nc = n, iters = 0;
+        while (nc > 1) {
+            const uint32_t g = (nc + T - 1) / T;
+            k_ploc_nn<<<g, T, 0, st>>>(cid, nc, n, nlo, nhi, radius, nn);
+            k_ploc_merge<<<g, T, 0, st>>>(cid, nc, n, nn, left, right, cnt, nlo, nhi, d_sel + 1, cost, dec, c_node, c_prim, merged);
+            CK(cub::DeviceSelect::If(sel_tmp, sel_bytes, merged, cid2, d_sel, (int) nc, NotRemoved(), st));
+            uint32_t nc_new = 0;
+            CK(cudaMemcpyAsync(&nc_new, d_sel, 4, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            if (nc_new >= nc || nc_new == 0) { err = "bvh_build: PLOC made no progress"; return false; }
+            nc = nc_new; std::swap(cid, cid2);
+            if (++iters > 100000u) { err = "bvh_build: PLOC iteration limit"; return false; }
+        }
+    }
     CK(cudaEventRecord(S.ev[2], st));
     // collapse, one launch per level of the wide tree
     CK(S.alloc(nodes, sizeof(uint4) * 5 * (size_t) max_nodes)); CK(S.alloc(tris, sizeof(float4) * 3 * (size_t) n));
@@ -393,7 +481,7 @@ bool bvh_build(const float *pos, const uint32_t *faces, const uint32_t *face_mes
     CK(cudaMemcpyAsync(counters, host_counters, sizeof(host_counters), cudaMemcpyHostToDevice, st));
     { uint32_t root_ref = n > 1 ? 0u : (0u | kLeafFlag); CK(cudaMemcpyAsync(w2b, &root_ref, 4, cudaMemcpyHostToDevice, st)); CK(cudaStreamSynchronize(st)); }
     {
-        CollapseArgs ca{ pos, faces, face_mesh, vals, left, right, range, nlo, nhi, use_dp ? dec : nullptr, w2b, nodes, tris, counters, n, max_nodes };
+        CollapseArgs ca{ pos, faces, face_mesh, vals, left, right, cnt, nlo, nhi, use_dp ? dec : nullptr, w2b, nodes, tris, counters, n, max_nodes };
         while (level_begin < level_end) {
             uint32_t cnt = level_end - level_begin;
             k_collapse<<<(cnt + 127) / 128, 128, 0, st>>>(ca, level_begin, level_end);
@@ -402,6 +490,11 @@ bool bvh_build(const float *pos, const uint32_t *faces, const uint32_t *face_mes
             if (host_counters[2]) { err = "bvh_build: wide node pool exhausted"; return false; }
             level_begin = level_end; level_end = host_counters[0]; depth++;
         }
+    }
+    float root_cost = 0.f; float4 root_lo = make_float4(0, 0, 0, 0), root_hi = root_lo;
+    if (n > 1) {
+        CK(cudaMemcpyAsync(&root_cost, cost, 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(&root_lo, nlo, 16, cudaMemcpyDeviceToHost, st)); CK(cudaMemcpyAsync(&root_hi, nhi, 16, cudaMemcpyDeviceToHost, st));
     }
     CK(S.alloc(nodes_final, sizeof(uint4) * 5 * (size_t) host_counters[0]));
     CK(cudaMemcpyAsync(nodes_final, nodes, sizeof(uint4) * 5 * (size_t) host_counters[0], cudaMemcpyDeviceToDevice, st));
@@ -413,6 +506,10 @@ bool bvh_build(const float *pos, const uint32_t *faces, const uint32_t *face_mes
     out.node_bytes = sizeof(uint4) * 5 * (size_t) out.n_nodes; out.tri_bytes = sizeof(float4) * 3 * (size_t) n;
     cudaEventElapsedTime(&out.ms_morton_sort, S.ev[0], S.ev[1]); cudaEventElapsedTime(&out.ms_lbvh, S.ev[1], S.ev[2]);
     cudaEventElapsedTime(&out.ms_collapse, S.ev[2], S.ev[3]); cudaEventElapsedTime(&out.ms_total, S.ev[0], S.ev[3]);
+    {   // SAH cost of the collapsed tree (the DP's optimum at the root), in units of c_node per unit of root area
+        float dx = root_hi.x - root_lo.x, dy = root_hi.y - root_lo.y, dz = root_hi.z - root_lo.z, A = dx * dy + dy * dz + dz * dx;
+        out.sah_cost = A > 0.f ? root_cost / A : 0.f; out.builder = (builder == 0 || n < 2) ? 0 : 1;
+    }
     S.release(tris); S.release(nodes_final);
     return true;
 }

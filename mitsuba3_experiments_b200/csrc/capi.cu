@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -23,6 +24,7 @@ struct b2_scene {
     b2_ctx *ctx = nullptr;
     DScene d{};
     Bvh bvh;
+    float *host_film = nullptr, *host_image = nullptr;   // device staging of b2_render_host
     std::vector<void *> allocs;
     std::vector<b2_bsdf> bsdfs;                 // host mirror (for set_param / grad target validation)
     std::vector<DTexture> textures;             // host mirror of the device texture records
@@ -187,15 +189,28 @@ void b2_scene_destroy(b2_scene *scene) {
 
 int b2_scene_build_accel(b2_scene *s, int builder, uintptr_t stream, b2_build_stats *stats) {
     if (!s) return fail(-1, "b2_scene_build_accel: null scene");
-    if (builder != 0) return fail(-2, "b2_scene_build_accel: unknown builder (0 = LBVH -> compressed 8-wide)");
+    if (builder == B2_BUILDER_DEFAULT) { const char *e = getenv("B2_BVH_BUILDER"); builder = e ? atoi(e) : B2_BUILDER_AUTO; }
+    if (builder != B2_BUILDER_LBVH && builder != B2_BUILDER_PLOC && builder != B2_BUILDER_AUTO) return fail(-2, "b2_scene_build_accel: unknown builder (0 = LBVH, 1 = PLOC, 2 = both + SAH pick, -1 = default)");
     CUDA_OK(cudaSetDevice(s->ctx->device));
     bvh_free(s->bvh);
     std::string err;
-    if (!bvh_build(s->d.pos, s->d.faces, s->face_mesh_dev, s->d.n_faces, (cudaStream_t) stream, s->bvh, err)) return fail(-11, err);
+    if (builder == B2_BUILDER_AUTO) {
+        // build both trees and keep the one the SAH model prefers (the build is a few ms; the render traces it for seconds)
+        Bvh a, b;
+        if (!bvh_build(s->d.pos, s->d.faces, s->face_mesh_dev, s->d.n_faces, B2_BUILDER_LBVH, (cudaStream_t) stream, a, err)) return fail(-11, err);
+        if (!bvh_build(s->d.pos, s->d.faces, s->face_mesh_dev, s->d.n_faces, B2_BUILDER_PLOC, (cudaStream_t) stream, b, err)) { bvh_free(a); return fail(-11, err); }
+        // PLOC's clusters are not octant-shaped, so the slot ^ octant child order is less strictly front to back than on
+        // the radix tree: it has to win the SAH estimate by 10 % (bedroom stand-in: 0.78 -> PLOC, +13 % Msamples/s;
+        // 10 M random triangles: 0.98 -> LBVH, where PLOC measured 11 % slower; profiles/README.md)
+        const bool keep_a = !(b.sah_cost < 0.9f * a.sah_cost);
+        const float ms = a.ms_total + b.ms_total;
+        if (keep_a) { bvh_free(b); s->bvh = a; } else { bvh_free(a); s->bvh = b; }
+        s->bvh.ms_total = ms;
+    } else if (!bvh_build(s->d.pos, s->d.faces, s->face_mesh_dev, s->d.n_faces, builder, (cudaStream_t) stream, s->bvh, err)) return fail(-11, err);
     s->d.nodes = s->bvh.nodes; s->d.tris = s->bvh.tris; s->d.n_nodes = s->bvh.n_nodes;
     if (stats) {
         stats->ms_morton_sort = s->bvh.ms_morton_sort; stats->ms_lbvh = s->bvh.ms_lbvh; stats->ms_collapse = s->bvh.ms_collapse; stats->ms_total = s->bvh.ms_total;
-        stats->n_nodes8 = s->bvh.n_nodes; stats->n_tris = s->bvh.n_tris; stats->max_depth = s->bvh.depth;
+        stats->n_nodes8 = s->bvh.n_nodes; stats->n_tris = s->bvh.n_tris; stats->max_depth = s->bvh.depth; stats->builder = (uint32_t) s->bvh.builder; stats->sah_cost = s->bvh.sah_cost; stats->reserved = 0.f;
         stats->node_bytes = s->bvh.node_bytes; stats->tri_bytes = s->bvh.tri_bytes;
     }
     return 0;
@@ -431,19 +446,18 @@ int b2_render_host(b2_scene *s, const b2_render_args *a, float *film_host, float
     if (!s || !a || !film_host) return fail(-1, "b2_render_host: null argument");
     CUDA_OK(cudaSetDevice(s->ctx->device));
     const size_t npix = (size_t) s->d.sensor.crop_width * s->d.sensor.crop_height;
-    float *film = nullptr, *image = nullptr;
-    CUDA_OK(cudaMalloc((void **) &film, npix * 16));
-    cudaError_t e = cudaMalloc((void **) &image, npix * 12);
-    if (e != cudaSuccess) { cudaFree(film); return fail(-10, cudaGetErrorString(e)); }
-    int rc = 0;
-    auto guard = [&](cudaError_t err) { if (err != cudaSuccess && rc == 0) rc = fail(-10, cudaGetErrorString(err)); };
-    guard(cudaMemcpy(film, film_host, npix * 16, cudaMemcpyHostToDevice));
-    if (rc == 0) rc = b2_render(s, a, film, 0, counters);
-    if (rc == 0 && image_host) rc = b2_develop(s, film, image, 0);
-    if (rc == 0) guard(cudaMemcpy(film_host, film, npix * 16, cudaMemcpyDeviceToHost));
-    if (rc == 0 && image_host) guard(cudaMemcpy(image_host, image, npix * 12, cudaMemcpyDeviceToHost));
-    cudaFree(film); cudaFree(image);
-    return rc;
+    // staging buffers live with the scene (allocated on first use): no allocator call per render
+    if (!s->host_film) { CUDA_OK(cudaMalloc((void **) &s->host_film, npix * 16)); s->allocs.push_back(s->host_film); }
+    if (image_host && !s->host_image) { CUDA_OK(cudaMalloc((void **) &s->host_image, npix * 12)); s->allocs.push_back(s->host_image); }
+    cudaStream_t st = 0;
+    CUDA_OK(cudaMemcpyAsync(s->host_film, film_host, npix * 16, cudaMemcpyHostToDevice, st));
+    int rc = b2_render(s, a, s->host_film, (uintptr_t) st, counters);
+    if (rc == 0 && image_host) rc = b2_develop(s, s->host_film, s->host_image, (uintptr_t) st);
+    if (rc != 0) return rc;
+    CUDA_OK(cudaMemcpyAsync(film_host, s->host_film, npix * 16, cudaMemcpyDeviceToHost, st));
+    if (image_host) CUDA_OK(cudaMemcpyAsync(image_host, s->host_image, npix * 12, cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    return 0;
 }
 
 }  // extern "C"

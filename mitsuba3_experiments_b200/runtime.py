@@ -37,7 +37,7 @@ def as_device_tensor(x, device, dtype=None):
 class DeviceScene:
     """Owns a ``b2_scene`` on one CUDA device."""
 
-    def __init__(self, scene, device: int = 0, base_path: str = "."):
+    def __init__(self, scene, device: int = 0, base_path: str = ".", builder: int = -1):
         torch = _torch()
         self.lib = capi.load_library()
         if not torch.cuda.is_available():
@@ -49,7 +49,7 @@ class DeviceScene:
         self.handle = C.c_void_p()
         capi.check(self.lib.b2_scene_create(self.ctx, C.byref(self.desc.c), C.byref(self.handle)))
         self.build_stats = capi.BuildStats()
-        capi.check(self.lib.b2_scene_build_accel(self.handle, 0, self._stream(), C.byref(self.build_stats)))
+        capi.check(self.lib.b2_scene_build_accel(self.handle, builder, self._stream(), C.byref(self.build_stats)))
 
     def close(self):
         if getattr(self, "handle", None):
@@ -70,8 +70,8 @@ class DeviceScene:
     def film_shape(self):
         return self.desc.film_shape
 
-    def rebuild_accel(self):
-        capi.check(self.lib.b2_scene_build_accel(self.handle, 0, self._stream(), C.byref(self.build_stats)))
+    def rebuild_accel(self, builder=-1):
+        capi.check(self.lib.b2_scene_build_accel(self.handle, builder, self._stream(), C.byref(self.build_stats)))
         return self.build_stats.as_dict()
 
     def make_args(self, seed=0, spp=None, max_depth=8, rr_depth=4, variant=capi.VARIANT_PATH, spp_per_pass=0,

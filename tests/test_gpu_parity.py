@@ -42,11 +42,15 @@ def random_rays(n, seed, extent=1.5):
     return np.concatenate([o, d, maxt[:, None], np.zeros((n, 1))], axis=1).astype(np.float32)
 
 
+BUILDERS = [pytest.param(0, id="lbvh"), pytest.param(1, id="ploc")]
+
+
+@pytest.mark.parametrize("builder", BUILDERS)
 @pytest.mark.parametrize("scene_name", ["cornell", "soup"])
-def test_trace_bit_exact(scene_name):
+def test_trace_bit_exact(scene_name, builder):
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
     d = cornell_box(16, 16) if scene_name == "cornell" else triangles_scene(30000)
-    ds = DeviceScene(d); orc = OracleScene(ds.desc)
+    ds = DeviceScene(d, builder=builder); orc = OracleScene(ds.desc)
     rays = random_rays(200000, 11, 0.95 if scene_name == "cornell" else 1.5)
     g, c = ds.trace(rays), orc.trace(rays)
     assert np.array_equal(g["prim"], c["prim"])
@@ -58,8 +62,11 @@ def test_trace_bit_exact(scene_name):
     assert np.array_equal(ga["prim"], ca["prim"])
 
 
-def test_bvh_stats_and_edge_cases():
+@pytest.mark.parametrize("builder", BUILDERS)
+def test_bvh_stats_and_edge_cases(builder):
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    from functools import partial
+    DeviceScene = partial(DeviceScene, builder=builder)
     ds = DeviceScene(cornell_box(8, 8))
     st = ds.build_stats.as_dict()
     assert st["n_tris"] == 36 and st["n_nodes8"] >= 1 and st["node_bytes"] == 80 * st["n_nodes8"] and st["tri_bytes"] == 48 * 36
