@@ -30,7 +30,7 @@ constexpr int kFetchBatch = 96;        // rays a warp takes from the global coun
 #define B2_SHADE_MINBLOCKS 3
 #endif
 #ifndef B2_TRACE_SLICE
-#define B2_TRACE_SLICE 5               // traversal steps between two refill points
+#define B2_TRACE_SLICE 8               // traversal micro-steps between two refill points (re-tuned on the PLOC tree: 5 -> 8, +3 %)
 #endif
 
 // ------------------------------------------------------------------------------------------ state <-> registers
@@ -507,10 +507,21 @@ void wf_collect_timing(WfTiming &t, double ms[WF_K_COUNT], uint64_t n[WF_K_COUNT
 // tuning knobs (environment overrides are for sweeps on the GPU box; the defaults are the measured optimum)
 static int env_int(const char *name, int def) { const char *v = getenv(name); return v ? std::max(1, atoi(v)) : def; }
 static const uint32_t tune_slice = (uint32_t) env_int("B2_TRACE_SLICE", B2_TRACE_SLICE);
-static const uint32_t tune_tri = (uint32_t) env_int("B2_TRI_THRESH", 8);
+static const uint32_t tune_tri = (uint32_t) env_int("B2_TRI_THRESH", 10);
 static const uint32_t tune_prefetch = (uint32_t) env_int("B2_PREFETCH", 1);
 static const int tune_trace_blocks = getenv("B2_TRACE_BLOCKS") ? atoi(getenv("B2_TRACE_BLOCKS")) : 0;
 static const int tune_sort = getenv("B2_SHADE_SORT") ? atoi(getenv("B2_SHADE_SORT")) : -1;   // 0/1 force, -1 = by scene content
+
+// resident blocks per SM of one kernel instantiation (queried once): every shade specialisation gets the grid its own
+// register count allows (the diffuse kernels fit 4 blocks/SM, the glossy ones 3)
+template <auto Kern> static int occ_of() {
+    static const int occ = [] { int o = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, Kern, 256, 0); return std::max(o, 1); }();
+    return occ;
+}
+static const int tune_shade_mult = getenv("B2_SHADE_GRID_MULT") ? std::max(1, atoi(getenv("B2_SHADE_GRID_MULT"))) : 1;
+#define B2_SHADE_LAUNCH(...) do { constexpr auto kern_ = k_wf_shade<__VA_ARGS__>; \
+    const int g_ = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_of<kern_>() * sm_count * tune_shade_mult); \
+    tm_begin(WF_K_SHADE, stream); kern_<<<g_, 256, 0, stream>>>(p, w); tm_end(stream); launches++; } while (0)
 
 template <int V, bool COUNT>
 static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {
@@ -544,16 +555,16 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
                 const uint32_t cmask = st.class_mask;
                 const bool sort = tune_sort >= 0 ? tune_sort != 0     // default: sort when the BSDFs differ enough to diverge
                                                  : (__builtin_popcount(cmask) >= 2 && (cmask & ((1u << CLS_CONDUCTOR) | (1u << CLS_DIELECTRIC))) != 0);
-                if (!sort && cmask == (1u << CLS_DIFFUSE)) { tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false, CLS_DIFFUSE, false><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++; }
+                if (!sort && cmask == (1u << CLS_DIFFUSE)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_DIFFUSE, false);
                 else if (sort) {
                     tm_begin(WF_K_SHADE, stream); k_wf_classify<<<g_shade, 256, 0, stream>>>(w); tm_end(stream); launches++;
                     const uint32_t cm = st.class_mask;
-                    if (cm & (1u << CLS_DIFFUSE)) { tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false, CLS_DIFFUSE><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++; }
-                    if (cm & (1u << CLS_DIFFUSE_TEX)) { tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false, CLS_DIFFUSE_TEX><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++; }
-                    if (cm & (1u << CLS_CONDUCTOR)) { tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false, CLS_CONDUCTOR><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++; }
-                    if (cm & (1u << CLS_DIELECTRIC)) { tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false, CLS_DIELECTRIC><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++; }
-                    tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false, CLS_MISS><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++;
-                } else { tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++; }
+                    if (cm & (1u << CLS_DIFFUSE)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_DIFFUSE);
+                    if (cm & (1u << CLS_DIFFUSE_TEX)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_DIFFUSE_TEX);
+                    if (cm & (1u << CLS_CONDUCTOR)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_CONDUCTOR);
+                    if (cm & (1u << CLS_DIELECTRIC)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_DIELECTRIC);
+                    B2_SHADE_LAUNCH(V, COUNT, false, CLS_MISS);
+                } else B2_SHADE_LAUNCH(V, COUNT);
                 ++it;
                 if (!bounded && (k & 3u) == 3u) {       // unbounded depth: Russian roulette ends the paths; poll the live count
                     uint32_t live = 0;
@@ -604,7 +615,7 @@ static long wf_render_backward_t(RenderParams p, WfState &st, int sm_count, cuda
         for (uint32_t k = 0; k < n_iter; ++k) {
             w.it = it; w.vis_bit = k ? k - 1u : 0xffffffffu;
             tm_begin(WF_K_TRACE, stream); k_wf_trace<COUNT><<<g_trace, kTraceThreads, 0, stream>>>(p.sc, w, p.counters); tm_end(stream); launches++;
-            tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, false><<<g_shade, 256, 0, stream>>>(p, w); tm_end(stream); launches++;
+            B2_SHADE_LAUNCH(V, COUNT, false);
             ++it;
         }
         w.it = it; w.vis_bit = n_iter - 1u;
