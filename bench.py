@@ -280,7 +280,7 @@ def main():
                      "algorithmic_bytes_per_launch": tr_bytes_step / max(tr_n // max(args.steps, 1), 1), "bytes_per_ray": b_ray, "peak_kind": peak_kind,
                      "whole_step": {"achieved": step_gbs, "frac": step_gbs / peak, "algorithmic_bytes": alg_bytes, "render_ms": kernel_ms,
                                     "ms_per_step_by_kind": {k: v[0] / max(args.steps, 1) for k, v in ktimes.items()}},
-                     "note": "irregular gathers: nodes + triangles (108 MB) stay L2-resident on B200, so DRAM traffic is below the algorithmic bytes; the kernel is issue-bound (ncu: 66-75 % issue slots busy), see DESIGN.md"},
+                     "note": "irregular gathers: nodes + triangles (100 MB) stay L2-resident on B200, so DRAM traffic is below the algorithmic bytes; ncu: issue slots 66 % busy, ALU pipe 55-72 %, 44 % of stall cycles long-scoreboard (profiles/r01_v4_*), see DESIGN.md 4.3"},
     }
     if world == 1 and not args.no_cpu_baseline:
         v1, dt1, cores, n1 = cpu_oracle_rate(scene_dict, kw, 1)              # calibrate, then ~15 s of CPU work

@@ -41,7 +41,8 @@ extern "C" {
 #define B2_ABI_VERSION 1
 
 /* ------------------------------------------------------------------ enums */
-enum { B2_BSDF_DIFFUSE = 0, B2_BSDF_ROUGHCONDUCTOR = 1, B2_BSDF_DIELECTRIC = 2 };
+enum { B2_BSDF_DIFFUSE = 0, B2_BSDF_ROUGHCONDUCTOR = 1, B2_BSDF_DIELECTRIC = 2,
+       B2_BSDF_CONDUCTOR = 3 /* smooth conductor (conductor.cpp:249-307), SURVEY 8(f) rank 1 */ };
 enum { B2_BSDF_FLAG_TWOSIDED = 1 };           /* wrapped in a `twosided` adapter (twosided.cpp:110-260) */
 enum { B2_MF_BECKMANN = 0, B2_MF_GGX = 1 };   /* MicrofacetType (microfacet.h) */
 enum { B2_TEX_F32 = 0, B2_TEX_F16 = 1 };      /* storage (bitmap.cpp:231-246) */

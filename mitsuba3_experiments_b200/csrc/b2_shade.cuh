@@ -28,7 +28,8 @@ enum { LOBE_DIFFUSE = 1, LOBE_GLOSSY = 2, LOBE_DELTA_R = 4, LOBE_DELTA_T = 8,
 enum { CLS_GENERIC = -1, CLS_DIFFUSE = 0, CLS_DIFFUSE_TEX = 1, CLS_CONDUCTOR = 2, CLS_DIELECTRIC = 3, CLS_MISS = 4, CLS_COUNT = 5 };
 template <int CLS> B2_DEV int cls_type(int runtime_type) {
     return (CLS == CLS_DIFFUSE || CLS == CLS_DIFFUSE_TEX) ? B2_BSDF_DIFFUSE : CLS == CLS_CONDUCTOR ? B2_BSDF_ROUGHCONDUCTOR
-           : CLS == CLS_DIELECTRIC ? B2_BSDF_DIELECTRIC : runtime_type;
+           : CLS == CLS_DIELECTRIC ? (runtime_type == B2_BSDF_CONDUCTOR ? B2_BSDF_CONDUCTOR : B2_BSDF_DIELECTRIC)   // the delta class
+           : runtime_type;
 }
 template <int CLS> B2_DEV bool cls_textured(int tex) { return CLS == CLS_DIFFUSE ? false : CLS == CLS_DIFFUSE_TEX ? true : tex >= 0; }
 
@@ -329,6 +330,13 @@ B2_DEV void bsdf_sample(const DBsdf &b, f3 wi_in, float s1, f2 s2, RF &&refl, BS
             const f3 F = fresnel_conductor3(dot(wi, m), b);
             const f3 wv = f3(w) * refl();
             if (active) weight = F * wv;
+        }
+    } else if (type == B2_BSDF_CONDUCTOR) {
+        // SmoothConductor::sample (conductor.cpp:249-307)
+        if (ci > 0.f) {
+            bs.wo = f3(-wi.x, -wi.y, wi.z);
+            bs.pdf = 1.f; bs.eta = 1.f; bs.type = LOBE_DELTA_R;
+            weight = refl() * fresnel_conductor3(ci, b);
         }
     } else {
         float r_i, cos_t, eta_it, eta_ti; fresnel(ci, b.ior, r_i, cos_t, eta_it, eta_ti);

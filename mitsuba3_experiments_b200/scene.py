@@ -7,7 +7,7 @@ Mitsuba plugins, so this module understands the same dictionary schema for the p
 
 * shapes ``rectangle`` (rectangle.cpp:102-176), ``cube`` (cube.cpp:105-163), ``obj`` (obj.cpp subset) and a raw
   ``mesh`` (explicit arrays) -> world-space vertex/normal/uv/face buffers (Mesh layout, mesh.h:564-568)
-* bsdfs ``diffuse``, ``roughconductor``, ``dielectric``, ``twosided`` (single nested BRDF), ``ref``
+* bsdfs ``diffuse``, ``roughconductor``, ``conductor``, ``dielectric``, ``twosided`` (single nested BRDF), ``ref``
 * textures ``rgb`` / plain lists, ``bitmap`` (filename | data array; fp16 storage rule of bitmap.cpp:231-246)
 * emitters ``area``, ``envmap`` (Hierarchical2D pyramid, distr_2d.h:403-509), ``constant``
 * sensor ``perspective`` (perspective.cpp:173-199, sensor.h:229-265, sensor.cpp:147-200), ``hdrfilm``,
@@ -383,6 +383,12 @@ class SceneDesc:
             else:
                 b.alpha_u = b.alpha_v = float(spec.get("alpha", 0.1))
             self._reflectance(b, spec.get("specular_reflectance"), 1.0)
+        elif t == "conductor":
+            b.type = capi.BSDF_CONDUCTOR                       # conductor.cpp:228-239: eta = 0, k = 1 when material == "none"
+            if spec.get("material", "none") != "none" and "eta" not in spec:
+                raise ValueError("conductor: named materials need Mitsuba's ior database; pass eta/k")
+            b.eta[:] = _rgb(spec.get("eta"), 0.0).tolist(); b.k[:] = _rgb(spec.get("k"), 1.0).tolist()
+            self._reflectance(b, spec.get("specular_reflectance"), 1.0)
         elif t == "dielectric":
             if flags & capi.BSDF_FLAG_TWOSIDED:
                 raise ValueError("Only materials without a transmission component can be nested!")
@@ -395,7 +401,7 @@ class SceneDesc:
             b.reflectance[:] = _rgb(spec.get("specular_reflectance"), 1.0).tolist()
             b.transmittance[:] = _rgb(spec.get("specular_transmittance"), 1.0).tolist()
         else:
-            raise ValueError(f"unsupported BSDF type {t!r} (hot-path scope: diffuse, roughconductor, dielectric, twosided)")
+            raise ValueError(f"unsupported BSDF type {t!r} (hot-path scope: diffuse, roughconductor, conductor, dielectric, twosided)")
         self.bsdfs.append(b)
         idx = len(self.bsdfs) - 1
         self.bsdf_names.append(name or f"__bsdf{idx}")
@@ -552,7 +558,7 @@ class SceneDesc:
             if not isinstance(v, dict):
                 continue
             t = v.get("type")
-            if t in ("diffuse", "roughconductor", "dielectric", "twosided"):
+            if t in ("diffuse", "roughconductor", "conductor", "dielectric", "twosided"):
                 self._add_bsdf(v, name)
         for name, v in d.items():   # declaration order defines the emitter order (scene.cpp:26-66)
             if not isinstance(v, dict):
@@ -570,7 +576,7 @@ class SceneDesc:
             elif t in ("path", "prb", "mypath", "path_test", "b2path", "b2path_mis", "b2prb"):
                 self.integrator_props = {k: v[k] for k in v if k != "type"}
                 self.integrator_props["type"] = t
-            elif t in ("diffuse", "roughconductor", "dielectric", "twosided"):
+            elif t in ("diffuse", "roughconductor", "conductor", "dielectric", "twosided"):
                 pass
             else:
                 raise ValueError(f"unsupported scene element {name!r} of type {t!r}")

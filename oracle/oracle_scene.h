@@ -476,7 +476,8 @@ static inline void bsdf_eval_pdf(const Scene &sc, const b2_bsdf &b, const SI &si
 }
 
 // SmoothDiffuse::sample (diffuse.cpp:100-124), RoughConductor::sample (roughconductor.cpp:227-313),
-// SmoothDielectric::sample (dielectric.cpp:245-370), TwoSidedBRDF::sample (twosided.cpp:110-147)
+// SmoothDielectric::sample (dielectric.cpp:245-370), SmoothConductor::sample (conductor.cpp:249-307),
+// TwoSidedBRDF::sample (twosided.cpp:110-147)
 static inline void bsdf_sample(const Scene &sc, const b2_bsdf &b, const SI &si_, float s1, V2 s2, BS &bs, V3 &weight, Counters &c) {
     SI si = si_;
     bs = BS(); weight = V3(0.f);
@@ -503,6 +504,14 @@ static inline void bsdf_sample(const Scene &sc, const b2_bsdf &b, const SI &si_,
             V3 F(fresnel_conductor(cm, b.eta[0], b.k[0]), fresnel_conductor(cm, b.eta[1], b.k[1]), fresnel_conductor(cm, b.eta[2], b.k[2]));
             V3 wv = V3(w) * sc.reflectance(b, si, c);
             if (active) weight = F * wv;
+        }
+    } else if (b.type == B2_BSDF_CONDUCTOR) {
+        // SmoothConductor::sample (bsdfs/conductor.cpp:249-307): delta reflection, weight = specular_reflectance * F(cos_i)
+        if (ci > 0.f) {
+            bs.wo = V3(-si.wi.x, -si.wi.y, si.wi.z);                  // reflect(wi)
+            bs.pdf = 1.f; bs.eta = 1.f; bs.type = LOBE_DELTA_R;
+            V3 F(fresnel_conductor(ci, b.eta[0], b.k[0]), fresnel_conductor(ci, b.eta[1], b.k[1]), fresnel_conductor(ci, b.eta[2], b.k[2]));
+            weight = sc.reflectance(b, si, c) * F;
         }
     } else { // dielectric (never two-sided)
         float r_i, cos_t, eta_it, eta_ti; fresnel(ci, b.ior, r_i, cos_t, eta_it, eta_ti);

@@ -49,6 +49,10 @@ def materials_scene(width=48, height=40, spp=8, envmap=True, filter_type="gaussi
     d["back"]["bsdf"] = {"type": "ref", "id": "tex"}
     d["floor"]["bsdf"] = {"type": "ref", "id": "tex16"}
     d["red-wall"]["bsdf"] = {"type": "ref", "id": "beck"}
+    # smooth conductor (delta reflection), copper-like eta/k, tinted specular_reflectance, twosided
+    d["mirror"] = {"type": "twosided", "nested": {"type": "conductor", "eta": [0.27, 0.68, 1.32], "k": [3.6, 2.62, 2.29],
+                                                   "specular_reflectance": [0.9, 0.95, 1.0]}}
+    d["green-wall"]["bsdf"] = {"type": "ref", "id": "mirror"}
     if mesh_light:
         pos = np.array([[-0.6, 0.2, -0.6], [-0.3, 0.2, -0.6], [-0.45, 0.45, -0.5], [-0.45, 0.3, -0.3]], np.float32)
         faces = np.array([[0, 1, 2], [0, 3, 1], [1, 3, 2], [0, 2, 3]], np.uint32)
@@ -75,4 +79,20 @@ def triangles_scene(n_tris=20000, width=64, height=48, spp=4, seed=3):
         "light": {"type": "rectangle", "to_world": T().translate([0, 1.4, 0]).rotate([1, 0, 0], 90).scale(0.5),
                   "emitter": {"type": "area", "radiance": {"type": "rgb", "value": [50, 50, 50]}}},
         "sky": {"type": "constant", "radiance": {"type": "rgb", "value": [0.4, 0.5, 0.6]}},
+    }
+
+
+def mirror_scene(width=16, height=16, spp=4, tilt_deg=30.0, eta=(0.2, 0.92, 1.1), k=(3.9, 2.45, 2.14), refl=(0.9, 0.8, 0.7), radiance=(1.0, 2.0, 3.0)):
+    """Known-answer scene for the smooth conductor: a huge mirror under a constant environment.  Every camera ray hits the
+    mirror once and escapes, so radiance(pixel) = specular_reflectance * F_conductor(cos_i; eta, k) * radiance, with
+    cos_i = dot(-d, n) known in closed form per pixel (conductor.cpp:249-307, fresnel.h:92-117)."""
+    return {
+        "type": "scene",
+        "sensor": {"type": "perspective", "fov": 20, "near_clip": 0.01, "far_clip": 100.0,
+                   "to_world": T().look_at([0, 0, 4], [0, 0, 0], [0, 1, 0]),
+                   "sampler": {"type": "independent", "sample_count": spp},
+                   "film": {"type": "hdrfilm", "width": width, "height": height, "rfilter": {"type": "box"}}},
+        "m": {"type": "conductor", "eta": list(eta), "k": list(k), "specular_reflectance": list(refl)},
+        "plane": {"type": "rectangle", "to_world": T().rotate([1, 0, 0], tilt_deg).scale(50.0), "bsdf": {"type": "ref", "id": "m"}},
+        "env": {"type": "constant", "radiance": {"type": "rgb", "value": list(radiance)}},
     }

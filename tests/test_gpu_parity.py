@@ -283,3 +283,23 @@ def test_autograd_render_op():
     loss.backward()
     g = params["red.reflectance.value"].grad
     assert g is not None and torch.isfinite(g).all() and (g.abs() > 0).any()
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_smooth_conductor_known_answer_and_parity(kernel):
+    """smooth conductor.  CUDA == oracle on the mirror scene, and both == the closed form
+    specular_reflectance * fresnel_conductor(cos_i) * radiance (tests/test_oracle_golden.py::mirror_expected)."""
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    from scenes_for_tests import mirror_scene
+    from test_oracle_golden import mirror_expected
+    from oracle.oracle_py import lib
+    d = mirror_scene(16, 16, 64)
+    ds = DeviceScene(d); orc = OracleScene(ds.desc)
+    for variant in (0, 1):
+        kw = dict(seed=0, spp=64, max_depth=4, rr_depth=8, variant=variant)
+        img, cnt = ds.render(counters=True, kernel=kernel, **kw)
+        ref, rc = orc.render(**kw)
+        check_image(img.cpu().numpy(), ref, 0.999, 1e-4)
+        assert cnt["closest_rays"] == rc["closest_rays"] and cnt["shadow_rays"] == 0
+        exp = mirror_expected(d, lib())
+        assert np.abs(img.cpu().numpy() - exp).max() / exp.max() < 5e-3
