@@ -43,7 +43,8 @@ extern "C" {
 /* ------------------------------------------------------------------ enums */
 enum { B2_BSDF_DIFFUSE = 0, B2_BSDF_ROUGHCONDUCTOR = 1, B2_BSDF_DIELECTRIC = 2,
        B2_BSDF_CONDUCTOR = 3 /* smooth conductor (conductor.cpp:249-307), SURVEY 8(f) rank 1 */ };
-enum { B2_BSDF_FLAG_TWOSIDED = 1 };           /* wrapped in a `twosided` adapter (twosided.cpp:110-260) */
+enum { B2_BSDF_FLAG_TWOSIDED = 1,             /* wrapped in a `twosided` adapter (twosided.cpp:110-260) */
+       B2_BSDF_FLAG_MASK = 2 };               /* outermost `mask` adapter with constant `opacity` (mask.cpp:123-215), SURVEY 8(f) rank 1 */
 enum { B2_MF_BECKMANN = 0, B2_MF_GGX = 1 };   /* MicrofacetType (microfacet.h) */
 enum { B2_TEX_F32 = 0, B2_TEX_F16 = 1 };      /* storage (bitmap.cpp:231-246) */
 enum { B2_WRAP_REPEAT = 0, B2_WRAP_MIRROR = 1, B2_WRAP_CLAMP = 2 };
@@ -81,6 +82,7 @@ typedef struct b2_bsdf {
     float k[3];             /* conductor k */
     float alpha_u, alpha_v;
     float ior;              /* dielectric: int_ior / ext_ior */
+    float opacity;          /* B2_BSDF_FLAG_MASK: probability of interacting with the nested BSDF; else 1 */
 } b2_bsdf;
 
 typedef struct b2_mesh {

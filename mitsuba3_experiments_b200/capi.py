@@ -17,6 +17,7 @@ B2_MAX_WARP_LEVELS = 24
 # enums (keep in sync with b2path.h)
 BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC, BSDF_CONDUCTOR = 0, 1, 2, 3
 BSDF_FLAG_TWOSIDED = 1
+BSDF_FLAG_MASK = 2
 MF_BECKMANN, MF_GGX = 0, 1
 TEX_F32, TEX_F16 = 0, 1
 WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = 0, 1, 2
@@ -40,7 +41,7 @@ class Texture(C.Structure):
 class Bsdf(C.Structure):
     _fields_ = [("type", i32), ("flags", i32), ("reflectance_tex", i32), ("distribution", i32),
                 ("sample_visible", i32), ("reflectance", f32 * 3), ("transmittance", f32 * 3),
-                ("eta", f32 * 3), ("k", f32 * 3), ("alpha_u", f32), ("alpha_v", f32), ("ior", f32)]
+                ("eta", f32 * 3), ("k", f32 * 3), ("alpha_u", f32), ("alpha_v", f32), ("ior", f32), ("opacity", f32)]
 
 
 class Mesh(C.Structure):

@@ -222,7 +222,6 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
             s.rng.skip(6);
             return false;
         }
-        if (V == B2_VARIANT_PATH_MIS) s.valid_ray = true;
     }
 
     // ---- emitter sampling (NEE) + BSDF sampling.  si is valid from here on.
@@ -250,6 +249,7 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
         so->tex = tex;
     } else if (active_em) bsdf_eval_pdf<CLS>(bsdf, si.wi, wo, refl, bsdf_val, bsdf_pdf);
     bsdf_sample<CLS>(bsdf, si.wi, s1, s2, refl, bs, bsdf_weight);
+    if (V == B2_VARIANT_PATH_MIS && !(bs.type & LOBE_NULL)) s.valid_ray = true;            // path-mis.py:129-133
     const f3 f_before = s.f;
     float mis_em;
     if (V == B2_VARIANT_PATH) {

@@ -17,7 +17,8 @@ struct alignas(16) DBsdf {          // 64 B
     float refl[3]; int32_t sample_visible;
     float eta[3]; float alpha_u;
     float k[3]; float alpha_v;
-    float trans[3]; float ior;       // 80 B total
+    float trans[3]; float ior;
+    float opacity; float pad[3];     // mask adapter (B2_BSDF_FLAG_MASK); 96 B total
 };
 
 struct alignas(16) DTexture {

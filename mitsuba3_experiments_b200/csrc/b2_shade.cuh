@@ -19,8 +19,8 @@
 
 namespace b2 {
 
-enum { LOBE_DIFFUSE = 1, LOBE_GLOSSY = 2, LOBE_DELTA_R = 4, LOBE_DELTA_T = 8,
-       LOBE_SMOOTH = LOBE_DIFFUSE | LOBE_GLOSSY, LOBE_DELTA = LOBE_DELTA_R | LOBE_DELTA_T };
+enum { LOBE_DIFFUSE = 1, LOBE_GLOSSY = 2, LOBE_DELTA_R = 4, LOBE_DELTA_T = 8, LOBE_NULL = 16,
+       LOBE_SMOOTH = LOBE_DIFFUSE | LOBE_GLOSSY, LOBE_DELTA = LOBE_DELTA_R | LOBE_DELTA_T | LOBE_NULL };   // BSDFFlags::Delta includes Null
 
 // Shading classes: the wavefront sorts the hits of a bounce by class and runs one specialised shade kernel per class
 // (CLS >= 0 turns the BSDF-type switch and the textured/constant test into compile-time constants); CLS_GENERIC keeps
@@ -270,7 +270,8 @@ struct Microfacet {
 template <int CLS = CLS_GENERIC>
 B2_DEV uint32_t bsdf_lobes(const DBsdf &b) {
     const int type = cls_type<CLS>(b.type);
-    return type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : (type == B2_BSDF_ROUGHCONDUCTOR ? LOBE_GLOSSY : LOBE_DELTA);
+    const uint32_t l = type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : (type == B2_BSDF_ROUGHCONDUCTOR ? LOBE_GLOSSY : (LOBE_DELTA_R | LOBE_DELTA_T));
+    return (b.flags & B2_BSDF_FLAG_MASK) ? (l | LOBE_NULL) : l;      // mask.cpp:96-110
 }
 B2_DEV f3 fresnel_conductor3(float c, const DBsdf &b) {
     return f3(fresnel_conductor(c, b.eta[0], b.k[0]), fresnel_conductor(c, b.eta[1], b.k[1]), fresnel_conductor(c, b.eta[2], b.k[2]));
@@ -279,7 +280,7 @@ B2_DEV f3 fresnel_conductor3(float c, const DBsdf &b) {
 // eval_pdf.  `refl()` yields the (possibly textured) reflectance at si and is invoked exactly where the reference
 // evaluates it; pass a functor returning f3(1) to obtain the linear coefficient d value / d reflectance (PRB adjoint).
 template <int CLS = CLS_GENERIC, class RF>
-B2_DEV void bsdf_eval_pdf(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &val, float &pdf) {
+B2_DEV void bsdf_eval_pdf_nested(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &val, float &pdf) {
     val = f3(0.f); pdf = 0.f;
     if (b.flags & B2_BSDF_FLAG_TWOSIDED) { wo.z = mulsign(wo.z, wi.z); wi.z = fabsf(wi.z); }
     const float ci = wi.z, co = wo.z;
@@ -302,12 +303,24 @@ B2_DEV void bsdf_eval_pdf(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &val, floa
     }
 }
 
+// OpacityMask::eval_pdf (mask.cpp:196-215): nested value and pdf scaled by the opacity
+template <int CLS = CLS_GENERIC, class RF>
+B2_DEV void bsdf_eval_pdf(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &val, float &pdf) {
+    bsdf_eval_pdf_nested<CLS>(b, wi, wo, refl, val, pdf);
+    if (b.flags & B2_BSDF_FLAG_MASK) { val = val * b.opacity; pdf *= b.opacity; }
+}
+
 // sample.  Same lazy `refl()` convention as bsdf_eval_pdf.
 template <int CLS = CLS_GENERIC, class RF>
 B2_DEV void bsdf_sample(const DBsdf &b, f3 wi_in, float s1, f2 s2, RF &&refl, BS &bs, f3 &weight) {
     const int type = cls_type<CLS>(b.type);
     f3 wi = wi_in;
     bs.wo = f3(); bs.pdf = 0.f; bs.eta = 0.f; bs.type = 0u; weight = f3(0.f);
+    const bool masked = (b.flags & B2_BSDF_FLAG_MASK) != 0;
+    if (masked) {           // OpacityMask::sample (mask.cpp:123-171)
+        if (!(s1 < b.opacity)) { bs.wo = -wi_in; bs.eta = 1.f; bs.type = LOBE_NULL; bs.pdf = 1.f - b.opacity; weight = f3(1.f); return; }
+        s1 /= b.opacity;
+    }
     const bool two = (b.flags & B2_BSDF_FLAG_TWOSIDED) != 0;
     if (two) wi.z = fabsf(wi.z);
     const float ci = wi.z;
@@ -351,6 +364,7 @@ B2_DEV void bsdf_sample(const DBsdf &b, f3 wi_in, float s1, f2 s2, RF &&refl, BS
         else { weight *= f3(b.trans[0], b.trans[1], b.trans[2]); weight *= sqr(eta_ti); }
     }
     if (two) bs.wo.z = mulsign(bs.wo.z, wi_in.z);
+    if (masked) bs.pdf *= b.opacity;
 }
 
 // -------------------------------------------------------------------------------- environment map

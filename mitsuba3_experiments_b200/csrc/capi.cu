@@ -120,6 +120,8 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
         o.type = b.type; o.flags = b.flags; o.tex = b.reflectance_tex; o.distribution = b.distribution; o.sample_visible = b.sample_visible;
         for (int k = 0; k < 3; ++k) { o.refl[k] = b.reflectance[k]; o.eta[k] = b.eta[k]; o.k[k] = b.k[k]; o.trans[k] = b.transmittance[k]; }
         o.alpha_u = b.alpha_u; o.alpha_v = b.alpha_v; o.ior = b.ior;
+        o.opacity = (b.flags & B2_BSDF_FLAG_MASK) ? b.opacity : 1.f; o.pad[0] = o.pad[1] = o.pad[2] = 0.f;
+        if ((b.flags & B2_BSDF_FLAG_MASK) && !(b.opacity >= 0.f && b.opacity <= 1.f)) return fail(-2, "b2_scene_create: mask opacity outside [0, 1]");
     }
     CUDA_OK(s->upload(bs.data(), bs.size(), s->bsdfs_dev)); d.bsdfs = s->bsdfs_dev;
     // emitters

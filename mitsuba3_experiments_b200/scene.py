@@ -7,7 +7,7 @@ Mitsuba plugins, so this module understands the same dictionary schema for the p
 
 * shapes ``rectangle`` (rectangle.cpp:102-176), ``cube`` (cube.cpp:105-163), ``obj`` (obj.cpp subset) and a raw
   ``mesh`` (explicit arrays) -> world-space vertex/normal/uv/face buffers (Mesh layout, mesh.h:564-568)
-* bsdfs ``diffuse``, ``roughconductor``, ``conductor``, ``dielectric``, ``twosided`` (single nested BRDF), ``ref``
+* bsdfs ``diffuse``, ``roughconductor``, ``conductor``, ``dielectric``, ``twosided`` (single nested BRDF), ``mask`` (constant opacity, outermost), ``ref``
 * textures ``rgb`` / plain lists, ``bitmap`` (filename | data array; fp16 storage rule of bitmap.cpp:231-246)
 * emitters ``area``, ``envmap`` (Hierarchical2D pyramid, distr_2d.h:403-509), ``constant``
 * sensor ``perspective`` (perspective.cpp:173-199, sensor.h:229-265, sensor.cpp:147-200), ``hdrfilm``,
@@ -355,7 +355,19 @@ class SceneDesc:
         t = spec["type"]
         if t == "ref":
             return self.bsdf_ids[spec["id"]]
-        flags = 0
+        flags = 0; opacity = 1.0
+        if t == "mask":                                         # mask.cpp:72-95: one nested BSDF + `opacity`
+            nested = [v for k, v in spec.items() if isinstance(v, dict) and k != "opacity"]
+            if len(nested) != 1:
+                raise ValueError("mask: exactly one nested BSDF is supported")
+            op = spec.get("opacity", 0.5)
+            if isinstance(op, dict) and op.get("type") == "bitmap":
+                raise ValueError("mask: textured opacity is not supported (constant opacity only)")
+            opacity = float(np.clip(np.mean(_rgb(op, 0.5)), 0.0, 1.0))   # eval_opacity (mask.cpp:232-234): clip(texture value, 0, 1)
+            spec = nested[0]
+            if spec["type"] in ("ref", "mask"):
+                raise ValueError("mask: nested ref / mask not supported")
+            t = spec["type"]; flags |= capi.BSDF_FLAG_MASK
         if t == "twosided":
             nested = [v for k, v in spec.items() if isinstance(v, dict)]
             if len(nested) != 1:
@@ -365,7 +377,7 @@ class SceneDesc:
                 raise ValueError("twosided: nested ref not supported")
             t = spec["type"]; flags |= capi.BSDF_FLAG_TWOSIDED
         b = capi.Bsdf()
-        b.flags = flags; b.reflectance_tex = -1; b.sample_visible = 1
+        b.flags = flags; b.reflectance_tex = -1; b.sample_visible = 1; b.opacity = opacity
         b.reflectance[:] = [1, 1, 1]; b.transmittance[:] = [1, 1, 1]; b.eta[:] = [0, 0, 0]; b.k[:] = [1, 1, 1]
         b.alpha_u = b.alpha_v = 0.1; b.ior = 1.0
         if t == "diffuse":
@@ -558,7 +570,7 @@ class SceneDesc:
             if not isinstance(v, dict):
                 continue
             t = v.get("type")
-            if t in ("diffuse", "roughconductor", "conductor", "dielectric", "twosided"):
+            if t in ("diffuse", "roughconductor", "conductor", "dielectric", "twosided", "mask"):
                 self._add_bsdf(v, name)
         for name, v in d.items():   # declaration order defines the emitter order (scene.cpp:26-66)
             if not isinstance(v, dict):
@@ -576,7 +588,7 @@ class SceneDesc:
             elif t in ("path", "prb", "mypath", "path_test", "b2path", "b2path_mis", "b2prb"):
                 self.integrator_props = {k: v[k] for k in v if k != "type"}
                 self.integrator_props["type"] = t
-            elif t in ("diffuse", "roughconductor", "conductor", "dielectric", "twosided"):
+            elif t in ("diffuse", "roughconductor", "conductor", "dielectric", "twosided", "mask"):
                 pass
             else:
                 raise ValueError(f"unsupported scene element {name!r} of type {t!r}")

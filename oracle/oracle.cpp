@@ -178,7 +178,7 @@ struct Integrator {
             if (active_em) result = fmadd(throughput, bsdf_val * em_weight * mi_em, result);
             if (si.valid) ray = Scene::spawn_ray(si.p, si.n, si.sh.to_world(bs.wo));
             throughput *= bsdf_weight; eta *= bs.eta;
-            valid_ray = valid_ray || (active && si.valid);
+            valid_ray = valid_ray || (active && si.valid && !(bs.type & LOBE_NULL));   // path-mis.py:129-133
             prev_p = si.p; prev_bsdf_pdf = bs.pdf; prev_bsdf_delta = (bs.type & LOBE_DELTA) != 0;
             if (si.valid) depth += 1;
             float tmax = hmax(throughput), rr_prop = fminf(tmax * sqr(eta), 0.95f);

@@ -12,8 +12,8 @@ namespace orc {
 struct Ray { V3 o, d; float maxt; };
 struct Hit { float t, u, v; uint32_t face; bool valid() const { return face != 0xffffffffu; } };
 
-enum { LOBE_DIFFUSE = 1, LOBE_GLOSSY = 2, LOBE_DELTA_R = 4, LOBE_DELTA_T = 8,
-       LOBE_SMOOTH = LOBE_DIFFUSE | LOBE_GLOSSY, LOBE_DELTA = LOBE_DELTA_R | LOBE_DELTA_T };
+enum { LOBE_DIFFUSE = 1, LOBE_GLOSSY = 2, LOBE_DELTA_R = 4, LOBE_DELTA_T = 8, LOBE_NULL = 16,
+       LOBE_SMOOTH = LOBE_DIFFUSE | LOBE_GLOSSY, LOBE_DELTA = LOBE_DELTA_R | LOBE_DELTA_T | LOBE_NULL };   // BSDFFlags::Delta includes Null
 
 struct SI {                 // SurfaceInteraction3f subset (interaction.h)
     bool valid = false;
@@ -442,12 +442,13 @@ struct Microfacet {
 // BSDFs.  `unit` = evaluate with the differentiable reflectance set to 1 (linear coefficient, PRB).
 // ---------------------------------------------------------------------------------------------
 static inline uint32_t bsdf_lobes(const b2_bsdf &b) {
-    return b.type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : (b.type == B2_BSDF_ROUGHCONDUCTOR ? LOBE_GLOSSY : LOBE_DELTA);
+    uint32_t l = b.type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : (b.type == B2_BSDF_ROUGHCONDUCTOR ? LOBE_GLOSSY : (LOBE_DELTA_R | LOBE_DELTA_T));
+    return (b.flags & B2_BSDF_FLAG_MASK) ? (l | LOBE_NULL) : l;     // mask.cpp:96-110: nested components + a null lobe
 }
 
 // SmoothDiffuse::eval_pdf (bsdfs/diffuse.cpp:159-179), RoughConductor::eval_pdf (roughconductor.cpp:429-518),
 // SmoothDielectric::eval/pdf = 0 (dielectric.cpp:372-380), TwoSidedBRDF::eval_pdf (twosided.cpp:218-260)
-static inline void bsdf_eval_pdf(const Scene &sc, const b2_bsdf &b, const SI &si_, V3 wo, V3 &val, float &pdf, bool unit, Counters &c) {
+static inline void bsdf_eval_pdf_nested(const Scene &sc, const b2_bsdf &b, const SI &si_, V3 wo, V3 &val, float &pdf, bool unit, Counters &c) {
     SI si = si_;
     val = V3(0.f); pdf = 0.f;
     if (b.flags & B2_BSDF_FLAG_TWOSIDED) { wo.z = mulsign(wo.z, si.wi.z); si.wi.z = fabsf(si.wi.z); }
@@ -475,12 +476,23 @@ static inline void bsdf_eval_pdf(const Scene &sc, const b2_bsdf &b, const SI &si
     }
 }
 
+// OpacityMask::eval_pdf (mask.cpp:196-215): nested value and pdf scaled by the opacity
+static inline void bsdf_eval_pdf(const Scene &sc, const b2_bsdf &b, const SI &si, V3 wo, V3 &val, float &pdf, bool unit, Counters &c) {
+    bsdf_eval_pdf_nested(sc, b, si, wo, val, pdf, unit, c);
+    if (b.flags & B2_BSDF_FLAG_MASK) { val *= V3(b.opacity); pdf *= b.opacity; }
+}
+
 // SmoothDiffuse::sample (diffuse.cpp:100-124), RoughConductor::sample (roughconductor.cpp:227-313),
 // SmoothDielectric::sample (dielectric.cpp:245-370), SmoothConductor::sample (conductor.cpp:249-307),
 // TwoSidedBRDF::sample (twosided.cpp:110-147)
 static inline void bsdf_sample(const Scene &sc, const b2_bsdf &b, const SI &si_, float s1, V2 s2, BS &bs, V3 &weight, Counters &c) {
     SI si = si_;
     bs = BS(); weight = V3(0.f);
+    const bool masked = (b.flags & B2_BSDF_FLAG_MASK) != 0;
+    if (masked) {           // OpacityMask::sample (mask.cpp:123-171)
+        if (!(s1 < b.opacity)) { bs.wo = -si.wi; bs.eta = 1.f; bs.type = LOBE_NULL; bs.pdf = 1.f - b.opacity; weight = V3(1.f); return; }
+        s1 /= b.opacity;
+    }
     bool two = (b.flags & B2_BSDF_FLAG_TWOSIDED) != 0;
     if (two) si.wi.z = fabsf(si.wi.z);
     float ci = si.wi.z;
@@ -526,6 +538,7 @@ static inline void bsdf_sample(const Scene &sc, const b2_bsdf &b, const SI &si_,
         else { weight *= V3(b.transmittance[0], b.transmittance[1], b.transmittance[2]); weight *= sqr(eta_ti); }
     }
     if (two) bs.wo.z = mulsign(bs.wo.z, si_.wi.z);
+    if (masked) bs.pdf *= b.opacity;
 }
 
 // ---------------------------------------------------------------------------------------------

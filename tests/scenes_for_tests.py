@@ -53,6 +53,10 @@ def materials_scene(width=48, height=40, spp=8, envmap=True, filter_type="gaussi
     d["mirror"] = {"type": "twosided", "nested": {"type": "conductor", "eta": [0.27, 0.68, 1.32], "k": [3.6, 2.62, 2.29],
                                                    "specular_reflectance": [0.9, 0.95, 1.0]}}
     d["green-wall"]["bsdf"] = {"type": "ref", "id": "mirror"}
+    # the bedroom's curtain (scene.xml:199-206): opacity mask over a twosided diffuse, hanging in front of the back wall
+    d["curtain-bsdf"] = {"type": "mask", "opacity": 0.531049, "nested": {"type": "twosided", "nested": {"type": "diffuse", "reflectance": [0.8, 0.7, 0.6]}}}
+    d["curtain"] = {"type": "rectangle", "to_world": T().translate([-0.3, 0.1, -0.55]).rotate([0, 1, 0], 20).scale(0.45),
+                    "bsdf": {"type": "ref", "id": "curtain-bsdf"}}
     if mesh_light:
         pos = np.array([[-0.6, 0.2, -0.6], [-0.3, 0.2, -0.6], [-0.45, 0.45, -0.5], [-0.45, 0.3, -0.3]], np.float32)
         faces = np.array([[0, 1, 2], [0, 3, 1], [1, 3, 2], [0, 2, 3]], np.uint32)
@@ -82,7 +86,7 @@ def triangles_scene(n_tris=20000, width=64, height=48, spp=4, seed=3):
     }
 
 
-def mirror_scene(width=16, height=16, spp=4, tilt_deg=30.0, eta=(0.2, 0.92, 1.1), k=(3.9, 2.45, 2.14), refl=(0.9, 0.8, 0.7), radiance=(1.0, 2.0, 3.0)):
+def mirror_scene(width=16, height=16, spp=4, tilt_deg=30.0, eta=(0.2, 0.92, 1.1), k=(3.9, 2.45, 2.14), refl=(0.9, 0.8, 0.7), radiance=(1.0, 2.0, 3.0), opacity=None):
     """Known-answer scene for the smooth conductor: a huge mirror under a constant environment.  Every camera ray hits the
     mirror once and escapes, so radiance(pixel) = specular_reflectance * F_conductor(cos_i; eta, k) * radiance, with
     cos_i = dot(-d, n) known in closed form per pixel (conductor.cpp:249-307, fresnel.h:92-117)."""
@@ -92,7 +96,8 @@ def mirror_scene(width=16, height=16, spp=4, tilt_deg=30.0, eta=(0.2, 0.92, 1.1)
                    "to_world": T().look_at([0, 0, 4], [0, 0, 0], [0, 1, 0]),
                    "sampler": {"type": "independent", "sample_count": spp},
                    "film": {"type": "hdrfilm", "width": width, "height": height, "rfilter": {"type": "box"}}},
-        "m": {"type": "conductor", "eta": list(eta), "k": list(k), "specular_reflectance": list(refl)},
+        "m": ({"type": "conductor", "eta": list(eta), "k": list(k), "specular_reflectance": list(refl)} if opacity is None else
+              {"type": "mask", "opacity": opacity, "nested": {"type": "conductor", "eta": list(eta), "k": list(k), "specular_reflectance": list(refl)}}),
         "plane": {"type": "rectangle", "to_world": T().rotate([1, 0, 0], tilt_deg).scale(50.0), "bsdf": {"type": "ref", "id": "m"}},
         "env": {"type": "constant", "radiance": {"type": "rgb", "value": list(radiance)}},
     }

@@ -303,3 +303,22 @@ def test_smooth_conductor_known_answer_and_parity(kernel):
         assert cnt["closest_rays"] == rc["closest_rays"] and cnt["shadow_rays"] == 0
         exp = mirror_expected(d, lib())
         assert np.abs(img.cpu().numpy() - exp).max() / exp.max() < 5e-3
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_opacity_mask_parity(kernel):
+    """OpacityMask (mask.cpp:123-215).  Same seeds => CUDA == oracle per pixel (the null / nested choice is
+    one comparison of the same PCG32 draw); a fully transparent mask must leave only the environment."""
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    from scenes_for_tests import mirror_scene
+    for op in (0.4, 0.0, 1.0):
+        d = mirror_scene(16, 16, 32, opacity=op)
+        ds = DeviceScene(d); orc = OracleScene(ds.desc)
+        for variant in (0, 1, 2):
+            kw = dict(seed=5, spp=32, max_depth=5, rr_depth=8, variant=variant)
+            img, cnt = ds.render(counters=True, kernel=kernel, **kw)
+            ref, rc = orc.render(**kw)
+            check_image(img.cpu().numpy(), ref, 0.999, 1e-4)
+            assert cnt["closest_rays"] == rc["closest_rays"]
+        if op == 0.0:
+            assert np.allclose(img.cpu().numpy(), np.asarray(d["env"]["radiance"]["value"])[None, None, :], rtol=1e-5)
