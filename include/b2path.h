@@ -42,7 +42,9 @@ extern "C" {
 
 /* ------------------------------------------------------------------ enums */
 enum { B2_BSDF_DIFFUSE = 0, B2_BSDF_ROUGHCONDUCTOR = 1, B2_BSDF_DIELECTRIC = 2,
-       B2_BSDF_CONDUCTOR = 3 /* smooth conductor (conductor.cpp:249-307), SURVEY 8(f) rank 1 */ };
+       B2_BSDF_CONDUCTOR = 3,      /* smooth conductor (conductor.cpp:249-307), SURVEY 8(f) rank 1 */
+       B2_BSDF_ROUGHDIELECTRIC = 4 /* rough dielectric (roughdielectric.cpp:242-605): `ior` = int/ext, alpha, distribution,
+                                      reflectance = specular_reflectance, transmittance = specular_transmittance */ };
 enum { B2_BSDF_FLAG_TWOSIDED = 1,             /* wrapped in a `twosided` adapter (twosided.cpp:110-260) */
        B2_BSDF_FLAG_MASK = 2 };               /* outermost `mask` adapter with constant `opacity` (mask.cpp:123-215), SURVEY 8(f) rank 1 */
 enum { B2_MF_BECKMANN = 0, B2_MF_GGX = 1 };   /* MicrofacetType (microfacet.h) */

@@ -15,7 +15,7 @@ B2_ABI_VERSION = 1
 B2_MAX_WARP_LEVELS = 24
 
 # enums (keep in sync with b2path.h)
-BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC, BSDF_CONDUCTOR = 0, 1, 2, 3
+BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC, BSDF_CONDUCTOR, BSDF_ROUGHDIELECTRIC = 0, 1, 2, 3, 4
 BSDF_FLAG_TWOSIDED = 1
 BSDF_FLAG_MASK = 2
 MF_BECKMANN, MF_GGX = 0, 1

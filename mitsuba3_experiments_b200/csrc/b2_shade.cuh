@@ -27,7 +27,8 @@ enum { LOBE_DIFFUSE = 1, LOBE_GLOSSY = 2, LOBE_DELTA_R = 4, LOBE_DELTA_T = 8, LO
 // both at run time (megakernel, adjoint replay).
 enum { CLS_GENERIC = -1, CLS_DIFFUSE = 0, CLS_DIFFUSE_TEX = 1, CLS_CONDUCTOR = 2, CLS_DIELECTRIC = 3, CLS_MISS = 4, CLS_COUNT = 5 };
 template <int CLS> B2_DEV int cls_type(int runtime_type) {
-    return (CLS == CLS_DIFFUSE || CLS == CLS_DIFFUSE_TEX) ? B2_BSDF_DIFFUSE : CLS == CLS_CONDUCTOR ? B2_BSDF_ROUGHCONDUCTOR
+    return (CLS == CLS_DIFFUSE || CLS == CLS_DIFFUSE_TEX) ? B2_BSDF_DIFFUSE
+           : CLS == CLS_CONDUCTOR ? (runtime_type == B2_BSDF_ROUGHDIELECTRIC ? B2_BSDF_ROUGHDIELECTRIC : B2_BSDF_ROUGHCONDUCTOR)   // the glossy class
            : CLS == CLS_DIELECTRIC ? (runtime_type == B2_BSDF_CONDUCTOR ? B2_BSDF_CONDUCTOR : B2_BSDF_DIELECTRIC)   // the delta class
            : runtime_type;
 }
@@ -182,6 +183,7 @@ B2_DEV float fresnel_conductor(float cos_i, float eta_r, float eta_i) {
 struct Microfacet {
     int type; float au, av; bool visible;
     B2_DEV Microfacet(int t, float a_u, float a_v, bool vis) : type(t), au(fmaxf(a_u, 1e-4f)), av(fmaxf(a_v, 1e-4f)), visible(vis) {}
+    B2_DEV void scale_alpha(float v) { au *= v; av *= v; }      // microfacet.h:174-177
     B2_DEV float eval(f3 m) const {
         const float alpha_uv = au * av, ct = m.z, ct2 = sqr(ct);
         float result;
@@ -270,7 +272,7 @@ struct Microfacet {
 template <int CLS = CLS_GENERIC>
 B2_DEV uint32_t bsdf_lobes(const DBsdf &b) {
     const int type = cls_type<CLS>(b.type);
-    const uint32_t l = type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : (type == B2_BSDF_ROUGHCONDUCTOR ? LOBE_GLOSSY : (LOBE_DELTA_R | LOBE_DELTA_T));
+    const uint32_t l = type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : ((type == B2_BSDF_ROUGHCONDUCTOR || type == B2_BSDF_ROUGHDIELECTRIC) ? LOBE_GLOSSY : (LOBE_DELTA_R | LOBE_DELTA_T));
     return (b.flags & B2_BSDF_FLAG_MASK) ? (l | LOBE_NULL) : l;      // mask.cpp:96-110
 }
 B2_DEV f3 fresnel_conductor3(float c, const DBsdf &b) {
@@ -300,6 +302,32 @@ B2_DEV void bsdf_eval_pdf_nested(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &va
         const f3 v = f3(value) * refl();
         const float p = b.sample_visible ? D * g1_wi / (4.f * ci) : distr.pdf(wi, H) / (4.f * dot(wo, H));
         if (D != 0.f) { val = F * v; pdf = p; }
+    } else if (type == B2_BSDF_ROUGHDIELECTRIC) {
+        // RoughDielectric::eval_pdf (roughdielectric.cpp:503-605)
+        if (ci == 0.f) return;
+        const bool reflect = ci * co > 0.f;
+        const float eta = ci > 0.f ? b.ior : rcp(b.ior), inv_eta = ci > 0.f ? rcp(b.ior) : b.ior;
+        f3 m = normalize(wi + wo * (reflect ? 1.f : eta));
+        m = f3(mulsign(m.x, m.z), mulsign(m.y, m.z), mulsign(m.z, m.z));
+        const float dwi = dot(wi, m), dwo = dot(wo, m);
+        if (!(dwi * ci > 0.f && dwo * co > 0.f)) return;
+        Microfacet distr(b.distribution, b.alpha_u, b.alpha_v, b.sample_visible != 0);
+        const float D = distr.eval(m);
+        float F, cos_t, eta_it, eta_ti; fresnel(dwi, b.ior, F, cos_t, eta_it, eta_ti);
+        const float G = distr.G(wi, wo, m);
+        if (reflect) {
+            val = f3(F * D * G / (4.f * fabsf(ci)));
+            val = val * refl();
+        } else {
+            const float scale = sqr(inv_eta);
+            val = f3(fabsf((scale * (1.f - F) * D * G * eta * eta * dwi * dwo) / (ci * sqr(dwi + eta * dwo))));
+            val = val * f3(b.trans[0], b.trans[1], b.trans[2]);
+        }
+        if (!b.sample_visible) distr.scale_alpha(1.2f - .2f * sqrtf(fabsf(ci)));
+        float p = distr.pdf(ci < 0.f ? -wi : wi, m);
+        p *= reflect ? F : 1.f - F;
+        const float dwh_dwo = reflect ? rcp(4.f * dwo) : (eta * eta * dwo) / sqr(dwi + eta * dwo);
+        pdf = p * fabsf(dwh_dwo);
     }
 }
 
@@ -343,6 +371,34 @@ B2_DEV void bsdf_sample(const DBsdf &b, f3 wi_in, float s1, f2 s2, RF &&refl, BS
             const f3 F = fresnel_conductor3(dot(wi, m), b);
             const f3 wv = f3(w) * refl();
             if (active) weight = F * wv;
+        }
+    } else if (type == B2_BSDF_ROUGHDIELECTRIC) {
+        // RoughDielectric::sample (roughdielectric.cpp:242-357)
+        if (ci != 0.f) {
+            Microfacet distr(b.distribution, b.alpha_u, b.alpha_v, b.sample_visible != 0), sample_distr = distr;
+            if (!b.sample_visible) sample_distr.scale_alpha(1.2f - .2f * sqrtf(fabsf(ci)));
+            const f3 m = sample_distr.sample(ci < 0.f ? -wi : wi, s2, bs.pdf);
+            const bool active = bs.pdf != 0.f;
+            float F, cos_t, eta_it, eta_ti; fresnel(dot(wi, m), b.ior, F, cos_t, eta_it, eta_ti);
+            const bool sel_r = s1 <= F && active, sel_t = !sel_r && active;
+            bs.pdf *= sel_r ? F : 1.f - F;
+            bs.eta = sel_r ? 1.f : eta_it; bs.type = LOBE_GLOSSY;
+            f3 w(1.f); float dwh_dwo = 0.f;
+            if (sel_r) {
+                bs.wo = fmadd(m, 2.f * dot(wi, m), -wi);                             // reflect(wi, m)
+                w = w * refl();
+                dwh_dwo = rcp(4.f * dot(bs.wo, m));
+            }
+            if (sel_t) {
+                bs.wo = fmadd(m, fma_(dot(wi, m), eta_ti, cos_t), -(wi * eta_ti));   // refract(wi, m, cos_t, eta_ti)
+                w = w * (f3(b.trans[0], b.trans[1], b.trans[2]) * sqr(eta_ti));
+                dwh_dwo = (sqr(bs.eta) * dot(bs.wo, m)) / sqr(dot(wi, m) + bs.eta * dot(bs.wo, m));
+            }
+            if (active) {
+                w = w * (b.sample_visible ? distr.smith_g1(bs.wo, m) : distr.G(wi, bs.wo, m) * dot(wi, m) / (ci * m.z));
+                weight = w;
+            }
+            bs.pdf *= fabsf(dwh_dwo);
         }
     } else if (type == B2_BSDF_CONDUCTOR) {
         // SmoothConductor::sample (conductor.cpp:249-307)

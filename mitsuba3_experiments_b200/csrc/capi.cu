@@ -89,7 +89,7 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
         if (m.bsdf < 0 || (uint32_t) m.bsdf >= desc->n_bsdfs) return fail(-2, "b2_scene_create: mesh references a missing BSDF");
         if ((uint64_t) m.first_face + m.n_faces > desc->n_faces) return fail(-2, "b2_scene_create: mesh face range out of bounds");
         const b2_bsdf &mb = desc->bsdfs[m.bsdf];
-        const uint32_t cls = mb.type == B2_BSDF_DIFFUSE ? (mb.reflectance_tex >= 0 ? 1u : 0u) : (mb.type == B2_BSDF_ROUGHCONDUCTOR ? 2u : 3u);   // CLS_* of b2_shade.cuh
+        const uint32_t cls = mb.type == B2_BSDF_DIFFUSE ? (mb.reflectance_tex >= 0 ? 1u : 0u) : ((mb.type == B2_BSDF_ROUGHCONDUCTOR || mb.type == B2_BSDF_ROUGHDIELECTRIC) ? 2u : 3u);   // CLS_* of b2_shade.cuh: glossy | delta
         s->class_mask |= 1u << cls;
         meshes[i] = DMesh{ m.bsdf, m.emitter, m.flags, m.first_face, m.n_faces, cls, { 0, 0 } };
         for (uint32_t f = 0; f < m.n_faces; ++f) face_mesh[m.first_face + f] = i;
@@ -116,7 +116,7 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
     for (uint32_t i = 0; i < desc->n_bsdfs; ++i) {
         const b2_bsdf &b = desc->bsdfs[i]; DBsdf &o = bs[i];
         if (b.reflectance_tex >= (int) desc->n_textures) return fail(-2, "b2_scene_create: BSDF references a missing texture");
-        if (b.type < 0 || b.type > B2_BSDF_CONDUCTOR) return fail(-2, "b2_scene_create: unsupported BSDF type");
+        if (b.type < 0 || b.type > B2_BSDF_ROUGHDIELECTRIC) return fail(-2, "b2_scene_create: unsupported BSDF type");
         o.type = b.type; o.flags = b.flags; o.tex = b.reflectance_tex; o.distribution = b.distribution; o.sample_visible = b.sample_visible;
         for (int k = 0; k < 3; ++k) { o.refl[k] = b.reflectance[k]; o.eta[k] = b.eta[k]; o.k[k] = b.k[k]; o.trans[k] = b.transmittance[k]; }
         o.alpha_u = b.alpha_u; o.alpha_v = b.alpha_v; o.ior = b.ior;
@@ -393,7 +393,7 @@ int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_i
             if (g.bsdf < 0 || g.bsdf >= (int) s->bsdfs.size() || !g.grad) return fail(-2, "b2_render_backward: bad gradient target");
             const bool textured = s->bsdfs[g.bsdf].reflectance_tex >= 0;
             if ((g.kind == 1) != textured) return fail(-2, "b2_render_backward: target kind does not match the BSDF's reflectance");
-            if (s->bsdfs[g.bsdf].type == B2_BSDF_DIELECTRIC || s->bsdfs[g.bsdf].type == B2_BSDF_CONDUCTOR) return fail(-2, "b2_render_backward: delta-lobe (dielectric / conductor) reflectance is not a supported target");
+            if (s->bsdfs[g.bsdf].type == B2_BSDF_DIELECTRIC || s->bsdfs[g.bsdf].type == B2_BSDF_CONDUCTOR || s->bsdfs[g.bsdf].type == B2_BSDF_ROUGHDIELECTRIC) return fail(-2, "b2_render_backward: delta-lobe (dielectric / conductor) reflectance is not a supported target");
             p.targets[t] = GradTargetDev{ g.bsdf, g.kind, g.grad };
         }
         CUDA_OK(cudaMemsetAsync(s->unit_counter, 0, 16, st));

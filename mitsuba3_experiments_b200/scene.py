@@ -7,7 +7,7 @@ Mitsuba plugins, so this module understands the same dictionary schema for the p
 
 * shapes ``rectangle`` (rectangle.cpp:102-176), ``cube`` (cube.cpp:105-163), ``obj`` (obj.cpp subset) and a raw
   ``mesh`` (explicit arrays) -> world-space vertex/normal/uv/face buffers (Mesh layout, mesh.h:564-568)
-* bsdfs ``diffuse``, ``roughconductor``, ``conductor``, ``dielectric``, ``twosided`` (single nested BRDF), ``mask`` (constant opacity, outermost), ``ref``
+* bsdfs ``diffuse``, ``roughconductor``, ``conductor``, ``dielectric``, ``roughdielectric``, ``twosided`` (single nested BRDF), ``mask`` (constant opacity, outermost), ``ref``
 * textures ``rgb`` / plain lists, ``bitmap`` (filename | data array; fp16 storage rule of bitmap.cpp:231-246)
 * emitters ``area``, ``envmap`` (Hierarchical2D pyramid, distr_2d.h:403-509), ``constant``
 * sensor ``perspective`` (perspective.cpp:173-199, sensor.h:229-265, sensor.cpp:147-200), ``hdrfilm``,
@@ -401,10 +401,19 @@ class SceneDesc:
                 raise ValueError("conductor: named materials need Mitsuba's ior database; pass eta/k")
             b.eta[:] = _rgb(spec.get("eta"), 0.0).tolist(); b.k[:] = _rgb(spec.get("k"), 1.0).tolist()
             self._reflectance(b, spec.get("specular_reflectance"), 1.0)
-        elif t == "dielectric":
+        elif t in ("dielectric", "roughdielectric"):
             if flags & capi.BSDF_FLAG_TWOSIDED:
                 raise ValueError("Only materials without a transmission component can be nested!")
-            b.type = capi.BSDF_DIELECTRIC
+            b.type = capi.BSDF_DIELECTRIC if t == "dielectric" else capi.BSDF_ROUGHDIELECTRIC
+            if t == "roughdielectric":                          # roughdielectric.cpp:166-213
+                b.distribution = {"beckmann": capi.MF_BECKMANN, "ggx": capi.MF_GGX}[str(spec.get("distribution", "beckmann")).lower()]
+                b.sample_visible = int(bool(spec.get("sample_visible", True)))
+                if "alpha_u" in spec or "alpha_v" in spec:
+                    b.alpha_u, b.alpha_v = float(spec["alpha_u"]), float(spec["alpha_v"])
+                else:
+                    b.alpha_u = b.alpha_v = float(spec.get("alpha", 0.1))
+                if isinstance(spec.get("specular_reflectance"), dict) and spec["specular_reflectance"].get("type") == "bitmap":
+                    raise ValueError("roughdielectric: textured specular_reflectance is not supported")
             iors = {"bk7": 1.5046, "air": 1.000277, "vacuum": 1.0, "water": 1.3330, "diamond": 2.419}
             def ior(v, d):
                 v = spec.get(v, d)
@@ -570,7 +579,7 @@ class SceneDesc:
             if not isinstance(v, dict):
                 continue
             t = v.get("type")
-            if t in ("diffuse", "roughconductor", "conductor", "dielectric", "twosided", "mask"):
+            if t in ("diffuse", "roughconductor", "conductor", "dielectric", "roughdielectric", "twosided", "mask"):
                 self._add_bsdf(v, name)
         for name, v in d.items():   # declaration order defines the emitter order (scene.cpp:26-66)
             if not isinstance(v, dict):
@@ -588,7 +597,7 @@ class SceneDesc:
             elif t in ("path", "prb", "mypath", "path_test", "b2path", "b2path_mis", "b2prb"):
                 self.integrator_props = {k: v[k] for k in v if k != "type"}
                 self.integrator_props["type"] = t
-            elif t in ("diffuse", "roughconductor", "conductor", "dielectric", "twosided", "mask"):
+            elif t in ("diffuse", "roughconductor", "conductor", "dielectric", "roughdielectric", "twosided", "mask"):
                 pass
             else:
                 raise ValueError(f"unsupported scene element {name!r} of type {t!r}")

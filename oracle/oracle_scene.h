@@ -353,6 +353,7 @@ static inline float fresnel_conductor(float cos_i, float eta_r, float eta_i) {
 struct Microfacet {
     int type; float au, av; bool visible;
     Microfacet(int t, float a_u, float a_v, bool vis) : type(t), au(fmaxf(a_u, 1e-4f)), av(fmaxf(a_v, 1e-4f)), visible(vis) {}
+    void scale_alpha(float v) { au *= v; av *= v; }      // microfacet.h:174-177
     float eval(V3 m) const {
         float alpha_uv = au * av, ct = m.z, ct2 = sqr(ct), result;
         if (type == B2_MF_BECKMANN)
@@ -442,7 +443,7 @@ struct Microfacet {
 // BSDFs.  `unit` = evaluate with the differentiable reflectance set to 1 (linear coefficient, PRB).
 // ---------------------------------------------------------------------------------------------
 static inline uint32_t bsdf_lobes(const b2_bsdf &b) {
-    uint32_t l = b.type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : (b.type == B2_BSDF_ROUGHCONDUCTOR ? LOBE_GLOSSY : (LOBE_DELTA_R | LOBE_DELTA_T));
+    uint32_t l = b.type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : ((b.type == B2_BSDF_ROUGHCONDUCTOR || b.type == B2_BSDF_ROUGHDIELECTRIC) ? LOBE_GLOSSY : (LOBE_DELTA_R | LOBE_DELTA_T));
     return (b.flags & B2_BSDF_FLAG_MASK) ? (l | LOBE_NULL) : l;     // mask.cpp:96-110: nested components + a null lobe
 }
 
@@ -473,6 +474,32 @@ static inline void bsdf_eval_pdf_nested(const Scene &sc, const b2_bsdf &b, const
         v = v * refl;
         float p = b.sample_visible ? D * g1_wi / (4.f * ci) : distr.pdf(si.wi, H) / (4.f * dot(wo, H));
         if (active) { val = F * v; pdf = p; }
+    } else if (b.type == B2_BSDF_ROUGHDIELECTRIC) {
+        // RoughDielectric::eval_pdf (roughdielectric.cpp:503-605)
+        if (ci == 0.f) return;
+        const bool reflect = ci * co > 0.f;
+        const float eta = ci > 0.f ? b.ior : rcp(b.ior), inv_eta = ci > 0.f ? rcp(b.ior) : b.ior;
+        V3 m = normalize(si.wi + wo * (reflect ? 1.f : eta));
+        m = V3(mulsign(m.x, m.z), mulsign(m.y, m.z), mulsign(m.z, m.z));
+        const float dwi = dot(si.wi, m), dwo = dot(wo, m);
+        if (!(dwi * ci > 0.f && dwo * co > 0.f)) return;
+        Microfacet distr(b.distribution, b.alpha_u, b.alpha_v, b.sample_visible != 0);
+        const float D = distr.eval(m);
+        float F, cos_t, eta_it, eta_ti; fresnel(dwi, b.ior, F, cos_t, eta_it, eta_ti);
+        const float G = distr.G(si.wi, wo, m);
+        if (reflect) {
+            val = V3(F * D * G / (4.f * fabsf(ci)));
+            val = val * (unit ? V3(1.f) : sc.reflectance(b, si, c));
+        } else {
+            const float scale = sqr(inv_eta);
+            val = V3(fabsf((scale * (1.f - F) * D * G * eta * eta * dwi * dwo) / (ci * sqr(dwi + eta * dwo))));
+            val = val * V3(b.transmittance[0], b.transmittance[1], b.transmittance[2]);
+        }
+        if (!b.sample_visible) distr.scale_alpha(1.2f - .2f * sqrtf(fabsf(ci)));
+        float p = distr.pdf(ci < 0.f ? -si.wi : si.wi, m);
+        p *= reflect ? F : 1.f - F;
+        const float dwh_dwo = reflect ? rcp(4.f * dwo) : (eta * eta * dwo) / sqr(dwi + eta * dwo);
+        pdf = p * fabsf(dwh_dwo);
     }
 }
 
@@ -516,6 +543,34 @@ static inline void bsdf_sample(const Scene &sc, const b2_bsdf &b, const SI &si_,
             V3 F(fresnel_conductor(cm, b.eta[0], b.k[0]), fresnel_conductor(cm, b.eta[1], b.k[1]), fresnel_conductor(cm, b.eta[2], b.k[2]));
             V3 wv = V3(w) * sc.reflectance(b, si, c);
             if (active) weight = F * wv;
+        }
+    } else if (b.type == B2_BSDF_ROUGHDIELECTRIC) {
+        // RoughDielectric::sample (roughdielectric.cpp:242-357)
+        if (ci != 0.f) {
+            Microfacet distr(b.distribution, b.alpha_u, b.alpha_v, b.sample_visible != 0), sample_distr = distr;
+            if (!b.sample_visible) sample_distr.scale_alpha(1.2f - .2f * sqrtf(fabsf(ci)));
+            V3 m = sample_distr.sample(ci < 0.f ? -si.wi : si.wi, s2, bs.pdf);
+            const bool active = bs.pdf != 0.f;
+            float F, cos_t, eta_it, eta_ti; fresnel(dot(si.wi, m), b.ior, F, cos_t, eta_it, eta_ti);
+            const bool sel_r = s1 <= F && active, sel_t = !sel_r && active;
+            bs.pdf *= sel_r ? F : 1.f - F;
+            bs.eta = sel_r ? 1.f : eta_it; bs.type = LOBE_GLOSSY;
+            V3 w(1.f); float dwh_dwo = 0.f;
+            if (sel_r) {
+                bs.wo = fmadd(m, 2.f * dot(si.wi, m), -si.wi);                       // reflect(wi, m)
+                w = w * sc.reflectance(b, si, c);
+                dwh_dwo = rcp(4.f * dot(bs.wo, m));
+            }
+            if (sel_t) {
+                bs.wo = fmadd(m, fmaf(dot(si.wi, m), eta_ti, cos_t), -(si.wi * eta_ti));   // refract(wi, m, cos_t, eta_ti)
+                w = w * (V3(b.transmittance[0], b.transmittance[1], b.transmittance[2]) * sqr(eta_ti));
+                dwh_dwo = (sqr(bs.eta) * dot(bs.wo, m)) / sqr(dot(si.wi, m) + bs.eta * dot(bs.wo, m));
+            }
+            if (active) {
+                w = w * (b.sample_visible ? distr.smith_g1(bs.wo, m) : distr.G(si.wi, bs.wo, m) * dot(si.wi, m) / (ci * m.z));
+                weight = w;
+            }
+            bs.pdf *= fabsf(dwh_dwo);
         }
     } else if (b.type == B2_BSDF_CONDUCTOR) {
         // SmoothConductor::sample (bsdfs/conductor.cpp:249-307): delta reflection, weight = specular_reflectance * F(cos_i)

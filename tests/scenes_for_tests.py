@@ -57,6 +57,11 @@ def materials_scene(width=48, height=40, spp=8, envmap=True, filter_type="gaussi
     d["curtain-bsdf"] = {"type": "mask", "opacity": 0.531049, "nested": {"type": "twosided", "nested": {"type": "diffuse", "reflectance": [0.8, 0.7, 0.6]}}}
     d["curtain"] = {"type": "rectangle", "to_world": T().translate([-0.3, 0.1, -0.55]).rotate([0, 1, 0], 20).scale(0.45),
                     "bsdf": {"type": "ref", "id": "curtain-bsdf"}}
+    # the bedroom's rough glass (scene.xml: roughdielectric, GGX): a frosted block floating above the boxes
+    d["frosted"] = {"type": "roughdielectric", "distribution": "ggx", "alpha": 0.15, "int_ior": 1.5, "ext_ior": 1.0,
+                    "specular_transmittance": [0.9, 0.95, 1.0]}
+    d["frosted-box"] = {"type": "cube", "to_world": T().translate([0.25, 0.45, 0.1]).rotate([0, 1, 0], 30).scale([0.2, 0.12, 0.2]),
+                        "bsdf": {"type": "ref", "id": "frosted"}}
     if mesh_light:
         pos = np.array([[-0.6, 0.2, -0.6], [-0.3, 0.2, -0.6], [-0.45, 0.45, -0.5], [-0.45, 0.3, -0.3]], np.float32)
         faces = np.array([[0, 1, 2], [0, 3, 1], [1, 3, 2], [0, 2, 3]], np.uint32)

@@ -322,3 +322,24 @@ def test_opacity_mask_parity(kernel):
             assert cnt["closest_rays"] == rc["closest_rays"]
         if op == 0.0:
             assert np.allclose(img.cpu().numpy(), np.asarray(d["env"]["radiance"]["value"])[None, None, :], rtol=1e-5)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("dist,visible", [("beckmann", False), ("ggx", True)])
+def test_roughdielectric_parity(kernel, dist, visible):
+    """RoughDielectric (roughdielectric.cpp:242-605), both sampling modes: CUDA == oracle on a Cornell box
+    whose small box is frosted glass (NEE through the glossy lobes, transmission with eta tracking for Russian roulette)."""
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    d = cornell_box(64, 64, 16)
+    d["frost"] = {"type": "roughdielectric", "distribution": dist, "alpha_u": 0.12, "alpha_v": 0.3, "int_ior": "bk7", "ext_ior": "air",
+                  "sample_visible": visible, "specular_reflectance": [1.0, 0.9, 0.8]}
+    d["small-box"]["bsdf"] = {"type": "ref", "id": "frost"}
+    d["small-box"]["to_world"] = d["small-box"]["to_world"].__class__().translate([0.335, -0.62, 0.38]).rotate([0, 1, 0], -17).scale(0.3)
+    ds = DeviceScene(d); orc = OracleScene(ds.desc)
+    for variant in (0, 1, 2):
+        kw = dict(seed=2, spp=16, max_depth=7, rr_depth=3, variant=variant)
+        img, cnt = ds.render(counters=True, kernel=kernel, all_shadow_rays=True, **kw)
+        ref, rc = orc.render(**kw)
+        check_image(img.cpu().numpy(), ref, 0.99, 2e-3)
+        for k in ("closest_rays", "shadow_rays", "vertices"):
+            assert abs(cnt[k] - rc[k]) <= 2e-3 * max(rc[k], 1) + 2, (k, cnt[k], rc[k])
