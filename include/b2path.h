@@ -43,8 +43,11 @@ extern "C" {
 /* ------------------------------------------------------------------ enums */
 enum { B2_BSDF_DIFFUSE = 0, B2_BSDF_ROUGHCONDUCTOR = 1, B2_BSDF_DIELECTRIC = 2,
        B2_BSDF_CONDUCTOR = 3,      /* smooth conductor (conductor.cpp:249-307), SURVEY 8(f) rank 1 */
-       B2_BSDF_ROUGHDIELECTRIC = 4 /* rough dielectric (roughdielectric.cpp:242-605): `ior` = int/ext, alpha, distribution,
-                                      reflectance = specular_reflectance, transmittance = specular_transmittance */ };
+       B2_BSDF_ROUGHDIELECTRIC = 4,/* rough dielectric (roughdielectric.cpp:242-605): `ior` = int/ext, alpha, distribution,
+                                      reflectance = specular_reflectance, transmittance = specular_transmittance */
+       B2_BSDF_ROUGHPLASTIC = 5    /* rough plastic (roughplastic.cpp:216-430): reflectance(+tex) = diffuse_reflectance, transmittance =
+                                      specular_reflectance, `ior`, alpha_u (isotropic), distribution, nonlinear, spec_sampling_weight;
+                                      the 64-entry transmittance table and the internal reflectance are computed by each implementation */ };
 enum { B2_BSDF_FLAG_TWOSIDED = 1,             /* wrapped in a `twosided` adapter (twosided.cpp:110-260) */
        B2_BSDF_FLAG_MASK = 2 };               /* outermost `mask` adapter with constant `opacity` (mask.cpp:123-215), SURVEY 8(f) rank 1 */
 enum { B2_MF_BECKMANN = 0, B2_MF_GGX = 1 };   /* MicrofacetType (microfacet.h) */
@@ -85,6 +88,8 @@ typedef struct b2_bsdf {
     float alpha_u, alpha_v;
     float ior;              /* dielectric: int_ior / ext_ior */
     float opacity;          /* B2_BSDF_FLAG_MASK: probability of interacting with the nested BSDF; else 1 */
+    int32_t nonlinear;      /* roughplastic: account for nonlinear colour shifts due to internal scattering */
+    float spec_sampling_weight; /* roughplastic: s_mean / (d_mean + s_mean) from the texture means (roughplastic.cpp:224-230) */
 } b2_bsdf;
 
 typedef struct b2_mesh {

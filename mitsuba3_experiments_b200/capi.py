@@ -15,7 +15,7 @@ B2_ABI_VERSION = 1
 B2_MAX_WARP_LEVELS = 24
 
 # enums (keep in sync with b2path.h)
-BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC, BSDF_CONDUCTOR, BSDF_ROUGHDIELECTRIC = 0, 1, 2, 3, 4
+BSDF_DIFFUSE, BSDF_ROUGHCONDUCTOR, BSDF_DIELECTRIC, BSDF_CONDUCTOR, BSDF_ROUGHDIELECTRIC, BSDF_ROUGHPLASTIC = 0, 1, 2, 3, 4, 5
 BSDF_FLAG_TWOSIDED = 1
 BSDF_FLAG_MASK = 2
 MF_BECKMANN, MF_GGX = 0, 1
@@ -41,7 +41,7 @@ class Texture(C.Structure):
 class Bsdf(C.Structure):
     _fields_ = [("type", i32), ("flags", i32), ("reflectance_tex", i32), ("distribution", i32),
                 ("sample_visible", i32), ("reflectance", f32 * 3), ("transmittance", f32 * 3),
-                ("eta", f32 * 3), ("k", f32 * 3), ("alpha_u", f32), ("alpha_v", f32), ("ior", f32), ("opacity", f32)]
+                ("eta", f32 * 3), ("k", f32 * 3), ("alpha_u", f32), ("alpha_v", f32), ("ior", f32), ("opacity", f32), ("nonlinear", i32), ("spec_sampling_weight", f32)]
 
 
 class Mesh(C.Structure):

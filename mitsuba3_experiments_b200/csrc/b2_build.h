@@ -22,4 +22,7 @@ struct Bvh {
 bool bvh_build(const float *pos, const uint32_t *faces, const uint32_t *face_mesh, uint32_t n_faces, int builder, cudaStream_t stream, Bvh &out, std::string &err);
 void bvh_free(Bvh &b);
 
+// rough-plastic tables (tables.cu): 64 external transmittances + the internal diffuse reflectance, computed on the device
+bool rough_tables_build(int distribution, float alpha, float eta, float *trans64_host, float *internal_reflectance, std::string &err);
+
 }  // namespace b2

@@ -18,7 +18,9 @@ struct alignas(16) DBsdf {          // 64 B
     float eta[3]; float alpha_u;
     float k[3]; float alpha_v;
     float trans[3]; float ior;
-    float opacity; float pad[3];     // mask adapter (B2_BSDF_FLAG_MASK); 96 B total
+    float opacity;                   // mask adapter (B2_BSDF_FLAG_MASK)
+    int32_t nonlinear; float spec_weight, int_refl;     // rough plastic: nonlinear flag, specular sampling weight, internal reflectance
+    const float *rough_table; uint64_t pad;             // rough plastic: 64 external transmittances (device); 112 B total
 };
 
 struct alignas(16) DTexture {

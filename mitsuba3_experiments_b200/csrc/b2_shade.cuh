@@ -28,7 +28,7 @@ enum { LOBE_DIFFUSE = 1, LOBE_GLOSSY = 2, LOBE_DELTA_R = 4, LOBE_DELTA_T = 8, LO
 enum { CLS_GENERIC = -1, CLS_DIFFUSE = 0, CLS_DIFFUSE_TEX = 1, CLS_CONDUCTOR = 2, CLS_DIELECTRIC = 3, CLS_MISS = 4, CLS_COUNT = 5 };
 template <int CLS> B2_DEV int cls_type(int runtime_type) {
     return (CLS == CLS_DIFFUSE || CLS == CLS_DIFFUSE_TEX) ? B2_BSDF_DIFFUSE
-           : CLS == CLS_CONDUCTOR ? (runtime_type == B2_BSDF_ROUGHDIELECTRIC ? B2_BSDF_ROUGHDIELECTRIC : B2_BSDF_ROUGHCONDUCTOR)   // the glossy class
+           : CLS == CLS_CONDUCTOR ? (runtime_type == B2_BSDF_ROUGHDIELECTRIC ? B2_BSDF_ROUGHDIELECTRIC : runtime_type == B2_BSDF_ROUGHPLASTIC ? B2_BSDF_ROUGHPLASTIC : B2_BSDF_ROUGHCONDUCTOR)   // the glossy class
            : CLS == CLS_DIELECTRIC ? (runtime_type == B2_BSDF_CONDUCTOR ? B2_BSDF_CONDUCTOR : B2_BSDF_DIELECTRIC)   // the delta class
            : runtime_type;
 }
@@ -272,11 +272,42 @@ struct Microfacet {
 template <int CLS = CLS_GENERIC>
 B2_DEV uint32_t bsdf_lobes(const DBsdf &b) {
     const int type = cls_type<CLS>(b.type);
-    const uint32_t l = type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : ((type == B2_BSDF_ROUGHCONDUCTOR || type == B2_BSDF_ROUGHDIELECTRIC) ? LOBE_GLOSSY : (LOBE_DELTA_R | LOBE_DELTA_T));
+    const uint32_t l = type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : ((type == B2_BSDF_ROUGHCONDUCTOR || type == B2_BSDF_ROUGHDIELECTRIC) ? LOBE_GLOSSY
+                       : (type == B2_BSDF_ROUGHPLASTIC ? (LOBE_GLOSSY | LOBE_DIFFUSE) : (LOBE_DELTA_R | LOBE_DELTA_T)));
     return (b.flags & B2_BSDF_FLAG_MASK) ? (l | LOBE_NULL) : l;      // mask.cpp:96-110
 }
 B2_DEV f3 fresnel_conductor3(float c, const DBsdf &b) {
     return f3(fresnel_conductor(c, b.eta[0], b.k[0]), fresnel_conductor(c, b.eta[1], b.k[1]), fresnel_conductor(c, b.eta[2], b.k[2]));
+}
+
+// RoughPlastic::lerp_gather (roughplastic.cpp:343-351)
+B2_DEV float lerp_gather(const float *__restrict__ data, float x, int size) {
+    x *= (float) (size - 1);
+    const uint32_t index = min((uint32_t) x, (uint32_t) (size - 2));
+    const float v0 = __ldg(data + index), v1 = __ldg(data + index + 1);
+    return lerp_(v0, v1, x - (float) index);
+}
+// RoughPlastic::eval / pdf (roughplastic.cpp:301-341, 353-393); wi.z > 0 and wo.z > 0 are the caller's precondition
+template <class RF>
+B2_DEV void roughplastic_eval_pdf(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &val, float &pdf) {
+    const float ci = wi.z, co = wo.z;
+    const Microfacet distr(b.distribution, b.alpha_u, b.alpha_u, b.sample_visible != 0);
+    const f3 H = normalize(wo + wi);
+    const float D = distr.eval(H);
+    float F, cos_t, eta_it, eta_ti; fresnel(dot(wi, H), b.ior, F, cos_t, eta_it, eta_ti);
+    const float G = distr.G(wi, wo, H);
+    const f3 value = f3(F * D * G / (4.f * ci)) * f3(b.trans[0], b.trans[1], b.trans[2]);      // specular_reflectance
+    const float t_i = lerp_gather(b.rough_table, ci, 64), t_o = lerp_gather(b.rough_table, co, 64);
+    f3 diff = refl();
+    diff = diff / (f3(1.f) - (b.nonlinear ? diff * b.int_refl : f3(b.int_refl)));
+    const float inv_eta_2 = 1.f / (b.ior * b.ior);
+    val = value + diff * (kInvPi * inv_eta_2 * co * t_i * t_o);
+    float prob_specular = (1.f - t_i) * b.spec_weight, prob_diffuse = t_i * (1.f - b.spec_weight);
+    prob_specular = prob_specular / (prob_specular + prob_diffuse); prob_diffuse = 1.f - prob_specular;
+    float r = b.sample_visible ? D * distr.smith_g1(wi, H) / (4.f * ci) : distr.pdf(wi, H) / (4.f * dot(wo, H));
+    r *= prob_specular;
+    r += prob_diffuse * (kInvPi * co);
+    pdf = r;
 }
 
 // eval_pdf.  `refl()` yields the (possibly textured) reflectance at si and is invoked exactly where the reference
@@ -302,6 +333,9 @@ B2_DEV void bsdf_eval_pdf_nested(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &va
         const f3 v = f3(value) * refl();
         const float p = b.sample_visible ? D * g1_wi / (4.f * ci) : distr.pdf(wi, H) / (4.f * dot(wo, H));
         if (D != 0.f) { val = F * v; pdf = p; }
+    } else if (type == B2_BSDF_ROUGHPLASTIC) {
+        if (!(ci > 0.f && co > 0.f)) return;
+        roughplastic_eval_pdf(b, wi, wo, refl, val, pdf);
     } else if (type == B2_BSDF_ROUGHDIELECTRIC) {
         // RoughDielectric::eval_pdf (roughdielectric.cpp:503-605)
         if (ci == 0.f) return;
@@ -371,6 +405,23 @@ B2_DEV void bsdf_sample(const DBsdf &b, f3 wi_in, float s1, f2 s2, RF &&refl, BS
             const f3 F = fresnel_conductor3(dot(wi, m), b);
             const f3 wv = f3(w) * refl();
             if (active) weight = F * wv;
+        }
+    } else if (type == B2_BSDF_ROUGHPLASTIC) {
+        // RoughPlastic::sample (roughplastic.cpp:264-299)
+        if (ci > 0.f) {
+            const float t_i = lerp_gather(b.rough_table, ci, 64);
+            float prob_specular = (1.f - t_i) * b.spec_weight; const float prob_diffuse = t_i * (1.f - b.spec_weight);
+            prob_specular = prob_specular / (prob_specular + prob_diffuse);
+            bs.eta = 1.f;
+            if (s1 < prob_specular) {
+                const Microfacet distr(b.distribution, b.alpha_u, b.alpha_u, b.sample_visible != 0);
+                float unused; const f3 m = distr.sample(wi, s2, unused);
+                bs.wo = fmadd(m, 2.f * dot(wi, m), -wi); bs.type = LOBE_GLOSSY;
+            } else { bs.wo = square_to_cosine_hemisphere(s2); bs.type = LOBE_DIFFUSE; }
+            f3 value(0.f); float p = 0.f;
+            if (bs.wo.z > 0.f) roughplastic_eval_pdf(b, wi, bs.wo, refl, value, p);
+            bs.pdf = p;
+            if (p > 0.f) weight = value / f3(p);
         }
     } else if (type == B2_BSDF_ROUGHDIELECTRIC) {
         // RoughDielectric::sample (roughdielectric.cpp:242-357)

@@ -89,7 +89,7 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
         if (m.bsdf < 0 || (uint32_t) m.bsdf >= desc->n_bsdfs) return fail(-2, "b2_scene_create: mesh references a missing BSDF");
         if ((uint64_t) m.first_face + m.n_faces > desc->n_faces) return fail(-2, "b2_scene_create: mesh face range out of bounds");
         const b2_bsdf &mb = desc->bsdfs[m.bsdf];
-        const uint32_t cls = mb.type == B2_BSDF_DIFFUSE ? (mb.reflectance_tex >= 0 ? 1u : 0u) : ((mb.type == B2_BSDF_ROUGHCONDUCTOR || mb.type == B2_BSDF_ROUGHDIELECTRIC) ? 2u : 3u);   // CLS_* of b2_shade.cuh: glossy | delta
+        const uint32_t cls = mb.type == B2_BSDF_DIFFUSE ? (mb.reflectance_tex >= 0 ? 1u : 0u) : ((mb.type == B2_BSDF_ROUGHCONDUCTOR || mb.type == B2_BSDF_ROUGHDIELECTRIC || mb.type == B2_BSDF_ROUGHPLASTIC) ? 2u : 3u);   // CLS_* of b2_shade.cuh: glossy | delta
         s->class_mask |= 1u << cls;
         meshes[i] = DMesh{ m.bsdf, m.emitter, m.flags, m.first_face, m.n_faces, cls, { 0, 0 } };
         for (uint32_t f = 0; f < m.n_faces; ++f) face_mesh[m.first_face + f] = i;
@@ -116,11 +116,27 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
     for (uint32_t i = 0; i < desc->n_bsdfs; ++i) {
         const b2_bsdf &b = desc->bsdfs[i]; DBsdf &o = bs[i];
         if (b.reflectance_tex >= (int) desc->n_textures) return fail(-2, "b2_scene_create: BSDF references a missing texture");
-        if (b.type < 0 || b.type > B2_BSDF_ROUGHDIELECTRIC) return fail(-2, "b2_scene_create: unsupported BSDF type");
+        if (b.type < 0 || b.type > B2_BSDF_ROUGHPLASTIC) return fail(-2, "b2_scene_create: unsupported BSDF type");
         o.type = b.type; o.flags = b.flags; o.tex = b.reflectance_tex; o.distribution = b.distribution; o.sample_visible = b.sample_visible;
         for (int k = 0; k < 3; ++k) { o.refl[k] = b.reflectance[k]; o.eta[k] = b.eta[k]; o.k[k] = b.k[k]; o.trans[k] = b.transmittance[k]; }
         o.alpha_u = b.alpha_u; o.alpha_v = b.alpha_v; o.ior = b.ior;
-        o.opacity = (b.flags & B2_BSDF_FLAG_MASK) ? b.opacity : 1.f; o.pad[0] = o.pad[1] = o.pad[2] = 0.f;
+        o.opacity = (b.flags & B2_BSDF_FLAG_MASK) ? b.opacity : 1.f;
+        o.nonlinear = b.nonlinear; o.spec_weight = b.spec_sampling_weight; o.int_refl = 0.f; o.rough_table = nullptr; o.pad = 0;
+        if (b.type == B2_BSDF_ROUGHPLASTIC) {
+            // tables by (distribution, alpha, eta), shared between BSDFs with equal parameters
+            int found = -1;
+            for (uint32_t j = 0; j < i; ++j) {
+                const b2_bsdf &q = desc->bsdfs[j];
+                if (q.type == B2_BSDF_ROUGHPLASTIC && q.distribution == b.distribution && q.alpha_u == b.alpha_u && q.ior == b.ior) { found = (int) j; break; }
+            }
+            if (found >= 0) { o.rough_table = bs[found].rough_table; o.int_refl = bs[found].int_refl; }
+            else {
+                float trans[64]; std::string terr; float *tdev = nullptr;
+                if (!(b.ior > 0.f) || b.ior == 1.f) return fail(-2, "b2_scene_create: roughplastic needs int_ior != ext_ior");
+                if (!rough_tables_build(b.distribution, b.alpha_u, b.ior, trans, &o.int_refl, terr)) return fail(-10, terr);
+                CUDA_OK(s->upload(trans, 64, tdev)); o.rough_table = tdev;
+            }
+        }
         if ((b.flags & B2_BSDF_FLAG_MASK) && !(b.opacity >= 0.f && b.opacity <= 1.f)) return fail(-2, "b2_scene_create: mask opacity outside [0, 1]");
     }
     CUDA_OK(s->upload(bs.data(), bs.size(), s->bsdfs_dev)); d.bsdfs = s->bsdfs_dev;

@@ -7,7 +7,7 @@ Mitsuba plugins, so this module understands the same dictionary schema for the p
 
 * shapes ``rectangle`` (rectangle.cpp:102-176), ``cube`` (cube.cpp:105-163), ``obj`` (obj.cpp subset) and a raw
   ``mesh`` (explicit arrays) -> world-space vertex/normal/uv/face buffers (Mesh layout, mesh.h:564-568)
-* bsdfs ``diffuse``, ``roughconductor``, ``conductor``, ``dielectric``, ``roughdielectric``, ``twosided`` (single nested BRDF), ``mask`` (constant opacity, outermost), ``ref``
+* bsdfs ``diffuse``, ``roughconductor``, ``conductor``, ``dielectric``, ``roughdielectric``, ``roughplastic``, ``twosided`` (single nested BRDF), ``mask`` (constant opacity, outermost), ``ref``
 * textures ``rgb`` / plain lists, ``bitmap`` (filename | data array; fp16 storage rule of bitmap.cpp:231-246)
 * emitters ``area``, ``envmap`` (Hierarchical2D pyramid, distr_2d.h:403-509), ``constant``
 * sensor ``perspective`` (perspective.cpp:173-199, sensor.h:229-265, sensor.cpp:147-200), ``hdrfilm``,
@@ -377,7 +377,7 @@ class SceneDesc:
                 raise ValueError("twosided: nested ref not supported")
             t = spec["type"]; flags |= capi.BSDF_FLAG_TWOSIDED
         b = capi.Bsdf()
-        b.flags = flags; b.reflectance_tex = -1; b.sample_visible = 1; b.opacity = opacity
+        b.flags = flags; b.reflectance_tex = -1; b.sample_visible = 1; b.opacity = opacity; b.nonlinear = 0; b.spec_sampling_weight = 0.5
         b.reflectance[:] = [1, 1, 1]; b.transmittance[:] = [1, 1, 1]; b.eta[:] = [0, 0, 0]; b.k[:] = [1, 1, 1]
         b.alpha_u = b.alpha_v = 0.1; b.ior = 1.0
         if t == "diffuse":
@@ -401,6 +401,32 @@ class SceneDesc:
                 raise ValueError("conductor: named materials need Mitsuba's ior database; pass eta/k")
             b.eta[:] = _rgb(spec.get("eta"), 0.0).tolist(); b.k[:] = _rgb(spec.get("k"), 1.0).tolist()
             self._reflectance(b, spec.get("specular_reflectance"), 1.0)
+        elif t == "roughplastic":                                # roughplastic.cpp:169-200
+            b.type = capi.BSDF_ROUGHPLASTIC
+            iors = {"bk7": 1.5046, "air": 1.000277, "vacuum": 1.0, "water": 1.3330, "polypropylene": 1.49}
+            def ior(v, d):
+                v = spec.get(v, d)
+                return float(iors[v]) if isinstance(v, str) else float(v)
+            b.ior = ior("int_ior", "polypropylene") / ior("ext_ior", "air")
+            if "alpha_u" in spec or "alpha_v" in spec:
+                raise ValueError("The 'roughplastic' plugin currently does not support anisotropic microfacet distributions!")
+            b.alpha_u = b.alpha_v = float(spec.get("alpha", 0.1))
+            b.distribution = {"beckmann": capi.MF_BECKMANN, "ggx": capi.MF_GGX}[str(spec.get("distribution", "beckmann")).lower()]
+            b.sample_visible = int(bool(spec.get("sample_visible", True)))
+            b.nonlinear = int(bool(spec.get("nonlinear", False)))
+            self._reflectance(b, spec.get("diffuse_reflectance"), 0.5)
+            sr = spec.get("specular_reflectance")
+            if isinstance(sr, dict) and sr.get("type") == "bitmap":
+                raise ValueError("roughplastic: textured specular_reflectance is not supported")
+            b.transmittance[:] = _rgb(sr, 1.0).tolist()          # the specular_reflectance slot of this BSDF
+            # Texture::mean(): bitmap = mean luminance (bitmap.cpp:829-853), rgb = mean of the channels (srgb.cpp:117-122)
+            if b.reflectance_tex >= 0:
+                a = np.asarray(self.texture_arrays[b.reflectance_tex], dtype=np.float32).reshape(-1, 3)
+                d_mean = float(np.mean(a @ np.array([0.212671, 0.715160, 0.072169], np.float32)))
+            else:
+                d_mean = float(np.mean(np.asarray(b.reflectance[:], np.float32)))
+            s_mean = float(np.mean(np.asarray(b.transmittance[:], np.float32))) if sr is not None else 1.0
+            b.spec_sampling_weight = s_mean / (d_mean + s_mean)
         elif t in ("dielectric", "roughdielectric"):
             if flags & capi.BSDF_FLAG_TWOSIDED:
                 raise ValueError("Only materials without a transmission component can be nested!")
@@ -579,7 +605,7 @@ class SceneDesc:
             if not isinstance(v, dict):
                 continue
             t = v.get("type")
-            if t in ("diffuse", "roughconductor", "conductor", "dielectric", "roughdielectric", "twosided", "mask"):
+            if t in ("diffuse", "roughconductor", "conductor", "dielectric", "roughdielectric", "roughplastic", "twosided", "mask"):
                 self._add_bsdf(v, name)
         for name, v in d.items():   # declaration order defines the emitter order (scene.cpp:26-66)
             if not isinstance(v, dict):
@@ -597,7 +623,7 @@ class SceneDesc:
             elif t in ("path", "prb", "mypath", "path_test", "b2path", "b2path_mis", "b2prb"):
                 self.integrator_props = {k: v[k] for k in v if k != "type"}
                 self.integrator_props["type"] = t
-            elif t in ("diffuse", "roughconductor", "conductor", "dielectric", "roughdielectric", "twosided", "mask"):
+            elif t in ("diffuse", "roughconductor", "conductor", "dielectric", "roughdielectric", "roughplastic", "twosided", "mask"):
                 pass
             else:
                 raise ValueError(f"unsupported scene element {name!r} of type {t!r}")

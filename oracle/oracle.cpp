@@ -496,14 +496,17 @@ void orc_microfacet(int type, float au, float av, int visible, int op, const flo
     else if (op == 2) out[0] = d.smith_g1(V3(in[0], in[1], in[2]), V3(in[3], in[4], in[5]));
     else if (op == 3) out[0] = d.pdf(V3(in[0], in[1], in[2]), V3(in[3], in[4], in[5]));
 }
+void orc_rough_tables(int type, float alpha, float eta, float *trans64, float *internal_reflectance) { rough_tables(type, alpha, eta, trans64, *internal_reflectance); }
 // BSDF in local frame with constant reflectance. sample: out = wo3, pdf, eta, type, weight3 ; eval_pdf: out = val3, pdf
 void orc_bsdf_sample(const b2_bsdf *b, const float *wi, float s1, const float *s2, float *out9) {
-    b2_scene_desc d{}; Scene sc; sc.d = &d; SI si; si.valid = true; si.wi = V3(wi[0], wi[1], wi[2]); Counters c;
+    static b2_scene_desc d{}; static Scene sc; sc.d = &d;      // static: keeps the rough-plastic table cache between calls (single-threaded test hook)
+    SI si; si.valid = true; si.wi = V3(wi[0], wi[1], wi[2]); Counters c;
     BS bs; V3 w; bsdf_sample(sc, *b, si, s1, V2{ s2[0], s2[1] }, bs, w, c);
     out9[0] = bs.wo.x; out9[1] = bs.wo.y; out9[2] = bs.wo.z; out9[3] = bs.pdf; out9[4] = bs.eta; out9[5] = (float) bs.type; out9[6] = w.x; out9[7] = w.y; out9[8] = w.z;
 }
 void orc_bsdf_eval_pdf(const b2_bsdf *b, const float *wi, const float *wo, float *out4) {
-    b2_scene_desc d{}; Scene sc; sc.d = &d; SI si; si.valid = true; si.wi = V3(wi[0], wi[1], wi[2]); Counters c;
+    static b2_scene_desc d{}; static Scene sc; sc.d = &d;
+    SI si; si.valid = true; si.wi = V3(wi[0], wi[1], wi[2]); Counters c;
     V3 v; float pdf; bsdf_eval_pdf(sc, *b, si, V3(wo[0], wo[1], wo[2]), v, pdf, false, c);
     out4[0] = v.x; out4[1] = v.y; out4[2] = v.z; out4[3] = pdf;
 }

@@ -49,6 +49,7 @@ def lib():
         l.orc_pcg32_uints.argtypes = [C.c_uint64, C.c_uint64, C.c_int, vp]; l.orc_pcg32_uints.restype = None
         l.orc_sampler_floats.argtypes = [C.c_uint32, C.c_uint32, C.c_int, vp]; l.orc_sampler_floats.restype = None
         l.orc_microfacet.argtypes = [C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, vp, vp]; l.orc_microfacet.restype = None
+        l.orc_rough_tables.argtypes = [C.c_int, C.c_float, C.c_float, vp, vp]; l.orc_rough_tables.restype = None
         l.orc_bsdf_sample.argtypes = [C.POINTER(capi.Bsdf), vp, C.c_float, vp, vp]; l.orc_bsdf_sample.restype = None
         l.orc_bsdf_eval_pdf.argtypes = [C.POINTER(capi.Bsdf), vp, vp, vp]; l.orc_bsdf_eval_pdf.restype = None
         l.orc_texture_eval.argtypes = [C.POINTER(capi.Texture), C.c_float, C.c_float, vp, vp, vp]; l.orc_texture_eval.restype = None

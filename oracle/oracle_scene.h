@@ -50,8 +50,19 @@ struct BVHNode { float lo[3], hi[3]; uint32_t left, count; /* count>0: leaf, lef
 struct TraceLog { float *out; int max_records, n; };
 static thread_local TraceLog *g_trace_log = nullptr;
 
+static inline void rough_tables(int type, float alpha, float eta, float *trans, float &internal_reflectance);
+struct RoughTab { int type; float alpha, eta; float trans[64]; float internal_reflectance; };
+
 struct Scene {
     const b2_scene_desc *d = nullptr;
+    mutable std::vector<RoughTab> rough;  // rough-plastic tables by (distribution, alpha, eta); filled in init()
+    const RoughTab &rough_of(const b2_bsdf &b) const {
+        for (const RoughTab &t : rough) if (t.type == b.distribution && t.alpha == b.alpha_u && t.eta == b.ior) return t;
+        RoughTab t; t.type = b.distribution; t.alpha = b.alpha_u; t.eta = b.ior;     // (single-threaded callers only: init, test hooks)
+        rough_tables(t.type, t.alpha, t.eta, t.trans, t.internal_reflectance);
+        rough.push_back(t);
+        return rough.back();
+    }
     std::vector<BVHNode> nodes;
     std::vector<uint32_t> prims;          // face indices in leaf order
     std::vector<int> face_mesh;           // face -> mesh index
@@ -68,6 +79,8 @@ struct Scene {
             for (uint32_t f = 0; f < d->meshes[m].n_faces; ++f) face_mesh[d->meshes[m].first_face + f] = (int) m;
         for (uint32_t e = 0; e < d->n_emitters; ++e)
             if (d->emitters[e].type != B2_EMITTER_AREA) env_emitter = (int) e;
+        rough.reserve(d->n_bsdfs + 1);
+        for (uint32_t i = 0; i < d->n_bsdfs; ++i) if (d->bsdfs[i].type == B2_BSDF_ROUGHPLASTIC) rough_of(d->bsdfs[i]);
         build();
     }
 
@@ -440,11 +453,111 @@ struct Microfacet {
 };
 
 // ---------------------------------------------------------------------------------------------
+// Rough-plastic tables (roughplastic.cpp:232-262): external transmittance at 64 cosines and the internal diffuse
+// reflectance, by Gauss-Legendre quadrature over the visible-normal sampling domain (microfacet.h:463-570,
+// quad.h:27-86, math.h:93-120).
+// ---------------------------------------------------------------------------------------------
+static inline void legendre_pd(int l, double x, double &lc, double &dc) {
+    lc = 0; dc = 0;
+    if (l > 1) {
+        double l_p_pred = 1, l_pred = x, d_p_pred = 0, d_pred = 1, k0 = 3, k1 = 2, k2 = 1;
+        for (int ki = 2; ki <= l; ++ki) {
+            lc = (k0 * x * l_pred - k2 * l_p_pred) / k1; dc = d_p_pred + k0 * l_pred;
+            l_p_pred = l_pred; l_pred = lc; d_p_pred = d_pred; d_pred = dc; k2 = k1; k0 += 2; k1 += 1;
+        }
+    } else if (l == 0) { lc = 1; dc = 0; } else { lc = x; dc = 1; }
+}
+static inline void gauss_legendre(int n, std::vector<float> &nodes, std::vector<float> &weights) {
+    nodes.assign(n, 0.f); weights.assign(n, 0.f);
+    n--;
+    if (n == 0) { nodes[0] = 0.f; weights[0] = 2.f; return; }
+    int m = (n + 1) / 2;
+    for (int i = 0; i < m; ++i) {
+        double x = -cos((double) (2 * i + 1) / (double) (2 * n + 2) * 3.14159265358979323846), lc, dc;
+        for (int it = 0; it < 20; ++it) {
+            legendre_pd(n + 1, x, lc, dc);
+            double step = lc / dc; x -= step;
+            if (fabs(step) <= 4 * fabs(x) * 1.1102230246251565e-16) break;
+        }
+        legendre_pd(n + 1, x, lc, dc);
+        weights[i] = weights[n - i] = (float) (2 / ((1 - x * x) * (dc * dc)));
+        nodes[i] = (float) x; nodes[n - i] = (float) -x;
+    }
+    if ((n % 2) == 0) { double lc, dc; legendre_pd(n + 1, 0.0, lc, dc); weights[n / 2] = (float) (2.0 / (dc * dc)); nodes[n / 2] = 0.f; }
+}
+// eval_reflectance / eval_transmittance (microfacet.h:463-570) for one incident direction
+static inline float rough_quadrature(int type, float alpha, V3 wi, float eta, bool transmit) {
+    const int res = eta > 1.f ? 32 : 128;
+    std::vector<float> nodes, weights; gauss_legendre(res, nodes, weights);
+    Microfacet distr(type, alpha, alpha, true);
+    float result = 0.f;
+    for (int jy = 0; jy < res; ++jy) for (int jx = 0; jx < res; ++jx) {          // dr::meshgrid(nodes, nodes): x runs fastest
+        V2 node{ fmaf(nodes[jx], .5f, .5f), fmaf(nodes[jy], .5f, .5f) };
+        float pdf; V3 m = distr.sample(wi, node, pdf);
+        float f, cos_t, eta_it, eta_ti; fresnel(dot(wi, m), eta, f, cos_t, eta_it, eta_ti);
+        float smith;
+        if (transmit) {
+            V3 wo = fmadd(m, fmaf(dot(wi, m), eta_ti, cos_t), -(wi * eta_ti));   // refract(wi, m, cos_t, eta_ti)
+            smith = distr.smith_g1(wo, m) * (1.f - f);
+            if (wo.z * wi.z >= 0.f) smith = 0.f;
+        } else {
+            V3 wo = fmadd(m, 2.f * dot(wi, m), -wi);                              // reflect(wi, m)
+            smith = distr.smith_g1(wo, m) * f;
+            if (wo.z <= 0.f || wi.z <= 0.f) smith = 0.f;
+        }
+        result += smith * (weights[jx] * weights[jy]) * 0.25f;
+    }
+    return result;
+}
+constexpr int kRoughRes = 64;   // MI_ROUGH_TRANSMITTANCE_RES (roughplastic.cpp:21)
+static inline void rough_tables(int type, float alpha, float eta, float *trans, float &internal_reflectance) {
+    float acc = 0.f;
+    for (int i = 0; i < kRoughRes; ++i) {
+        float mu = fmaxf(1e-6f, (float) i * (1.f / (float) (kRoughRes - 1)));
+        V3 wi(sqrtf(1.f - mu * mu), 0.f, mu);
+        trans[i] = rough_quadrature(type, alpha, wi, eta, true);
+        acc += rough_quadrature(type, alpha, wi, 1.f / eta, false) * wi.z;
+    }
+    internal_reflectance = acc / (float) kRoughRes * 2.f;
+}
+
+// ---------------------------------------------------------------------------------------------
 // BSDFs.  `unit` = evaluate with the differentiable reflectance set to 1 (linear coefficient, PRB).
 // ---------------------------------------------------------------------------------------------
 static inline uint32_t bsdf_lobes(const b2_bsdf &b) {
-    uint32_t l = b.type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : ((b.type == B2_BSDF_ROUGHCONDUCTOR || b.type == B2_BSDF_ROUGHDIELECTRIC) ? LOBE_GLOSSY : (LOBE_DELTA_R | LOBE_DELTA_T));
+    uint32_t l = b.type == B2_BSDF_DIFFUSE ? LOBE_DIFFUSE : ((b.type == B2_BSDF_ROUGHCONDUCTOR || b.type == B2_BSDF_ROUGHDIELECTRIC) ? LOBE_GLOSSY
+               : (b.type == B2_BSDF_ROUGHPLASTIC ? (LOBE_GLOSSY | LOBE_DIFFUSE) : (LOBE_DELTA_R | LOBE_DELTA_T)));
     return (b.flags & B2_BSDF_FLAG_MASK) ? (l | LOBE_NULL) : l;     // mask.cpp:96-110: nested components + a null lobe
+}
+
+// RoughPlastic::lerp_gather (roughplastic.cpp:343-351)
+static inline float lerp_gather(const float *data, float x, int size) {
+    x *= (float) (size - 1);
+    uint32_t index = std::min((uint32_t) x, (uint32_t) (size - 2));
+    float v0 = data[index], v1 = data[index + 1];
+    return lerp(v0, v1, x - (float) index);
+}
+// RoughPlastic::eval / pdf (roughplastic.cpp:301-341, 353-393); wi.z > 0 and wo.z > 0 are the caller's precondition
+static inline void roughplastic_eval_pdf(const Scene &sc, const b2_bsdf &b, const SI &si, V3 wo, V3 &val, float &pdf, bool unit, Counters &c) {
+    const RoughTab &tab = sc.rough_of(b);
+    const float ci = si.wi.z, co = wo.z;
+    Microfacet distr(b.distribution, b.alpha_u, b.alpha_u, b.sample_visible != 0);
+    const V3 H = normalize(wo + si.wi);
+    const float D = distr.eval(H);
+    float F, cos_t, eta_it, eta_ti; fresnel(dot(si.wi, H), b.ior, F, cos_t, eta_it, eta_ti);
+    const float G = distr.G(si.wi, wo, H);
+    V3 value = V3(F * D * G / (4.f * ci)) * V3(b.transmittance[0], b.transmittance[1], b.transmittance[2]);   // specular_reflectance
+    const float t_i = lerp_gather(tab.trans, ci, kRoughRes), t_o = lerp_gather(tab.trans, co, kRoughRes);
+    V3 diff = unit ? V3(1.f) : sc.reflectance(b, si, c);
+    diff = diff / (V3(1.f) - (b.nonlinear ? diff * tab.internal_reflectance : V3(tab.internal_reflectance)));
+    const float inv_eta_2 = 1.f / (b.ior * b.ior);
+    val = value + diff * (InvPi * inv_eta_2 * co * t_i * t_o);
+    float prob_specular = (1.f - t_i) * b.spec_sampling_weight, prob_diffuse = t_i * (1.f - b.spec_sampling_weight);
+    prob_specular = prob_specular / (prob_specular + prob_diffuse); prob_diffuse = 1.f - prob_specular;
+    float r = b.sample_visible ? D * distr.smith_g1(si.wi, H) / (4.f * ci) : distr.pdf(si.wi, H) / (4.f * dot(wo, H));
+    r *= prob_specular;
+    r += prob_diffuse * square_to_cosine_hemisphere_pdf(wo);
+    pdf = r;
 }
 
 // SmoothDiffuse::eval_pdf (bsdfs/diffuse.cpp:159-179), RoughConductor::eval_pdf (roughconductor.cpp:429-518),
@@ -474,6 +587,9 @@ static inline void bsdf_eval_pdf_nested(const Scene &sc, const b2_bsdf &b, const
         v = v * refl;
         float p = b.sample_visible ? D * g1_wi / (4.f * ci) : distr.pdf(si.wi, H) / (4.f * dot(wo, H));
         if (active) { val = F * v; pdf = p; }
+    } else if (b.type == B2_BSDF_ROUGHPLASTIC) {
+        if (!(ci > 0.f && co > 0.f)) return;
+        roughplastic_eval_pdf(sc, b, si, wo, val, pdf, unit, c);
     } else if (b.type == B2_BSDF_ROUGHDIELECTRIC) {
         // RoughDielectric::eval_pdf (roughdielectric.cpp:503-605)
         if (ci == 0.f) return;
@@ -543,6 +659,24 @@ static inline void bsdf_sample(const Scene &sc, const b2_bsdf &b, const SI &si_,
             V3 F(fresnel_conductor(cm, b.eta[0], b.k[0]), fresnel_conductor(cm, b.eta[1], b.k[1]), fresnel_conductor(cm, b.eta[2], b.k[2]));
             V3 wv = V3(w) * sc.reflectance(b, si, c);
             if (active) weight = F * wv;
+        }
+    } else if (b.type == B2_BSDF_ROUGHPLASTIC) {
+        // RoughPlastic::sample (roughplastic.cpp:264-299)
+        if (ci > 0.f) {
+            const RoughTab &tab = sc.rough_of(b);
+            const float t_i = lerp_gather(tab.trans, ci, kRoughRes);
+            float prob_specular = (1.f - t_i) * b.spec_sampling_weight, prob_diffuse = t_i * (1.f - b.spec_sampling_weight);
+            prob_specular = prob_specular / (prob_specular + prob_diffuse);
+            bs.eta = 1.f;
+            if (s1 < prob_specular) {
+                Microfacet distr(b.distribution, b.alpha_u, b.alpha_u, b.sample_visible != 0);
+                float unused; V3 m = distr.sample(si.wi, s2, unused);
+                bs.wo = fmadd(m, 2.f * dot(si.wi, m), -si.wi); bs.type = LOBE_GLOSSY;
+            } else { bs.wo = square_to_cosine_hemisphere(s2); bs.type = LOBE_DIFFUSE; }
+            V3 value(0.f); float p = 0.f;
+            if (bs.wo.z > 0.f) roughplastic_eval_pdf(sc, b, si, bs.wo, value, p, false, c);
+            bs.pdf = p;
+            if (p > 0.f) weight = value / V3(p);
         }
     } else if (b.type == B2_BSDF_ROUGHDIELECTRIC) {
         // RoughDielectric::sample (roughdielectric.cpp:242-357)

@@ -5,7 +5,7 @@
 //   mitsuba/core/random.h               sample_tea_32 / sample_tea_float32
 //   mitsuba/core/warp.h                 square_to_* warps, interval_to_linear, square_to_bilinear
 //   mitsuba/render/fresnel.h            fresnel, fresnel_conductor
-//   mitsuba/render/microfacet.h         MicrofacetDistribution
+//   mitsuba/render/microfacet.h         MicrofacetDistribution, eval_transmittance / eval_reflectance (+ core/quad.h)
 //   mitsuba/core/distr_2d.h             Hierarchical2D<float, 0>
 //   mitsuba/core/vector.h               coordinate_system
 #include <vector>
@@ -69,6 +69,19 @@ void ref_microfacet(int type, float au, float av, int visible, int op, const flo
     else if (op == 1) out[0] = d.eval(Vector3f(in[0], in[1], in[2]));
     else if (op == 2) out[0] = d.smith_g1(Vector3f(in[0], in[1], in[2]), Vector3f(in[3], in[4], in[5]));
     else if (op == 3) out[0] = d.pdf(Vector3f(in[0], in[1], in[2]), Vector3f(in[3], in[4], in[5]));
+}
+// the rough-plastic precomputation exactly as RoughPlastic::parameters_changed runs it (roughplastic.cpp:232-262)
+void ref_rough_tables(int type, float alpha, float eta, float *trans64, float *internal_reflectance) {
+    using FloatX = dr::DynamicArray<float>;
+    using Vector3fX = Vector<FloatX, 3>;
+    using FloatP = dr::Packet<float>;
+    MicrofacetDistribution<FloatP, Color<float, 3>> distr(type == 0 ? MicrofacetType::Beckmann : MicrofacetType::GGX, alpha);
+    FloatX mu = dr::maximum(1e-6f, dr::linspace<FloatX>(0, 1, 64));
+    FloatX zero = dr::zeros<FloatX>(64);
+    Vector3fX wi = Vector3fX(dr::sqrt(1 - mu * mu), zero, mu);
+    auto t = eval_transmittance(distr, wi, eta);
+    for (int i = 0; i < 64; ++i) trans64[i] = t[i];
+    *internal_reflectance = dr::mean(eval_reflectance(distr, wi, 1.f / eta) * wi.z()) * 2.f;
 }
 // Hierarchical2D<float,0> over data [h][w]
 void *ref_h2d_create(const float *data, uint32_t w, uint32_t h) { return new Hierarchical2D<float, 0>(data, Vector<uint32_t, 2>(w, h)); }

@@ -343,3 +343,28 @@ def test_roughdielectric_parity(kernel, dist, visible):
         check_image(img.cpu().numpy(), ref, 0.99, 2e-3)
         for k in ("closest_rays", "shadow_rays", "vertices"):
             assert abs(cnt[k] - rc[k]) <= 2e-3 * max(rc[k], 1) + 2, (k, cnt[k], rc[k])
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_roughplastic_parity(kernel):
+    """RoughPlastic (roughplastic.cpp:216-430) as the bedroom uses it (scene.xml:108-143): GGX and Beckmann,
+    nonlinear, textured and constant diffuse_reflectance.  The device-side table precomputation (tables.cu) is covered through
+    the image: CUDA == oracle, whose own tables are pinned to the reference's eval_transmittance / eval_reflectance."""
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    from scenes_for_tests import value_noise_texture
+    d = cornell_box(64, 64, 16)
+    d["wood"] = {"type": "twosided", "nested": {"type": "roughplastic", "distribution": "ggx", "alpha": 0.15, "int_ior": 1.5, "ext_ior": 1.0,
+                                                 "nonlinear": True, "diffuse_reflectance": {"type": "bitmap", "data": value_noise_texture(), "raw": True}}}
+    d["panel"] = {"type": "roughplastic", "distribution": "beckmann", "alpha": 0.15, "int_ior": 1.5, "ext_ior": 1.0, "nonlinear": False,
+                  "diffuse_reflectance": [0.3, 0.5, 0.2], "specular_reflectance": [0.9, 0.9, 1.0]}
+    d["floor"]["bsdf"] = {"type": "ref", "id": "wood"}
+    d["large-box"]["bsdf"] = {"type": "ref", "id": "panel"}
+    ds = DeviceScene(d); orc = OracleScene(ds.desc)
+    assert 0.0 < ds.desc.bsdfs[ds.desc.bsdf_ids["panel"]].spec_sampling_weight < 1.0
+    for variant in (0, 1, 2):
+        kw = dict(seed=4, spp=16, max_depth=6, rr_depth=3, variant=variant)
+        img, cnt = ds.render(counters=True, kernel=kernel, all_shadow_rays=True, **kw)
+        ref, rc = orc.render(**kw)
+        check_image(img.cpu().numpy(), ref, 0.99, 2e-3)
+        for k in ("closest_rays", "shadow_rays", "vertices", "tex_evals"):
+            assert abs(cnt[k] - rc[k]) <= 2e-3 * max(rc[k], 1) + 2, (k, cnt[k], rc[k])
