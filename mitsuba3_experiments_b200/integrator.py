@@ -105,6 +105,14 @@ def load_dict(scene_dict: dict, device: int = 0, base_path: str = ".") -> Device
     return DeviceScene(scene_dict, device=device, base_path=base_path)
 
 
+def load_file(path: str, device: int = 0, **params) -> DeviceScene:
+    """``mi.load_file(path, **params)`` stand-in: the XML subset of xml_loader.py; keyword arguments override ``<default>``
+    parameters (``spp=16, resx=640`` ...), relative file names resolve against the directory of ``path``."""
+    import os
+    from .xml_loader import load_file as _xml
+    return DeviceScene(_xml(path, **params), device=device, base_path=os.path.dirname(os.path.abspath(path)))
+
+
 class _Props(dict):
     """Minimal ``mi.Properties``: ``props.get(name, default)``."""
 

@@ -368,3 +368,19 @@ def test_roughplastic_parity(kernel):
         check_image(img.cpu().numpy(), ref, 0.99, 2e-3)
         for k in ("closest_rays", "shadow_rays", "vertices", "tex_evals"):
             assert abs(cnt[k] - rc[k]) <= 2e-3 * max(rc[k], 1) + 2, (k, cnt[k], rc[k])
+
+
+def test_xml_scene_parity(tmp_path):
+    """a scene.xml in the bedroom's style (defaults, refs, OBJ mesh, bitmap file, the rank-1 material set)
+    loaded through load_file renders like the oracle fed the same dictionary."""
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    from mitsuba3_experiments_b200.integrator import load_file, make_integrator
+    from test_host import _write_mini_scene
+    ds = load_file(_write_mini_scene(tmp_path), spp=16, resx=48, resy=32)
+    orc = OracleScene(ds.desc)
+    integ = make_integrator(None, ds)                      # the <integrator> of the file: path, max_depth 5
+    assert integ.max_depth == 5
+    kw = dict(seed=1, spp=16, max_depth=5, rr_depth=3, variant=1)
+    img, _ = ds.render(**kw)
+    ref, _ = orc.render(**kw)
+    check_image(img.cpu().numpy(), ref, 0.99, 2e-3)
