@@ -43,6 +43,10 @@ def build_workload(name, n_gpus):
         spp = 64 * n_gpus
         d = scenes.bedroom_standin(1280, 720, spp)
         return d, dict(variant=1, max_depth=8, rr_depth=2), spp, "bedroom stand-in 1280x720 (1.8M tris, 2 area lights + envmap), path-mis.py loop"
+    if name == "bedroom4k":      # BASELINE.json configs[4]: fixed total work (strong scaling), 2 passes x 512 spp (integrator.cpp:251-257)
+        spp = 1024
+        d = scenes.bedroom_standin(3840, 2160, spp)
+        return d, dict(variant=1, max_depth=8, rr_depth=2), spp, "bedroom stand-in 3840x2160 1024 spp (1.8M tris, 2 area lights + envmap), path-mis.py loop, lanes sharded over the GPUs"
     if name == "cornell":
         spp = 16 * n_gpus
         return scenes.cornell_box(256, 256, spp), dict(variant=0, max_depth=8, rr_depth=4), spp, "mi.cornell_box() 256x256, path.py loop"
@@ -135,7 +139,7 @@ def run_reference(args, rank):
     ms = 1e3 * float(np.mean(times)); value = n / (ms * 1e-3) / 1e6
     sample = f"{sample_spp} spp of the {spp} spp workload per step ({n} paths)"
     line = {"impl": "reference", "metric": "path Msamples/s bedroom 720p", "value": value, "unit": "Msamples/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if args.workload == "bedroom4k" else "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": {"workload": wl, "sample": sample, "note": "CPU oracle port of the reference's llvm_ad_rgb path (Mitsuba not installable offline)"},
             "cpu_baseline": {"value": value, "unit": "Msamples/s", "cores": lib().orc_num_threads(), "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
@@ -148,9 +152,10 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b2", choices=["b2", "reference"])
-    ap.add_argument("--workload", default="bedroom", choices=["bedroom", "cornell"])
+    ap.add_argument("--workload", default="bedroom", choices=["bedroom", "cornell", "bedroom4k"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-prb", action="store_true")
+    ap.add_argument("--shard", default="samples", choices=["samples", "bands"], help="multi-GPU split: sample slices of every pixel (balanced) or image bands")
     ap.add_argument("--bands", type=int, default=2, help="image bands per rank (N > 1); bands are interleaved across ranks")
     args = ap.parse_args()
     rank_env = int(os.environ.get("RANK", "0"))
@@ -172,15 +177,22 @@ def main():
     ds = DeviceScene(scene_dict, device=local)
     H, W = ds.film_shape
     n_total = ds.wavefront_size(spp)
-    plan = b2dist.shard_plan(n_total, spp, W, world, rank, bands_per_rank=args.bands if world > 1 else 1)
+    spp_pp = n_total // (H * W)                              # samples per pixel per pass (< spp when H W spp exceeds 2^32 - 1 lanes)
+    paths_total = H * W * spp
+    plan = b2dist.shard_plan(n_total, spp_pp, W, world, rank, bands_per_rank=args.bands if world > 1 else 1)
     n_local = sum(b - a for a, b in plan)
+    shard = b2dist.sample_shard(spp_pp, world, rank) if args.shard == "samples" else None
+    shard_kw = {}
+    if shard is not None:                                   # every rank: all pixels, its slice of the samples of each pass
+        shard_kw = dict(sample_begin=shard[0], sample_count=shard[1])
+        plan = [(0, H * W * shard[1])]; n_local = plan[0][1]
     film = ds.new_film()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
     def render_bands(counters=False):
         tot = None
         for a, b in plan:
-            _, c = ds.render_film(film=film, counters=counters, seed=0, spp=spp, lane_begin=a, lane_end=b, **kw)
+            _, c = ds.render_film(film=film, counters=counters, seed=0, spp=spp, lane_begin=a, lane_end=b, **shard_kw, **kw)
             if counters:
                 tot = c if tot is None else {k: tot[k] + c[k] for k in c}
         return tot
@@ -220,7 +232,7 @@ def main():
     if world > 1:
         tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
     ms_per_step, kernel_ms = float(t[0]), float(t[1])
-    value = n_total / (ms_per_step * 1e-3) / 1e6
+    value = paths_total / (ms_per_step * 1e-3) / 1e6
 
     # end-to-end through host buffers
     film_h = torch.zeros((H, W, 4), dtype=torch.float32).pin_memory()
@@ -242,7 +254,7 @@ def main():
     t = torch.tensor([float(np.mean(e2e_times))], device=dev, dtype=torch.float64)
     if world > 1:
         tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
-    e2e_value = n_total / float(t[0]) / 1e6
+    e2e_value = paths_total / float(t[0]) / 1e6
 
     if world > 1:
         tdist.barrier(); tdist.destroy_process_group()
@@ -262,11 +274,11 @@ def main():
         pass
     launches_per_step = cnt["launches"] + 1                 # wavefront kernels of all bands (counted run) + k_develop
     line = {
-        "metric": "path Msamples/s bedroom 720p" if args.workload == "bedroom" else "path Msamples/s cornell 256x256",
+        "metric": {"bedroom": "path Msamples/s bedroom 720p", "bedroom4k": "path Msamples/s bedroom 2160p 1024 spp", "cornell": "path Msamples/s cornell 256x256"}[args.workload],
         "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wl, "spp_per_gpu": spp // world, "spp_total": spp, "paths_per_step": n_total, "max_depth": kw["max_depth"],
-                   "rr_depth": kw["rr_depth"], "parallelism": f"image bands x all samples over {world} GPU(s), NCCL film all-reduce",
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if args.workload == "bedroom4k" else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl, "spp_per_gpu": spp // world, "spp_total": spp, "paths_per_step": paths_total, "passes": spp // spp_pp, "max_depth": kw["max_depth"],
+                   "rr_depth": kw["rr_depth"], "parallelism": (f"all pixels x {shard[1]} of {spp_pp} samples per pass on each of {world} GPU(s)" if shard is not None else f"image bands x all samples over {world} GPU(s)") + ", NCCL film all-reduce",
                    "l2": "flushed between timed iterations (256 MiB memset)", "bvh_build_ms": ds.build_stats.ms_total,
                    "bvh_nodes": ds.build_stats.n_nodes8, "triangles": ds.build_stats.n_tris,
                    "rays_per_step_rank0": cnt["closest_rays"] + cnt["shadow_rays"], "Mrays_per_s_rank0": (cnt["closest_rays"] + cnt["shadow_rays"]) / (kernel_ms * 1e-3) / 1e6},

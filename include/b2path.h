@@ -173,6 +173,10 @@ typedef struct b2_render_args {
     uint32_t reserved;      /* bit 0 (render_backward only): reuse the weight film of the previous call with the same (seed, spp);
                                bit 1 (render): trace every shadow ray, also those of emitter samples whose value is exactly zero
                                (the reference does; the image is identical either way, only b2_counters.shadow_rays differs) */
+    uint32_t sample_begin, sample_count; /* sample shard: render only samples [sample_begin, sample_begin + sample_count) of every pixel
+                               of a pass (0, 0 = all).  Lane i of the shard is pixel i / sample_count, sample sample_begin + i % sample_count,
+                               and draws the stream of the global lane pixel * spp_per_pass + sample, so the union of the shards is
+                               the full render; lane_begin / lane_end then index the shard's own lanes.  Perfectly balanced multi-GPU split. */
 } b2_render_args;
 
 typedef struct b2_counters {

@@ -81,7 +81,7 @@ class SceneDesc(C.Structure):
 class RenderArgs(C.Structure):
     _fields_ = [("seed", u32), ("spp", u32), ("spp_per_pass", u32), ("max_depth", i32), ("rr_depth", i32),
                 ("variant", i32), ("kernel", i32), ("env_warp", i32), ("lane_begin", u64), ("lane_end", u64),
-                ("chunk_lanes", u32), ("reserved", u32)]
+                ("chunk_lanes", u32), ("reserved", u32), ("sample_begin", u32), ("sample_count", u32)]
 
 
 class Counters(C.Structure):

@@ -89,6 +89,14 @@ struct Path {
     uint32_t lane, pass;
 };
 
+// sample shard (b2_render_args.sample_begin / sample_count): the lane of the shard -> the lane of the full wavefront whose
+// PCG32 stream it draws (sampler.cpp:129-148 seeds by the global index)
+B2_DEV uint32_t global_lane(const RenderParams &p, uint32_t lane) {
+    if (p.remap_spp == 0u) return lane;
+    const uint32_t pix = (p.spp_shift != 0xffffffffu) ? (lane >> p.spp_shift) : (lane / p.spp_per_pass);
+    return pix * p.remap_spp + p.remap_off + (lane - pix * p.spp_per_pass);
+}
+
 // lane -> pixel (integrator.cpp:293-310) and the jittered film position (the first two draws of the lane's stream)
 B2_DEV f2 lane_sample_pos(const RenderParams &p, uint32_t lane, Pcg32 &rng, int &px, int &py) {
     const DSensor &sn = p.sc.sensor;

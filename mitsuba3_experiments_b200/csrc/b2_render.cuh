@@ -14,6 +14,7 @@ struct GradTargetDev { int32_t bsdf, kind; float *grad; };
 struct RenderParams {
     DScene sc;
     uint32_t seed, spp_per_pass, n_passes, spp_shift;   // spp_shift: log2(spp_per_pass) or 0xffffffff (integrator.cpp:293-300)
+    uint32_t remap_spp, remap_off;                       // sample shard: global samples per pixel per pass (0 = no shard) and first sample
     int32_t cull_nee;                                    // wavefront: skip shadow rays of zero-valued emitter samples
     int32_t max_depth, rr_depth, env_warp, filter_n;     // filter_n = ceil(radius - 0.5) (imageblock.cpp:438-441); box: 0
     uint64_t lane_begin, lane_end;                       // shard of the per-pass wavefront

@@ -280,6 +280,10 @@ static int derive_passes(const b2_scene *s, const b2_render_args *a, uint32_t &s
     if (wavefront > limit) { spp_per_pass /= (uint32_t) ((wavefront + limit - 1) / limit); wavefront = npix * spp_per_pass; }
     if (spp_per_pass == 0 || a->spp % spp_per_pass) return fail(-2, "sample_count must be a multiple of spp_per_pass");
     n_passes = a->spp / spp_per_pass;
+    if (a->sample_count) {       // sample shard: the shard's own wavefront has sample_count lanes per pixel
+        if ((uint64_t) a->sample_begin + a->sample_count > spp_per_pass) return fail(-2, "sample shard exceeds the samples per pixel of a pass");
+        wavefront = npix * a->sample_count;
+    }
     return 0;
 }
 
@@ -290,6 +294,8 @@ static int setup_params(b2_scene *s, const b2_render_args *a, int mode, bool cou
     if (a->max_depth < 0) return fail(-2, "render: max_depth = -1 (unbounded) is not supported; pass a finite depth");
     const DSensor &sn = s->d.sensor;
     p.sc = s->d;
+    p.remap_spp = 0; p.remap_off = 0;
+    if (a->sample_count) { p.remap_spp = spp_per_pass; p.remap_off = a->sample_begin; spp_per_pass = a->sample_count; }
     p.seed = a->seed; p.spp_per_pass = spp_per_pass; p.n_passes = mode == MODE_RENDER ? n_passes : 1;
     p.spp_shift = 0xffffffffu;
     for (uint32_t k = 0; k < 32; ++k) if ((1u << k) == spp_per_pass) p.spp_shift = k;
@@ -379,6 +385,7 @@ int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_i
     uint32_t spp_per_pass, n_passes; uint64_t wavefront;
     if (int rc = derive_passes(s, a, spp_per_pass, n_passes, wavefront)) return rc;
     if (n_passes != 1) return fail(-2, "render_backward: wavefront exceeds 2^32 lanes (common.py:358-363)");
+    if (a->sample_count) return fail(-2, "render_backward: sample shards are a render-only split (shard the adjoint by lane ranges)");
     const size_t film_bytes = sizeof(float) * 4 * (size_t) s->d.sensor.crop_width * s->d.sensor.crop_height;
     if (!s->wfilm) { CUDA_OK(cudaMalloc((void **) &s->wfilm, film_bytes)); s->allocs.push_back(s->wfilm); }
     const bool count = counters != nullptr;

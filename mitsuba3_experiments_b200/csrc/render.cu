@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_render(const __grid_constant_
                 if (i >= n_lanes) exhausted = true;
                 else {
                     s.lane = (uint32_t) (lane_lo + i); s.pass = 0; s.adjoint = false;
-                    s.rng.seed_lane(p.seed, s.lane);
+                    s.rng.seed_lane(p.seed, global_lane(p, s.lane));
                     start_path<V>(p, s);
                     have = true;
                 }
@@ -73,7 +73,7 @@ __global__ void __launch_bounds__(kBlockThreads) k_render(const __grid_constant_
                 if (!s.adjoint) {
                     // primal pass done (common.py:750-760); replay the identical stream for the adjoint pass (:763-773)
                     const f3 L = s.L;
-                    s.rng.seed_lane(p.seed, s.lane);
+                    s.rng.seed_lane(p.seed, global_lane(p, s.lane));
                     start_path<V>(p, s);
                     s.adjoint = true; s.L = L;
                     // dL = sum_p grad_in[p] * w(p) / W[p]   (adjoint of splat + develop, common.py:728-744)

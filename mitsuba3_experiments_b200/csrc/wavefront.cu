@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(256) k_wf_generate(const __grid_constant__ Ren
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < w.n; i += gridDim.x * blockDim.x) {
         Path s;
         s.lane = (uint32_t) (w.chunk_begin + i); s.pass = w.pass; s.adjoint = false; s.dL = f3(0.f);
-        if (w.pass == 0) s.rng.seed_lane(p.seed, s.lane);
+        if (w.pass == 0) s.rng.seed_lane(p.seed, global_lane(p, s.lane));
         else { const uint4 r = st.rng(i); s.rng.state = (uint64_t) r.x | ((uint64_t) r.y << 32); s.rng.inc = (uint64_t) r.z | ((uint64_t) r.w << 32); }
         start_path<V>(p, s);
         wf_store_path(st, i, s, true);
@@ -371,7 +371,7 @@ __global__ void __launch_bounds__(256) k_wf_generate_adj(const __grid_constant__
         Path s;
         s.lane = (uint32_t) (w.chunk_begin + i); s.pass = 0; s.adjoint = true;
         const float4 l = st.rad(i);
-        s.rng.seed_lane(p.seed, s.lane);
+        s.rng.seed_lane(p.seed, global_lane(p, s.lane));
         start_path<B2_VARIANT_PRB>(p, s);
         s.L = f3(l.x, l.y, l.z);
         f3 dL(0.f);
@@ -420,7 +420,7 @@ __global__ void __launch_bounds__(256) k_wf_splat(const __grid_constant__ Render
             f2 ps{ 0.f, 0.f }; f3 L(0.f);
             if (valid) {
                 if (WEIGHTS_ONLY) {             // weight film of the sample set: positions re-derived from (seed, lane)
-                    Pcg32 rng; const uint32_t ln = (uint32_t) (lane_lo + i); rng.seed_lane(p.seed, ln);
+                    Pcg32 rng; const uint32_t ln = (uint32_t) (lane_lo + i); rng.seed_lane(p.seed, global_lane(p, ln));
                     int px, py; ps = lane_sample_pos(p, ln, rng, px, py);
                     if (sn.rfilter == B2_RFILTER_BOX) ps = f2{ (float) px, (float) py };
                 } else {

@@ -25,6 +25,16 @@ def shard_plan(wavefront: int, spp_per_pass: int, width: int, world: int, rank: 
     return out
 
 
+def sample_shard(spp_per_pass: int, world: int, rank: int):
+    """(sample_begin, sample_count) of this rank: every rank renders every pixel with its own slice of the samples of a
+    pass, so the split is perfectly balanced whatever the image content (b2_render_args.sample_begin / sample_count).
+    Returns None when the samples do not divide evenly -- use shard_plan (image bands) then."""
+    if world <= 1 or spp_per_pass % world:
+        return None
+    n = spp_per_pass // world
+    return rank * n, n
+
+
 def init_from_env(backend: str | None = None):
     """Initialise torch.distributed from torchrun's environment (RANK / WORLD_SIZE / LOCAL_RANK / MASTER_*).
     Returns (rank, world, local_rank); a plain single-process run returns (0, 1, 0) without initialising anything."""

@@ -76,7 +76,7 @@ class DeviceScene:
 
     def make_args(self, seed=0, spp=None, max_depth=8, rr_depth=4, variant=capi.VARIANT_PATH, spp_per_pass=0,
                   lane_begin=0, lane_end=0, chunk_lanes=0, env_warp=capi.ENV_WARP_HIERARCHICAL, reuse_weights=False,
-                  kernel=capi.KERNEL_WAVEFRONT, all_shadow_rays=False):
+                  kernel=capi.KERNEL_WAVEFRONT, all_shadow_rays=False, sample_begin=0, sample_count=0):
         a = capi.RenderArgs()
         a.seed = int(seed) & 0xffffffff
         a.spp = int(spp or self.desc.spp); a.spp_per_pass = int(spp_per_pass)
@@ -84,6 +84,7 @@ class DeviceScene:
         a.kernel = int(kernel); a.env_warp = int(env_warp)
         a.lane_begin, a.lane_end, a.chunk_lanes = int(lane_begin), int(lane_end), int(chunk_lanes)
         a.reserved = (1 if reuse_weights else 0) | (2 if all_shadow_rays else 0)
+        a.sample_begin, a.sample_count = int(sample_begin), int(sample_count)
         return a
 
     def wavefront_size(self, spp, spp_per_pass=0):

@@ -327,6 +327,7 @@ int orc_render(void *hp, const b2_render_args *a, float *film_rgbw, b2_counters 
     Handle *h = (Handle *) hp; const b2_scene_desc &d = h->desc; const b2_sensor &s = d.sensor;
     uint32_t spp_per_pass, n_passes; uint64_t wavefront; derive_passes(d, *a, spp_per_pass, n_passes, wavefront);
     if (spp_per_pass == 0 || a->spp % spp_per_pass) { g_err = "sample_count must be a multiple of spp_per_pass"; return -2; }
+    if (a->sample_count) { g_err = "the oracle renders whole pixels only (sample shards are a product-side split)"; return -2; }
     uint64_t lb = a->lane_begin, le = a->lane_end ? a->lane_end : wavefront;
     Film film(s); Integrator integ(h->scene, a->max_depth, a->rr_depth);
     Counters total;

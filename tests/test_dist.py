@@ -59,3 +59,11 @@ def test_film_merge_gloo_world2(tmp_path):
     ref = torch.zeros((rows * width, 4))
     ref.index_add_(0, lanes // spp, torch.stack([torch.sin(lanes * 0.37), torch.cos(lanes * 0.11), lanes.float() / n, torch.ones(n)], 1))
     np.testing.assert_allclose(f0.reshape(-1, 4), ref.numpy(), rtol=1e-5, atol=1e-5)
+
+
+def test_sample_shard_partitions_samples():
+    from mitsuba3_experiments_b200.dist import sample_shard
+    for world in (2, 4, 8):
+        parts = [sample_shard(64, world, r) for r in range(world)]
+        assert [p[0] for p in parts] == [r * (64 // world) for r in range(world)] and all(p[1] == 64 // world for p in parts)
+    assert sample_shard(64, 1, 0) is None and sample_shard(6, 4, 1) is None      # single rank / uneven split -> image bands

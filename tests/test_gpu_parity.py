@@ -384,3 +384,26 @@ def test_xml_scene_parity(tmp_path):
     img, _ = ds.render(**kw)
     ref, _ = orc.render(**kw)
     check_image(img.cpu().numpy(), ref, 0.99, 2e-3)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_sample_shards_sum_to_the_full_render(kernel):
+    """Multi-GPU split by sample slices (b2_render_args.sample_begin / sample_count): shard lane i draws the stream of the
+    global lane pixel * spp + sample, so the shards' films add up to the full render (fp32 summation order aside) and the
+    event counters add up exactly; spp = 12 also covers the non-power-of-two lane -> pixel path."""
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    for spp, parts in ((16, 4), (12, 3)):
+        ds = DeviceScene(materials_scene(48, 32, spp, envmap=True, filter_type="tent"))
+        kw = dict(seed=7, spp=spp, max_depth=6, rr_depth=2, variant=1, kernel=kernel)
+        full, cf = ds.render_film(counters=True, **kw)
+        acc = ds.new_film(); tot = None
+        n = spp // parts
+        for r in range(parts):
+            _, c = ds.render_film(film=acc, counters=True, sample_begin=r * n, sample_count=n, **kw)
+            tot = c if tot is None else {k: tot[k] + c[k] for k in c}
+        a, b = acc.cpu().numpy(), full.cpu().numpy()
+        assert np.allclose(a, b, rtol=2e-5, atol=1e-5 * np.abs(b).max())
+        for k in ("samples", "closest_rays", "shadow_rays", "vertices", "tex_evals", "nee_area", "nee_env", "env_escapes", "splat_taps"):
+            assert tot[k] == cf[k], (k, tot[k], cf[k])
+    with pytest.raises(Exception):
+        ds.render_film(sample_begin=8, sample_count=8, **kw)             # exceeds the 12 samples of a pass
