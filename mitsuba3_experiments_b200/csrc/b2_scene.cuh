@@ -63,6 +63,9 @@ struct DScene {
     const float *area_cdf;
     const uint4 *nodes;              // 5 x uint4 per wide node
     const float4 *tris;              // 3 x float4 per triangle, leaf order
+    const float4 *shade;             // 6 x float4 per face (original face order): p0 p1 p2 n0 n1 n2 uv0 uv1 uv2, the inputs of
+                                     // Mesh::compute_surface_interaction gathered once at scene creation (one 96-B record per hit
+                                     // instead of a face -> 3 vertices x {pos, nrm, uv} pointer chase: 27 scalar loads -> 6 x 128-bit)
     uint32_t n_emitters, n_faces, n_nodes; int32_t env_emitter;
     uint32_t qmagic;                 // = 0x47: exponent byte of 32768 + q, read from the constant bank (b2_bvh.cuh, qbyte_biased)
     DEnvmap env;

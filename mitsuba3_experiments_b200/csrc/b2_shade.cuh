@@ -59,8 +59,9 @@ B2_DEV void make_si(const DScene &sc, const Ray &ray, const Hit &h, SI &si, Coun
     const uint32_t f = h.face;
     const DMesh m = sc.meshes[h.mesh];
     si.mesh = (int) h.mesh; si.bsdf = m.bsdf; si.emitter = m.emitter;
-    const uint32_t i0 = __ldg(sc.faces + 3 * (size_t) f), i1 = __ldg(sc.faces + 3 * (size_t) f + 1), i2 = __ldg(sc.faces + 3 * (size_t) f + 2);
-    const f3 p0 = load3(sc.pos, i0), p1 = load3(sc.pos, i1), p2 = load3(sc.pos, i2);
+    const float4 *rec = sc.shade + (size_t) f * 6;
+    const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2);
+    const f3 p0(r0.x, r0.y, r0.z), p1(r0.w, r1.x, r1.y), p2(r1.z, r1.w, r2.x);
     const float b1 = h.u, b2 = h.v, b0 = 1.f - b1 - b2;
     si.p = fmadd(p0, b0, fmadd(p1, b1, p2 * b2));
     const f3 dp0 = p1 - p0, dp1 = p2 - p0;
@@ -69,7 +70,8 @@ B2_DEV void make_si(const DScene &sc, const Ray &ray, const Hit &h, SI &si, Coun
     f3 dp_du, dp_dv;
     coordinate_system(si.n, dp_du, dp_dv);
     if (m.flags & B2_MESH_HAS_UV) {
-        const f2 uv0 = load2(sc.uv, i0), uv1 = load2(sc.uv, i1), uv2 = load2(sc.uv, i2);
+        const float4 r4 = __ldg(rec + 4), r5 = __ldg(rec + 5);
+        const f2 uv0{ r4.z, r4.w }, uv1{ r5.x, r5.y }, uv2{ r5.z, r5.w };
         si.uv.x = fma_(uv2.x, b2, fma_(uv1.x, b1, uv0.x * b0));
         si.uv.y = fma_(uv2.y, b2, fma_(uv1.y, b1, uv0.y * b0));
         const float du0x = uv1.x - uv0.x, du0y = uv1.y - uv0.y, du1x = uv2.x - uv0.x, du1y = uv2.y - uv0.y;
@@ -80,7 +82,8 @@ B2_DEV void make_si(const DScene &sc, const Ray &ray, const Hit &h, SI &si, Coun
         }
     }
     if (m.flags & B2_MESH_HAS_NORMALS) {
-        const f3 n0 = load3(sc.nrm, i0), n1 = load3(sc.nrm, i1), n2 = load3(sc.nrm, i2);
+        const float4 r3 = __ldg(rec + 3), r4n = __ldg(rec + 4);
+        const f3 n0(r2.y, r2.z, r2.w), n1(r3.x, r3.y, r3.z), n2(r3.w, r4n.x, r4n.y);
         const f3 n = fmadd(n2, b2, fmadd(n1, b1, n0 * b0));
         si.sh.n = n * rsqrt_(squared_norm(n));
     } else si.sh.n = si.n;

@@ -82,6 +82,21 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
     CUDA_OK(s->upload(desc->texcoords, (size_t) desc->n_vertices * 2, uv));
     CUDA_OK(s->upload(desc->faces, (size_t) desc->n_faces * 3, faces));
     d.pos = pos; d.nrm = nrm; d.uv = uv; d.faces = faces; d.n_faces = desc->n_faces;
+    for (size_t i = 0; i < (size_t) desc->n_faces * 3; ++i)
+        if (desc->faces[i] >= desc->n_vertices) return fail(-2, "b2_scene_create: face index out of bounds");
+    {   // per-face shading records (b2_scene.cuh, DScene::shade): the same fp32 values, regrouped
+        std::vector<float> rec((size_t) desc->n_faces * 24, 0.f);
+        for (size_t f = 0; f < desc->n_faces; ++f) {
+            float *r = rec.data() + f * 24;
+            for (int k = 0; k < 3; ++k) {
+                const size_t v = desc->faces[3 * f + k];
+                for (int c = 0; c < 3; ++c) r[3 * k + c] = desc->positions[3 * v + c];
+                if (desc->normals) for (int c = 0; c < 3; ++c) r[9 + 3 * k + c] = desc->normals[3 * v + c];
+                if (desc->texcoords) for (int c = 0; c < 2; ++c) r[18 + 2 * k + c] = desc->texcoords[2 * v + c];
+            }
+        }
+        float *rec_dev; CUDA_OK(s->upload(rec.data(), rec.size(), rec_dev)); d.shade = (const float4 *) rec_dev;
+    }
     // meshes + face -> mesh table
     std::vector<DMesh> meshes(desc->n_meshes); std::vector<uint32_t> face_mesh(desc->n_faces, 0);
     for (uint32_t i = 0; i < desc->n_meshes; ++i) {
@@ -94,8 +109,6 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
         meshes[i] = DMesh{ m.bsdf, m.emitter, m.flags, m.first_face, m.n_faces, cls, { 0, 0 } };
         for (uint32_t f = 0; f < m.n_faces; ++f) face_mesh[m.first_face + f] = i;
     }
-    for (size_t i = 0; i < (size_t) desc->n_faces * 3; ++i)
-        if (desc->faces[i] >= desc->n_vertices) return fail(-2, "b2_scene_create: face index out of bounds");
     DMesh *meshes_dev; CUDA_OK(s->upload(meshes.data(), meshes.size(), meshes_dev)); d.meshes = meshes_dev;
     CUDA_OK(s->upload(face_mesh.data(), face_mesh.size(), s->face_mesh_dev));
     // textures
