@@ -25,6 +25,7 @@
  *                             / PRBIntegrator.sample primal (prb.py:63-265)
  *   b2_develop             <- HDRFilm::develop (mi3/src/films/hdrfilm.cpp:304-405)
  *   b2_render_backward     <- RBIntegrator.render_backward (mi3/src/python/python/ad/integrators/common.py:623-781)
+ *   b2_render_forward      <- RBIntegrator.render_forward  (mi3/src/python/python/ad/integrators/common.py:495-621)
  *   b2_kernel_times        <- dr.kernel_history() as printed by path.py:332-351
  *   b2_trace               <- Scene::ray_intersect_preliminary / ray_test (mi3/src/render/scene.cpp:191-235)
  */
@@ -234,6 +235,11 @@ int  b2_develop(b2_scene *scene, const float *film_rgbw_dev, float *image_rgb_de
 /* grad_in_dev: [crop_h][crop_w][3]; runs weight-film splat, primal pass and adjoint replay for (seed, spp) */
 int  b2_render_backward(b2_scene *scene, const b2_render_args *args, const float *grad_in_dev,
                         const b2_grad_target *targets, int n_targets, uintptr_t stream, b2_counters *counters);
+/* Forward-mode PRB: RBIntegrator.render_forward (common.py:495-621).  tangents[t].grad_dev = DEVICE pointer to the tangent of
+   target t (3 floats for a constant reflectance, [h][w][3] for a bitmap; read only).  The lanes' d L are splatted into
+   film_rgbw_dev (accumulated, like b2_render); b2_develop of that film is the gradient image. */
+int  b2_render_forward(b2_scene *scene, const b2_render_args *args, const b2_grad_target *tangents, int n_targets,
+                       float *film_rgbw_dev, uintptr_t stream, b2_counters *counters);
 /* unit-test hook: rays_dev [n][8] = o.xyz, d.xyz, tmax, unused */
 int  b2_trace(b2_scene *scene, const float *rays_dev, uint64_t n, int any_hit, b2_hit *hits_dev, uintptr_t stream);
 /* host-buffer convenience entry points (what a reference-side binding with host arrays calls):

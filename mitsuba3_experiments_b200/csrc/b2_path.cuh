@@ -310,34 +310,47 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
         if (ADJ) {
             // d/d(reflectance) of [ Lr_dir + L * bsdf_val / detach(bsdf_weight * pdf) ] (prb.py:202-250); every
             // supported BSDF is linear in its reflectance, so the derivative is the value with reflectance := 1.
+            // forward mode (render_forward, common.py:495-621): the same coefficient with dL := 1, contracted with the
+            // parameter tangent at this vertex and accumulated in s.dL (the lane's d L, splatted after the replay)
+            const f3 dLw = p.forward ? f3(1.f) : s.dL;
             f3 g(0.f);
             if (active_em) {
                 f3 unit; float dummy; bsdf_eval_pdf<CLS>(bsdf, si.wi, wo, ones, unit, dummy);
-                g += s.dL * (f_before * mis_em * unit * em_weight);
+                g += dLw * (f_before * mis_em * unit * em_weight);
             }
             if (active) {
                 const f3 wo2 = si.sh.to_local(s.ray.d);
                 f3 unit; float dummy; bsdf_eval_pdf<CLS>(bsdf, si.wi, wo2, ones, unit, dummy);
                 const f3 det = bsdf_weight * bs.pdf;
                 const f3 inv(det.x != 0.f ? rcp(det.x) : 0.f, det.y != 0.f ? rcp(det.y) : 0.f, det.z != 0.f ? rcp(det.z) : 0.f);
-                g += s.dL * (s.L * (inv * unit));
+                g += dLw * (s.L * (inv * unit));
             }
             if (!is_zero(g)) {
                 for (int t = 0; t < p.n_targets; ++t) {
                     if (p.targets[t].bsdf != si.bsdf) continue;
+                    float *gp = p.targets[t].grad;
                     if (p.targets[t].kind == 0) {
-                        atomicAdd(gs.s_const + 3 * t, g.x); atomicAdd(gs.s_const + 3 * t + 1, g.y); atomicAdd(gs.s_const + 3 * t + 2, g.z);
-                        cnt.add(C_GRAD, 3);
+                        if (p.forward) s.dL += g * f3(__ldg(gp), __ldg(gp + 1), __ldg(gp + 2));
+                        else {
+                            atomicAdd(gs.s_const + 3 * t, g.x); atomicAdd(gs.s_const + 3 * t + 1, g.y); atomicAdd(gs.s_const + 3 * t + 2, g.z);
+                            cnt.add(C_GRAD, 3);
+                        }
                     } else {
                         uint32_t idx[4]; float w[4]; Counters<false> none;
                         tex_eval(sc, bsdf.tex, si.uv, idx, w, none);
-                        float *gp = p.targets[t].grad;
+                        if (p.forward) {
+                            f3 tan(0.f);
 #pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            atomicAdd(gp + 3 * (size_t) idx[q], g.x * w[q]); atomicAdd(gp + 3 * (size_t) idx[q] + 1, g.y * w[q]);
-                            atomicAdd(gp + 3 * (size_t) idx[q] + 2, g.z * w[q]);
+                            for (int q = 0; q < 4; ++q) tan += f3(__ldg(gp + 3 * (size_t) idx[q]), __ldg(gp + 3 * (size_t) idx[q] + 1), __ldg(gp + 3 * (size_t) idx[q] + 2)) * w[q];
+                            s.dL += g * tan;
+                        } else {
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                atomicAdd(gp + 3 * (size_t) idx[q], g.x * w[q]); atomicAdd(gp + 3 * (size_t) idx[q] + 1, g.y * w[q]);
+                                atomicAdd(gp + 3 * (size_t) idx[q] + 2, g.z * w[q]);
+                            }
+                            cnt.add(C_GRAD, 12);
                         }
-                        cnt.add(C_GRAD, 12);
                     }
                 }
             }

@@ -26,6 +26,7 @@ struct RenderParams {
     const float *grad_in;                                // [crop_h][crop_w][3]
     const float *wfilm;                                  // RGBW film holding the weights of this sample set
     GradTargetDev targets[kMaxGradTargets]; int32_t n_targets;
+    int32_t forward;                                     // adjoint replay in forward mode: targets[].grad are TANGENTS (read), dL accumulates d L
 };
 
 void launch_render(int variant, int mode, bool count, const RenderParams &p, int blocks, size_t smem, cudaStream_t st);

@@ -335,7 +335,7 @@ static int setup_params(b2_scene *s, const b2_render_args *a, int mode, bool cou
         p.unit_end = (uint32_t) ((pix1 / W) * p.units_per_row + (pix1 % W) / P) + 1;
     } else p.unit_begin = p.unit_end = 0;
     p.unit_counter = s->unit_counter; p.counters = count ? s->counters_dev : nullptr;
-    p.grad_in = nullptr; p.wfilm = nullptr; p.n_targets = 0; p.film = nullptr;
+    p.grad_in = nullptr; p.wfilm = nullptr; p.n_targets = 0; p.film = nullptr; p.forward = 0;
     int occ = render_occupancy(variant, mode, count, smem);
     if (occ <= 0) return fail(-12, "render: kernel cannot be resident (occupancy 0)");
     uint32_t units = p.unit_end - p.unit_begin;
@@ -389,6 +389,14 @@ int b2_develop(b2_scene *s, const float *film, float *image, uintptr_t stream) {
     return 0;
 }
 
+// PRB differentiates through f(reflectance) with "value at reflectance := 1" (b2_path.cuh): valid for BSDFs that are linear in
+// the reflectance slot and carry it on every lobe -- diffuse and rough conductor
+static int check_grad_target(const b2_scene *s, const b2_grad_target &g, const char *who) {
+    const int t = s->bsdfs[g.bsdf].type;
+    if (t == B2_BSDF_DIFFUSE || t == B2_BSDF_ROUGHCONDUCTOR) return 0;
+    return fail(-2, std::string(who) + ": the reflectance of this BSDF type (delta lobes, rough dielectric, rough plastic) is not a supported target");
+}
+
 int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_in, const b2_grad_target *targets, int n_targets,
                        uintptr_t stream, b2_counters *counters) {
     if (!s || !a || !grad_in || (n_targets && !targets)) return fail(-1, "b2_render_backward: null argument");
@@ -429,7 +437,7 @@ int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_i
             if (g.bsdf < 0 || g.bsdf >= (int) s->bsdfs.size() || !g.grad) return fail(-2, "b2_render_backward: bad gradient target");
             const bool textured = s->bsdfs[g.bsdf].reflectance_tex >= 0;
             if ((g.kind == 1) != textured) return fail(-2, "b2_render_backward: target kind does not match the BSDF's reflectance");
-            if (s->bsdfs[g.bsdf].type == B2_BSDF_DIELECTRIC || s->bsdfs[g.bsdf].type == B2_BSDF_CONDUCTOR || s->bsdfs[g.bsdf].type == B2_BSDF_ROUGHDIELECTRIC) return fail(-2, "b2_render_backward: delta-lobe (dielectric / conductor) reflectance is not a supported target");
+            if (int rc = check_grad_target(s, g, "b2_render_backward")) return rc;
             p.targets[t] = GradTargetDev{ g.bsdf, g.kind, g.grad };
         }
         CUDA_OK(cudaMemsetAsync(s->unit_counter, 0, 16, st));
@@ -447,6 +455,52 @@ int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_i
         } else if (p.unit_end > p.unit_begin) { launch_render(B2_VARIANT_PRB, MODE_BACKWARD, count, p, blocks, smem, st); launches++; }
         CUDA_OK(cudaGetLastError());
     }
+    if (count) {
+        unsigned long long h[C_N];
+        CUDA_OK(cudaMemcpyAsync(h, s->counters_dev, sizeof(h), cudaMemcpyDeviceToHost, st));
+        CUDA_OK(cudaStreamSynchronize(st));
+        export_counters(h, launches, counters);
+    }
+    s->launches += launches;
+    return 0;
+}
+
+int b2_render_forward(b2_scene *s, const b2_render_args *a, const b2_grad_target *tangents, int n_targets, float *film_rgbw_dev,
+                      uintptr_t stream, b2_counters *counters) {
+    if (!s || !a || !film_rgbw_dev || (n_targets && !tangents)) return fail(-1, "b2_render_forward: null argument");
+    if (n_targets < 0 || n_targets > kMaxGradTargets) return fail(-2, "b2_render_forward: too many tangent targets");
+    if (a->kernel != B2_KERNEL_WAVEFRONT || a->max_depth > 32) return fail(-2, "b2_render_forward: wavefront kernel with max_depth <= 32 only");
+    if (a->sample_count) return fail(-2, "b2_render_forward: sample shards are a render-only split (shard by lane ranges)");
+    CUDA_OK(cudaSetDevice(s->ctx->device));
+    cudaStream_t st = (cudaStream_t) stream;
+    uint32_t spp_per_pass, n_passes; uint64_t wavefront;
+    if (int rc = derive_passes(s, a, spp_per_pass, n_passes, wavefront)) return rc;
+    if (n_passes != 1) return fail(-2, "render_forward: wavefront exceeds 2^32 lanes (common.py:358-363)");
+    const bool count = counters != nullptr;
+    uint64_t launches = 0;
+    RenderParams p; int blocks; size_t smem;
+    if (int rc = setup_params(s, a, MODE_BACKWARD, count, p, blocks, smem, a->lane_begin, a->lane_end)) return rc;
+    p.forward = 1; p.film = film_rgbw_dev; p.n_targets = n_targets;
+    for (int t = 0; t < n_targets; ++t) {
+        const b2_grad_target &g = tangents[t];
+        if (g.bsdf < 0 || g.bsdf >= (int) s->bsdfs.size() || !g.grad) return fail(-2, "b2_render_forward: bad tangent target");
+        const bool textured = s->bsdfs[g.bsdf].reflectance_tex >= 0;
+        if ((g.kind == 1) != textured) return fail(-2, "b2_render_forward: target kind does not match the BSDF's reflectance");
+        if (int rc = check_grad_target(s, g, "b2_render_forward")) return rc;
+        p.targets[t] = GradTargetDev{ g.bsdf, g.kind, g.grad };
+    }
+    CUDA_OK(cudaMemsetAsync(s->unit_counter, 0, 16, st));
+    if (count) CUDA_OK(cudaMemsetAsync(s->counters_dev, 0, sizeof(unsigned long long) * C_N, st));
+    if (p.lane_end > p.lane_begin) {
+        if (int rc = wf_reserve(s, p.lane_end - p.lane_begin, a->chunk_lanes, st)) return rc;
+        const char *err = nullptr;
+        wf_set_timing(s->timing_on ? &s->timing : nullptr);
+        const long n = wf_render_backward(count, p, s->wf, s->ctx->sm_count, st, &err);
+        wf_set_timing(nullptr);
+        if (n < 0) return fail(-11, err ? err : "wavefront render_forward failed");
+        launches += (uint64_t) n;
+    }
+    CUDA_OK(cudaGetLastError());
     if (count) {
         unsigned long long h[C_N];
         CUDA_OK(cudaMemcpyAsync(h, s->counters_dev, sizeof(h), cudaMemcpyDeviceToHost, st));

@@ -324,6 +324,7 @@ __global__ void __launch_bounds__(256, (CLS == CLS_DIFFUSE || CLS == CLS_MISS) ?
             }
             alive = path_step<V, ADJ, COUNT, true, CLS>(p, s, gs, cnt, &h, &so);
             if (ADJ && !alive) cnt.add(C_SAMPLES);
+            if (ADJ && p.forward) st.dl[slot] = make_float4(s.dL.x, s.dL.y, s.dL.z, 0.f);
             wf_store_path(st, slot, s, alive);
             shadow = so.valid;
             if (shadow) {
@@ -375,7 +376,7 @@ __global__ void __launch_bounds__(256) k_wf_generate_adj(const __grid_constant__
         start_path<B2_VARIANT_PRB>(p, s);
         s.L = f3(l.x, l.y, l.z);
         f3 dL(0.f);
-        film_taps(p, s.pos, [&](int x, int y, float wgt) {
+        if (!p.forward) film_taps(p, s.pos, [&](int x, int y, float wgt) {
             const size_t pix = (size_t) y * sn.crop_width + x;
             float W = __ldg(p.wfilm + 4 * pix + 3); W = W == 0.f ? 1.f : W;
             const float k = wgt / W;
@@ -386,6 +387,15 @@ __global__ void __launch_bounds__(256) k_wf_generate_adj(const __grid_constant__
         st.hit(i) = make_float4(s.ray.maxt, 0.f, 0.f, __uint_as_float(0xffffffffu));
         st.hit_mesh(i) = 0xffffffffu;
         q[i] = i;
+    }
+}
+
+// forward mode: the accumulated d L of every lane becomes the value the splat kernel reads
+__global__ void __launch_bounds__(256) k_wf_dl_to_rad(const __grid_constant__ WfLaunch w) {
+    const WfState &st = w.st;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < w.n; i += gridDim.x * blockDim.x) {
+        const float4 g = st.dl[i]; float4 l = st.rad(i);
+        st.rad(i) = make_float4(g.x, g.y, g.z, l.w);
     }
 }
 
@@ -598,6 +608,12 @@ static long wf_render_backward_t(RenderParams p, WfState &st, int sm_count, cuda
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_trace, k_wf_trace<COUNT>, kTraceThreads, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<V, COUNT, false>, 256, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_adj, k_wf_shade<V, COUNT, true>, 256, 0);
+    int occ_splat = 1; const size_t smem_splat = sizeof(float4) * (size_t) p.tile_cols * p.tile_rows;
+    if (p.forward) {
+        cudaFuncSetAttribute(k_wf_splat<V, COUNT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem_splat);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_splat, k_wf_splat<V, COUNT, false>, 256, smem_splat);
+        if (occ_splat <= 0) { *err = "wavefront: the splat kernel cannot be resident"; return -1; }
+    }
     if (occ_trace <= 0 || occ_shade <= 0 || occ_adj <= 0) { *err = "wavefront: a kernel cannot be resident (occupancy 0)"; return -1; }
     if (p.max_depth > 32) { *err = "wavefront render_backward: max_depth > 32"; return -1; }
     const uint32_t n_iter = (uint32_t) std::max(p.max_depth, 1);
@@ -630,6 +646,18 @@ static long wf_render_backward_t(RenderParams p, WfState &st, int sm_count, cuda
             w.vis_bit = k;
             tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, true><<<g_adj, 256, 0, stream>>>(p, w); tm_end(stream); launches++;
             ++it;
+        }
+        if (p.forward) {
+            // forward mode: splat the lanes' d L (accumulated in the dL stream) like a render splats L (common.py:585-600)
+            const DSensor &sn = p.sc.sensor; const uint32_t W = (uint32_t) sn.crop_width, P = p.unit_pixels;
+            tm_begin(WF_K_OTHER, stream); k_wf_dl_to_rad<<<g_gen, 256, 0, stream>>>(w); tm_end(stream); launches++;
+            RenderParams ps = p;
+            const uint64_t pix0 = c0 / p.spp_per_pass, pix1 = (c0 + n - 1) / p.spp_per_pass;
+            ps.unit_begin = (uint32_t) ((pix0 / W) * p.units_per_row + (pix0 % W) / P);
+            ps.unit_end = (uint32_t) ((pix1 / W) * p.units_per_row + (pix1 % W) / P) + 1;
+            cudaMemsetAsync(p.unit_counter, 0, 4, stream);
+            const int g_splat = (int) std::min<uint32_t>(ps.unit_end - ps.unit_begin, (uint32_t) (occ_splat * sm_count));
+            tm_begin(WF_K_SPLAT, stream); k_wf_splat<V, COUNT, false><<<g_splat, 256, smem_splat, stream>>>(ps, w); tm_end(stream); launches++;
         }
     }
     if (cudaGetLastError() != cudaSuccess) { *err = "wavefront: kernel launch failed"; return -1; }

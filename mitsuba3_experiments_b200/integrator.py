@@ -44,11 +44,12 @@ class SceneParameters(dict):
         import torch
         self.scene = scene
         self.grad: dict[str, "torch.Tensor"] = {}
+        self.tangent: dict[str, "torch.Tensor"] = {}      # forward mode: d(param), see set_tangent / render_forward
         self._index: dict[str, tuple[int, str]] = {}
         d = scene.desc
         for i, (name, b) in enumerate(zip(d.bsdf_names, d.bsdfs)):
-            if b.type == capi.BSDF_DIELECTRIC:
-                continue
+            if b.type not in (capi.BSDF_DIFFUSE, capi.BSDF_ROUGHCONDUCTOR):
+                continue                              # PRB differentiates reflectances that scale every lobe linearly
             if b.reflectance_tex >= 0:
                 arr = d.texture_arrays[b.reflectance_tex]
                 if arr.dtype != np.float32:
@@ -89,6 +90,21 @@ class SceneParameters(dict):
             if k not in self.grad:
                 self.grad[k] = torch.zeros_like(v.detach(), dtype=torch.float32).contiguous()
             out.append((i, 1 if what == "data" else 0, self.grad[k]))
+        return out
+
+    def set_tangent(self, key, value):
+        """Forward mode: the direction d(param) along which ``render_forward`` differentiates (``dr.set_grad`` + ``dr.forward``)."""
+        import torch
+        if key not in self._index or key not in self:
+            raise KeyError(f"unknown scene parameter {key!r}")
+        t = as_device_tensor(value, self.scene.device, torch.float32)
+        self.tangent[key] = torch.broadcast_to(t, self[key].shape).contiguous()
+
+    def tangents(self):
+        out = []
+        for k, t in self.tangent.items():
+            i, what = self._index[k]
+            out.append((i, 1 if what == "data" else 0, t))
         return out
 
     def zero_grad(self):
@@ -213,8 +229,14 @@ class PRBIntegrator(B2Integrator):
         self.last_counters = ds.render_backward(grad_in, params.targets(), counters=counters, **a)
         return None
 
-    def render_forward(self, scene, params, sensor=0, seed=0, spp=0):
-        raise RuntimeError("render_forward (forward-mode PRB) is a 'next' row of the scope table (SURVEY.md 8f rank 3)")
+    def render_forward(self, scene, params: SceneParameters, sensor=0, seed=0, spp=0, counters=False):
+        """``RBIntegrator.render_forward`` (common.py:495-621): the gradient image for the parameter tangents set with
+        ``params.set_tangent(key, d_value)`` -- one primal pass, one replay that gathers d L per lane, one splat."""
+        ds = self._scene(scene)
+        a = self._args(ds, seed, spp)
+        a.pop("variant")
+        film, self.last_counters = ds.render_forward(params.tangents(), counters=counters, **a)
+        return ds.develop(film)
 
 
 _REGISTRY = {"mypath": Path, "path_test": PathIntegrator, "path": PathIntegrator, "prb": PRBIntegrator,

@@ -141,6 +141,22 @@ class DeviceScene:
                                                C.byref(cnt) if counters else None))
         return cnt.as_dict() if counters else None
 
+    def render_forward(self, tangents, film=None, counters=False, **kw):
+        """tangents: list of (bsdf_index, kind, tangent tensor on this device, read only).  Splats the lanes' d L into ``film``
+        (RGBW, accumulated) and returns (film, counters | None); ``develop(film)`` is the gradient image."""
+        kw.pop("variant", None)
+        a = self.make_args(variant=capi.VARIANT_PRB, **kw)
+        if film is None:
+            film = self.new_film()
+        arr = (capi.GradTarget * max(1, len(tangents)))()
+        for i, (b, k, g) in enumerate(tangents):
+            assert g.is_cuda and g.dtype == _torch().float32 and g.is_contiguous()
+            arr[i].bsdf, arr[i].kind, arr[i].grad = int(b), int(k), g.data_ptr()
+        cnt = capi.Counters() if counters else None
+        capi.check(self.lib.b2_render_forward(self.handle, C.byref(a), arr, len(tangents), film.data_ptr(), self._stream(),
+                                              C.byref(cnt) if counters else None))
+        return film, (cnt.as_dict() if counters else None)
+
     def trace(self, rays, any_hit=False):
         torch = _torch()
         r = as_device_tensor(rays, self.device, torch.float32).reshape(-1, 8)

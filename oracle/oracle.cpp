@@ -455,6 +455,56 @@ int orc_render_backward(void *hp, const b2_render_args *a, const float *grad_in,
     return 0;
 }
 
+// Forward-mode PRB (RBIntegrator.render_forward, common.py:495-621; prb.py:249-250 dr.forward_to(Lo)): the tangent image of the
+// render w.r.t. the reflectance parameters, dI = develop(splat(dL_lane)), dL_lane = sum over vertices of
+// (d Lo / d reflectance) . tangent(vertex) -- the same per-vertex coefficient the adjoint scatters, gathered instead.
+// tangents[t].grad = the tangent of target t (3 floats, or [h][w][3] for a bitmap).  film_rgbw is accumulated into.
+int orc_render_forward(void *hp, const b2_render_args *a, const b2_grad_target *tangents, int n_targets, float *film_rgbw, b2_counters *counters) {
+    Handle *h = (Handle *) hp; const b2_scene_desc &d = h->desc; const b2_sensor &s = d.sensor;
+    uint32_t spp_per_pass, n_passes; uint64_t wavefront; derive_passes(d, *a, spp_per_pass, n_passes, wavefront);
+    if (n_passes != 1) { g_err = "render_forward: wavefront exceeds 2^32 (common.py:358-363)"; return -2; }
+    if (a->sample_count) { g_err = "the oracle renders whole pixels only"; return -2; }
+    uint64_t lb = a->lane_begin, le = a->lane_end ? a->lane_end : wavefront;
+    Film film(s); Integrator integ(h->scene, a->max_depth, a->rr_depth);
+    Counters total;
+#pragma omp parallel
+    {
+        Counters c;
+#pragma omp for schedule(dynamic, 1024)
+        for (int64_t lane = (int64_t) lb; lane < (int64_t) le; ++lane) {
+            Sampler smp; smp.rng = sampler_seed(a->seed, (uint32_t) lane);
+            int px, py; lane_to_pos(s, (uint64_t) lane, spp_per_pass, px, py);
+            V2 j = smp.next_2d();
+            V2 sample_pos{ (float) px + j.x, (float) py + j.y };
+            Ray ray = camera_ray(s, adjusted_pos(s, sample_pos));
+            V2 splat = s.rfilter == B2_RFILTER_BOX ? V2{ (float) px, (float) py } : sample_pos;
+            Sampler clone = smp;
+            V3 L = integ.sample_prb(true, clone, ray, V3(0.f), V3(0.f), [](int, const SI &, V3) {}, c);
+            V3 fwd(0.f);
+            integ.sample_prb(false, smp, ray, V3(1.f), L, [&](int bsdf, const SI &si, V3 g) {
+                for (int t = 0; t < n_targets; ++t) {
+                    if (tangents[t].bsdf != bsdf) continue;
+                    const float *tp = tangents[t].grad;
+                    if (tangents[t].kind == 0) fwd += g * V3(tp[0], tp[1], tp[2]);
+                    else {
+                        uint32_t idx[4]; float w[4]; Counters cc;
+                        h->scene.tex_eval(d.bsdfs[bsdf].reflectance_tex, si.uv, idx, w, cc);
+                        V3 tan(0.f);
+                        for (int q = 0; q < 4; ++q) tan += V3(tp[3 * (size_t) idx[q]], tp[3 * (size_t) idx[q] + 1], tp[3 * (size_t) idx[q] + 2]) * w[q];
+                        fwd += g * tan;
+                    }
+                }
+            }, c);
+            film.put(splat, fwd, c); c.samples++;
+        }
+#pragma omp critical
+        total.add(c);
+    }
+    for (size_t i = 0; i < film.acc.size(); ++i) film_rgbw[i] += (float) film.acc[i];
+    export_counters(total, counters);
+    return 0;
+}
+
 // rays [n][8] = o, d, maxt, pad
 int orc_trace(void *hp, const float *rays, uint64_t n, int any_hit, b2_hit *hits) {
     Handle *h = (Handle *) hp;

@@ -33,6 +33,7 @@ def lib():
         l.orc_scene_destroy.argtypes = [vp]; l.orc_scene_destroy.restype = None
         l.orc_render.argtypes = [vp, C.POINTER(capi.RenderArgs), vp, C.POINTER(capi.Counters)]
         l.orc_develop.argtypes = [vp, vp, vp]
+        l.orc_render_forward.argtypes = [vp, C.POINTER(capi.RenderArgs), C.POINTER(capi.GradTarget), C.c_int, vp, C.POINTER(capi.Counters)]
         l.orc_render_backward.argtypes = [vp, C.POINTER(capi.RenderArgs), vp, C.POINTER(capi.GradTarget), C.c_int, C.POINTER(capi.Counters)]
         l.orc_trace.argtypes = [vp, vp, C.c_uint64, C.c_int, vp]
         l.orc_last_error.restype = C.c_char_p
@@ -119,6 +120,20 @@ class OracleScene:
         if lib().orc_render_backward(self.h, C.byref(a), _ptr(gi), arr, len(targets), C.byref(cnt)) != 0:
             raise RuntimeError(lib().orc_last_error().decode())
         return cnt.as_dict()
+
+    def render_forward(self, tangents, **kw):
+        """tangents: list of (bsdf_index, kind, tangent ndarray float32) -> (gradient image [H, W, 3], counters)."""
+        from mitsuba3_experiments_b200 import capi
+        a = self.make_args(variant=2, **kw)
+        arr = (capi.GradTarget * max(1, len(tangents)))(); keep = []
+        for i, (b, k, g) in enumerate(tangents):
+            g = np.ascontiguousarray(g, dtype=np.float32); keep.append(g)
+            arr[i].bsdf, arr[i].kind, arr[i].grad = b, k, g.ctypes.data
+        h, w = self.desc.film_shape
+        film = np.zeros((h, w, 4), dtype=np.float32); cnt = capi.Counters()
+        if lib().orc_render_forward(self.h, C.byref(a), arr, len(tangents), _ptr(film), C.byref(cnt)) != 0:
+            raise RuntimeError(lib().orc_last_error().decode())
+        return self.develop(film), cnt.as_dict()
 
     def debug_lane(self, lane, max_records=64, **kw):
         """-> (records [n][11] float32: ray(7), t, u, v, face-bits ; L rgb) for one lane (diagnostics)."""

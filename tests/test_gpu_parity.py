@@ -407,3 +407,42 @@ def test_sample_shards_sum_to_the_full_render(kernel):
             assert tot[k] == cf[k], (k, tot[k], cf[k])
     with pytest.raises(Exception):
         ds.render_film(sample_begin=8, sample_count=8, **kw)             # exceeds the 12 samples of a pass
+
+
+def test_render_forward_parity_fd_and_adjoint_consistency():
+    """b2_render_forward.  (1) CUDA == oracle per pixel for a constant and a bitmap tangent; (2) == central
+    finite differences of the CUDA primal render; (3) <grad_in, J t> == <J^T grad_in, t> with J^T from render_backward on the same
+    sample set -- forward and adjoint differentiate the same estimator."""
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    from mitsuba3_experiments_b200.integrator import PRBIntegrator, traverse
+    from mitsuba3_experiments_b200.scenes import cornell_prb_scene
+    d = cornell_prb_scene(48, 48, 16)
+    ds = DeviceScene(d); orc = OracleScene(ds.desc)
+    prb = PRBIntegrator({"max_depth": 5, "rr_depth": 3})
+    params = traverse(ds); params.keep(["white.reflectance.data", "red.reflectance.value"])
+    rng = np.random.RandomState(0)
+    t_tex = rng.uniform(-1, 1, size=tuple(params["white.reflectance.data"].shape)).astype(np.float32)
+    t_red = np.array([0.5, -1.0, 0.25], np.float32)
+    params.set_tangent("white.reflectance.data", t_tex); params.set_tangent("red.reflectance.value", t_red)
+    g = prb.render_forward(ds, params, seed=3, spp=16).cpu().numpy()
+    names = ds.desc.bsdf_ids
+    ref, _ = orc.render_forward([(names["white"], 1, t_tex), (names["red"], 0, t_red)], seed=3, spp=16, max_depth=5, rr_depth=3)
+    assert np.abs(g - ref).max() <= 1e-3 * np.abs(ref).max() and np.abs(g - ref).mean() <= 1e-5 * np.abs(ref).max()
+    # (2) finite differences of the primal render along the same direction
+    base_tex = params["white.reflectance.data"].clone(); base_red = params["red.reflectance.value"].clone()
+    def primal(eps):
+        params.update({"white.reflectance.data": base_tex + eps * torch.from_numpy(t_tex).to(base_tex.device),
+                       "red.reflectance.value": base_red + eps * torch.from_numpy(t_red).to(base_red.device)})
+        return prb.render(ds, seed=3, spp=16).cpu().numpy()
+    fd = (primal(1e-2) - primal(-1e-2)) / 2e-2
+    params.update({"white.reflectance.data": base_tex, "red.reflectance.value": base_red})
+    assert np.abs(g - fd).mean() / np.abs(fd).mean() < 5e-3
+    # (3) adjoint consistency
+    grad_in = torch.from_numpy(rng.uniform(-1, 1, size=g.shape).astype(np.float32)).to(base_tex.device)
+    params.zero_grad()
+    prb.render_backward(ds, params, grad_in, seed=3, spp=16)
+    torch.cuda.synchronize()
+    lhs = float((grad_in.cpu().numpy().astype(np.float64) * g).sum())
+    rhs = float((params.grad["white.reflectance.data"].cpu().numpy().astype(np.float64) * t_tex).sum()
+                + (params.grad["red.reflectance.value"].cpu().numpy().astype(np.float64) * t_red).sum())
+    assert abs(lhs - rhs) <= 2e-3 * max(abs(lhs), abs(rhs)), (lhs, rhs)
