@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define B2_ABI_VERSION 1
+#define B2_ABI_VERSION 2
 
 /* ------------------------------------------------------------------ enums */
 enum { B2_BSDF_DIFFUSE = 0, B2_BSDF_ROUGHCONDUCTOR = 1, B2_BSDF_DIELECTRIC = 2,
@@ -141,6 +141,9 @@ typedef struct b2_sensor {
     int32_t rfilter;        /* B2_RFILTER_* */
     float rfilter_radius;
     float gaussian_coeff[10]; /* gaussian.cpp:69-89 (llvm Remez/Estrin coefficients) */
+    int32_t sample_border;  /* film.sample_border (film.cpp:33): samples are also drawn on a rim of border_size =
+                               ceil(radius - 0.5) pixels around the crop window (integrator.cpp:134-136,306-307) */
+    int32_t reserved;
 } b2_sensor;
 
 typedef struct b2_scene_desc {

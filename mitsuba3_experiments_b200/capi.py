@@ -11,7 +11,7 @@ import os
 import subprocess
 import sys
 
-B2_ABI_VERSION = 1
+B2_ABI_VERSION = 2
 B2_MAX_WARP_LEVELS = 24
 
 # enums (keep in sync with b2path.h)
@@ -66,7 +66,7 @@ class Sensor(C.Structure):
     _fields_ = [("sample_to_camera", f32 * 16), ("to_world", f32 * 16), ("near_clip", f32), ("far_clip", f32),
                 ("film_width", i32), ("film_height", i32), ("crop_offset_x", i32), ("crop_offset_y", i32),
                 ("crop_width", i32), ("crop_height", i32), ("rfilter", i32), ("rfilter_radius", f32),
-                ("gaussian_coeff", f32 * 10)]
+                ("gaussian_coeff", f32 * 10), ("sample_border", i32), ("reserved", i32)]
 
 
 class SceneDesc(C.Structure):

@@ -102,8 +102,8 @@ B2_DEV f2 lane_sample_pos(const RenderParams &p, uint32_t lane, Pcg32 &rng, int 
     const DSensor &sn = p.sc.sensor;
     uint32_t idx = lane;
     idx = (p.spp_shift != 0xffffffffu) ? (idx >> p.spp_shift) : (idx / p.spp_per_pass);
-    const uint32_t y = idx / (uint32_t) sn.crop_width, x = idx - (uint32_t) sn.crop_width * y;
-    px = (int) x + sn.crop_offset_x; py = (int) y + sn.crop_offset_y;
+    const uint32_t y = idx / (uint32_t) sn.grid_w, x = idx - (uint32_t) sn.grid_w * y;
+    px = (int) x - sn.border + sn.crop_offset_x; py = (int) y - sn.border + sn.crop_offset_y;
     const f2 j = rng.next_2d();
     return f2{ (float) px + j.x, (float) py + j.y };
 }

@@ -55,6 +55,7 @@ struct DSensor {
     int32_t rfilter; float rfilter_radius, inv_radius;
     float gaussian_coeff[10];
     float scale_x, scale_y, offset_x, offset_y;  // integrator.cpp:432-436
+    int32_t grid_w, grid_h, border;              // lane grid = crop window + 2 * border (sample_border, integrator.cpp:134-136)
 };
 
 struct DScene {

@@ -204,6 +204,9 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
         o.offset_x = -(float) e.crop_offset_x * o.scale_x; o.offset_y = -(float) e.crop_offset_y * o.scale_y;
         int n = e.rfilter == B2_RFILTER_BOX ? 0 : (int) std::ceil(e.rfilter_radius - .5f);
         if (n > 2) return fail(-2, "b2_scene_create: reconstruction filter footprint larger than 5x5");
+        // ReconstructionFilter::border_size (rfilter.cpp:25) = ceil(radius - 1/2 - 2 RayEpsilon)
+        o.border = (e.sample_border && e.rfilter != B2_RFILTER_BOX) ? (int) std::ceil(e.rfilter_radius - .5f - 2.f * 1500.f * 5.9604644775390625e-8f) : 0;
+        o.grid_w = e.crop_width + 2 * o.border; o.grid_h = e.crop_height + 2 * o.border;
     }
     CUDA_OK(cudaMalloc((void **) &s->unit_counter, 16)); s->allocs.push_back(s->unit_counter);
     CUDA_OK(cudaMalloc((void **) &s->counters_dev, sizeof(unsigned long long) * C_N)); s->allocs.push_back(s->counters_dev);
@@ -287,7 +290,7 @@ static int wf_reserve(b2_scene *s, uint64_t shard_lanes, uint32_t chunk_lanes, c
 // integrator.cpp:139-152,247-265
 static int derive_passes(const b2_scene *s, const b2_render_args *a, uint32_t &spp_per_pass, uint32_t &n_passes, uint64_t &wavefront) {
     if (a->spp == 0) return fail(-2, "render: spp must be > 0");
-    const uint64_t npix = (uint64_t) s->d.sensor.crop_width * s->d.sensor.crop_height, limit = 0xffffffffull;
+    const uint64_t npix = (uint64_t) s->d.sensor.grid_w * s->d.sensor.grid_h, limit = 0xffffffffull;
     spp_per_pass = a->spp_per_pass ? std::min(a->spp_per_pass, a->spp) : a->spp;
     wavefront = npix * spp_per_pass;
     if (wavefront > limit) { spp_per_pass /= (uint32_t) ((wavefront + limit - 1) / limit); wavefront = npix * spp_per_pass; }
@@ -317,7 +320,7 @@ static int setup_params(b2_scene *s, const b2_render_args *a, int mode, bool cou
     p.filter_n = sn.rfilter == B2_RFILTER_BOX ? 0 : (int) std::ceil(sn.rfilter_radius - .5f);
     p.lane_begin = lane_begin; p.lane_end = lane_end ? std::min(lane_end, wavefront) : wavefront;
     if (p.lane_begin > p.lane_end) return fail(-2, "render: lane_begin > lane_end");
-    const uint32_t W = (uint32_t) sn.crop_width;
+    const uint32_t W = (uint32_t) sn.grid_w;
     // unit = run of pixels of one row x all samples; aim for >= 8 units per resident CTA, 1k..8k lanes per unit
     const int variant = mode == MODE_RENDER ? a->variant : B2_VARIANT_PRB;
     if (variant < 0 || variant > B2_VARIANT_PRB) return fail(-2, "render: unknown variant");

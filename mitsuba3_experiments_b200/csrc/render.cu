@@ -40,11 +40,11 @@ __global__ void __launch_bounds__(kBlockThreads) k_render(const __grid_constant_
         const uint32_t unit = s_unit;
         if (unit >= p.unit_end) break;
         const uint32_t row = unit / p.units_per_row, ux = unit - row * p.units_per_row;
-        const uint32_t x0 = ux * p.unit_pixels, x1 = min(x0 + p.unit_pixels, (uint32_t) sn.crop_width);
-        uint64_t lane_lo = ((uint64_t) row * sn.crop_width + x0) * p.spp_per_pass, lane_hi = ((uint64_t) row * sn.crop_width + x1) * p.spp_per_pass;
+        const uint32_t x0 = ux * p.unit_pixels, x1 = min(x0 + p.unit_pixels, (uint32_t) sn.grid_w);
+        uint64_t lane_lo = ((uint64_t) row * sn.grid_w + x0) * p.spp_per_pass, lane_hi = ((uint64_t) row * sn.grid_w + x1) * p.spp_per_pass;
         lane_lo = max(lane_lo, p.lane_begin); lane_hi = min(lane_hi, p.lane_end);
         const uint32_t n_lanes = lane_hi > lane_lo ? (uint32_t) (lane_hi - lane_lo) : 0u;
-        const int tx0 = (int) x0 - p.filter_n, ty0 = (int) row - p.filter_n;
+        const int tx0 = (int) x0 - sn.border - p.filter_n, ty0 = (int) row - sn.border - p.filter_n;   // crop-relative tile origin
         if (MODE != MODE_BACKWARD) for (uint32_t i = tid; i < tile_cells; i += kBlockThreads) s_tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (tid == 0) s_next = 0u;
         __syncthreads();

@@ -417,11 +417,11 @@ __global__ void __launch_bounds__(256) k_wf_splat(const __grid_constant__ Render
         const uint32_t unit = s_unit;
         if (unit >= p.unit_end) break;
         const uint32_t row = unit / p.units_per_row, ux = unit - row * p.units_per_row;
-        const uint32_t x0 = ux * p.unit_pixels, x1 = min(x0 + p.unit_pixels, (uint32_t) sn.crop_width);
-        uint64_t lane_lo = ((uint64_t) row * sn.crop_width + x0) * p.spp_per_pass, lane_hi = ((uint64_t) row * sn.crop_width + x1) * p.spp_per_pass;
+        const uint32_t x0 = ux * p.unit_pixels, x1 = min(x0 + p.unit_pixels, (uint32_t) sn.grid_w);
+        uint64_t lane_lo = ((uint64_t) row * sn.grid_w + x0) * p.spp_per_pass, lane_hi = ((uint64_t) row * sn.grid_w + x1) * p.spp_per_pass;
         lane_lo = max(lane_lo, c_lo); lane_hi = min(lane_hi, c_hi);
         const uint32_t n_lanes = lane_hi > lane_lo ? (uint32_t) (lane_hi - lane_lo) : 0u;
-        const int tx0 = (int) x0 - p.filter_n, ty0 = (int) row - p.filter_n;
+        const int tx0 = (int) x0 - sn.border - p.filter_n, ty0 = (int) row - sn.border - p.filter_n;   // crop-relative tile origin
         for (uint32_t i = tid; i < tile_cells; i += 256) s_tile[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         __syncthreads();
         const uint32_t g = (p.spp_shift != 0xffffffffu) ? min(p.spp_per_pass, 32u) : 1u;     // lanes per pixel group in a warp
@@ -537,7 +537,7 @@ template <int V, bool COUNT>
 static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {
     long launches = 0;
     const DSensor &sn = p.sc.sensor;
-    const uint32_t W = (uint32_t) sn.crop_width, P = p.unit_pixels;
+    const uint32_t W = (uint32_t) sn.grid_w, P = p.unit_pixels;
     int occ_trace = 0, occ_shade = 0, occ_splat = 0;
     const size_t smem_splat = sizeof(float4) * (size_t) p.tile_cols * p.tile_rows;
     cudaFuncSetAttribute(k_wf_splat<V, COUNT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem_splat);
@@ -649,7 +649,7 @@ static long wf_render_backward_t(RenderParams p, WfState &st, int sm_count, cuda
         }
         if (p.forward) {
             // forward mode: splat the lanes' d L (accumulated in the dL stream) like a render splats L (common.py:585-600)
-            const DSensor &sn = p.sc.sensor; const uint32_t W = (uint32_t) sn.crop_width, P = p.unit_pixels;
+            const DSensor &sn = p.sc.sensor; const uint32_t W = (uint32_t) sn.grid_w, P = p.unit_pixels;
             tm_begin(WF_K_OTHER, stream); k_wf_dl_to_rad<<<g_gen, 256, 0, stream>>>(w); tm_end(stream); launches++;
             RenderParams ps = p;
             const uint64_t pix0 = c0 / p.spp_per_pass, pix1 = (c0 + n - 1) / p.spp_per_pass;

@@ -70,9 +70,9 @@ def render_sharded(integrator, scene, seed=0, spp=0, rank=0, world=1, develop=Tr
     spp = spp or ds.desc.spp
     spp_pp = integrator.samples_per_pass or spp
     n = ds.wavefront_size(spp, integrator.samples_per_pass)
-    spp_pp = n // (ds.film_shape[0] * ds.film_shape[1])
+    spp_pp = n // (ds.lane_grid[0] * ds.lane_grid[1])
     film = ds.new_film()
-    for a, b in shard_plan(n, spp_pp, ds.film_shape[1], world, rank, bands_per_rank):
+    for a, b in shard_plan(n, spp_pp, ds.lane_grid[1], world, rank, bands_per_rank):
         integrator.render(ds, seed=seed, spp=spp, develop=False, evaluate=False, film=film, lane_begin=a, lane_end=b)
     merge_sum(film)
     return ds.develop(film) if develop else film
@@ -84,7 +84,7 @@ def render_backward_sharded(integrator, scene, params, grad_in, seed=0, spp=0, r
     ds = integrator._scene(scene)
     spp = spp or ds.desc.spp
     n = ds.wavefront_size(spp, 0)
-    for i, (a, b) in enumerate(shard_plan(n, spp, ds.film_shape[1], world, rank, bands_per_rank)):
+    for i, (a, b) in enumerate(shard_plan(n, spp, ds.lane_grid[1], world, rank, bands_per_rank)):
         integrator.render_backward(ds, params, grad_in, seed=seed, spp=spp, lane_begin=a, lane_end=b, reuse_weights=i > 0)
     for g in params.grad.values():
         merge_sum(g)

@@ -70,6 +70,10 @@ class DeviceScene:
     def film_shape(self):
         return self.desc.film_shape
 
+    @property
+    def lane_grid(self):
+        return self.desc.lane_grid
+
     def rebuild_accel(self, builder=-1):
         capi.check(self.lib.b2_scene_build_accel(self.handle, builder, self._stream(), C.byref(self.build_stats)))
         return self.build_stats.as_dict()
@@ -89,7 +93,7 @@ class DeviceScene:
 
     def wavefront_size(self, spp, spp_per_pass=0):
         """Lanes per pass (integrator.cpp:247-265)."""
-        h, w = self.film_shape
+        h, w = self.lane_grid
         spp_pp = min(spp_per_pass, spp) if spp_per_pass else spp
         n = h * w * spp_pp
         if n > 0xffffffff:

@@ -107,13 +107,25 @@ def srgb_to_linear(x):
 
 
 def parse_fov(props, aspect):
-    """mitsuba3/src/render/sensor.cpp:147-200 (fov variant only)."""
-    fov = float(props["fov"])
-    axis = str(props.get("fov_axis", "x")).lower()
-    if axis == "smaller":
-        axis = "y" if aspect > 1 else "x"
-    elif axis == "larger":
-        axis = "x" if aspect > 1 else "y"
+    """mitsuba3/src/render/sensor.cpp:146-199: ``fov`` + ``fov_axis``, or ``focal_length`` (default "50mm") over a 36x24 mm
+    frame measured along the diagonal."""
+    if "fov" in props and "focal_length" in props:
+        raise ValueError("specify either a focal length ('focal_length') or a field of view ('fov')")
+    if "fov" in props:
+        fov = float(props["fov"])
+        axis = str(props.get("fov_axis", "x")).lower()
+        if axis == "smaller":
+            axis = "y" if aspect > 1 else "x"
+        elif axis == "larger":
+            axis = "x" if aspect > 1 else "y"
+    else:
+        f = str(props.get("focal_length", "50mm"))
+        try:
+            value = float(f[:-2] if f.endswith("mm") else f)
+        except ValueError:
+            raise ValueError("could not parse the focal length (must be of the form <x>mm)") from None
+        fov = 2.0 * math.degrees(math.atan(math.sqrt(36.0 * 36.0 + 24.0 * 24.0) / (2.0 * value)))
+        axis = "diagonal"
     if axis == "x":
         return fov
     if axis == "y":
@@ -489,7 +501,7 @@ class SceneDesc:
         bsdf_spec = spec.get("bsdf")
         if bsdf_spec is None:
             bsdf_spec = {"type": "diffuse"}
-        bsdf = self._add_bsdf(bsdf_spec, None)
+        bsdf = self._add_bsdf(bsdf_spec, f"{name}.bsdf" if name else None)    # mi.traverse names it '<shape>.bsdf'
         mesh = capi.Mesh()
         mesh.first_vertex, mesh.n_vertices = self._nv, len(pos)
         mesh.first_face, mesh.n_faces = self._nf, len(faces)
@@ -567,8 +579,6 @@ class SceneDesc:
         fw, fh = int(film.get("width", 768)), int(film.get("height", 576))
         cw, ch = int(film.get("crop_width", fw)), int(film.get("crop_height", fh))
         cox, coy = int(film.get("crop_offset_x", 0)), int(film.get("crop_offset_y", 0))
-        if film.get("sample_border", False):
-            raise ValueError("film.sample_border is not supported yet")
         near, far = float(spec.get("near_clip", 1e-2)), float(spec.get("far_clip", 1e4))
         x_fov = parse_fov(spec, fw / fh)
         c2s = perspective_projection((fw, fh), (cw, ch), (cox, coy), x_fov, near, far)
@@ -578,6 +588,7 @@ class SceneDesc:
         s.near_clip, s.far_clip = near, far
         s.film_width, s.film_height = fw, fh
         s.crop_offset_x, s.crop_offset_y, s.crop_width, s.crop_height = cox, coy, cw, ch
+        s.sample_border = int(bool(film.get("sample_border", False)))
         rf = film.get("rfilter", {"type": "gaussian"})
         s.gaussian_coeff[:] = [0.0] * 10
         if rf["type"] == "gaussian":
@@ -689,6 +700,16 @@ class SceneDesc:
     @property
     def film_shape(self):
         return (self.sensor.crop_height, self.sensor.crop_width)
+
+    @property
+    def lane_grid(self):
+        """(rows, columns) of the pixel grid the lanes enumerate: the crop window plus, with ``film.sample_border``, a rim of
+        ``border_size = ceil(radius - 1/2 - 2 RayEpsilon)`` pixels on every side (integrator.cpp:134-136, rfilter.cpp:25)."""
+        s = self.sensor
+        b = 0
+        if s.sample_border and s.rfilter != capi.RFILTER_BOX:
+            b = int(math.ceil(np.float32(s.rfilter_radius) - np.float32(0.5) - np.float32(2 * 1500 * 2.0 ** -24)))
+        return (s.crop_height + 2 * b, s.crop_width + 2 * b)
 
     def bsdf_index(self, name: str) -> int:
         return self.bsdf_ids[name]

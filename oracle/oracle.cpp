@@ -258,9 +258,15 @@ struct Handle {
     b2_scene_desc desc; Scene scene;
 };
 
+static inline int sensor_border(const b2_sensor &s) {
+    // ReconstructionFilter::border_size = ceil(radius - 1/2 - 2 RayEpsilon) (rfilter.cpp:25); the box filter (radius 1/2) -> 0
+    return (s.sample_border && s.rfilter != B2_RFILTER_BOX) ? (int) std::ceil(s.rfilter_radius - .5f - 2.f * 1500.f * 5.9604644775390625e-8f) : 0;
+}
 static void derive_passes(const b2_scene_desc &d, const b2_render_args &a, uint32_t &spp_per_pass, uint32_t &n_passes, uint64_t &wavefront) {
     // integrator.cpp:139-152,247-265
-    uint64_t npix = (uint64_t) d.sensor.crop_width * d.sensor.crop_height;
+    // film_size = crop_size + 2 * border_size when film.sample_border is set (integrator.cpp:134-136)
+    const int b = sensor_border(d.sensor);
+    uint64_t npix = (uint64_t) (d.sensor.crop_width + 2 * b) * (d.sensor.crop_height + 2 * b);
     spp_per_pass = a.spp_per_pass ? std::min(a.spp_per_pass, a.spp) : a.spp;
     wavefront = npix * spp_per_pass;
     const uint64_t limit = 0xffffffffull;
@@ -274,8 +280,9 @@ static inline void lane_to_pos(const b2_sensor &s, uint64_t lane, uint32_t spp_p
     // integrator.cpp:293-310
     uint32_t idx = (uint32_t) lane, lg = 0; while ((1u << (lg + 1)) <= spp_per_pass) lg++;
     if ((1u << lg) == spp_per_pass) idx >>= lg; else idx /= spp_per_pass;
-    uint32_t y = idx / (uint32_t) s.crop_width, x = idx - (uint32_t) s.crop_width * y;
-    px = (int) x + s.crop_offset_x; py = (int) y + s.crop_offset_y;
+    const int b = sensor_border(s); const uint32_t gw = (uint32_t) (s.crop_width + 2 * b);
+    uint32_t y = idx / gw, x = idx - gw * y;
+    px = (int) x - b + s.crop_offset_x; py = (int) y - b + s.crop_offset_y;      // :306-309 pos -= border_size; pos += crop_offset
 }
 static inline V2 adjusted_pos(const b2_sensor &s, V2 sample_pos) {
     // integrator.cpp:432-436: scale = 1/crop_size, offset = -crop_offset*scale, fmadd(sample_pos, scale, offset)

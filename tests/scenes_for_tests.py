@@ -106,3 +106,16 @@ def mirror_scene(width=16, height=16, spp=4, tilt_deg=30.0, eta=(0.2, 0.92, 1.1)
         "plane": {"type": "rectangle", "to_world": T().rotate([1, 0, 0], tilt_deg).scale(50.0), "bsdf": {"type": "ref", "id": "m"}},
         "env": {"type": "constant", "radiance": {"type": "rgb", "value": list(radiance)}},
     }
+
+
+def crop_window_scene(filter_type="gaussian"):
+    """CropWindowConfig of the reference's PRB acceptance tests (test_ad_integrators.py:250-277 over ConfigBase :39-66):
+    a diffuse rectangle under a constant emitter, 64x64 film cropped to 32x32 at (32, 20), gaussian(0.5), sample_border."""
+    rf = {"type": "gaussian", "stddev": 0.5} if filter_type == "gaussian" else {"type": filter_type}
+    return {"type": "scene",
+            "plane": {"type": "rectangle", "bsdf": {"type": "diffuse"}},
+            "light": {"type": "constant"},
+            "sensor": {"type": "perspective", "to_world": T().look_at(origin=[0, 0, 4], target=[0, 0, 0], up=[0, 1, 0]),
+                       "film": {"type": "hdrfilm", "rfilter": rf, "width": 64, "height": 64, "sample_border": True,
+                                "crop_width": 32, "crop_height": 32, "crop_offset_x": 32, "crop_offset_y": 20,
+                                "pixel_format": "rgb", "component_format": "float32"}}}

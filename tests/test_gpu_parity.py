@@ -446,3 +446,55 @@ def test_render_forward_parity_fd_and_adjoint_consistency():
     rhs = float((params.grad["white.reflectance.data"].cpu().numpy().astype(np.float64) * t_tex).sum()
                 + (params.grad["red.reflectance.value"].cpu().numpy().astype(np.float64) * t_red).sum())
     assert abs(lhs - rhs) <= 2e-3 * max(abs(lhs), abs(rhs)), (lhs, rhs)
+
+
+@pytest.mark.parametrize("filter_type", ["gaussian", "tent", "box"])
+@pytest.mark.parametrize("kernel", [0, 1])
+def test_sample_border_crop_window_parity(kernel, filter_type):
+    """film.sample_border (integrator.cpp:134-136,306-309) -- the lanes enumerate the crop window plus a
+    rim of border_size pixels, the film stays crop-sized.  Both launch modes against the oracle, every filter, and the band
+    split over the wider lane grid."""
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    from scenes_for_tests import crop_window_scene
+    ds = DeviceScene(crop_window_scene(filter_type)); orc = OracleScene(ds.desc)
+    border = {"gaussian": 2, "tent": 1, "box": 0}[filter_type]
+    assert ds.film_shape == (32, 32) and ds.lane_grid == (32 + 2 * border,) * 2
+    kw = dict(seed=5, spp=16, max_depth=3, rr_depth=2, variant=1)
+    img, cnt = ds.render(counters=True, kernel=kernel, **kw)
+    ref, rcnt = orc.render(**kw)
+    check_image(img.cpu().numpy(), ref, 0.999, 1e-4)
+    assert cnt["samples"] == rcnt["samples"] == ds.lane_grid[0] * ds.lane_grid[1] * 16 and cnt["splat_taps"] == rcnt["splat_taps"]
+    # lane ranges over the wider grid: two halves accumulate to the whole
+    n = ds.wavefront_size(16); cut = (n // 2 // 16) * 16 + 16 * 7
+    film = ds.new_film()
+    ds.render_film(film=film, kernel=kernel, lane_begin=0, lane_end=cut, **kw)
+    ds.render_film(film=film, kernel=kernel, lane_begin=cut, lane_end=n, **kw)
+    check_image(ds.develop(film).cpu().numpy(), ref, 0.999, 1e-4)
+
+
+def test_reference_prb_goldens_crop_window_cuda():
+    """The reference's own stored PRB images (tests/golden/ref_ad_integrators.npz <- resources/data/tests/integrators/
+    test_crop_window_image_{primal,fwd}_ref.exr) under the reference's own acceptance criteria (test_ad_integrators.py:750-864),
+    through the public integrator API: primal, render_forward and render_backward."""
+    import os
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    from mitsuba3_experiments_b200.integrator import PRBIntegrator, Path, traverse
+    from scenes_for_tests import crop_window_scene
+    refs = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_ad_integrators.npz"))
+    ds = DeviceScene(crop_window_scene())
+    ref, fref = refs["crop_window_primal"], refs["crop_window_fwd"]
+    for integ in (Path({"max_depth": 2}), PRBIntegrator({"max_depth": 2})):
+        img = integ.render(ds, seed=0, spp=1024).cpu().numpy()
+        err = np.abs(img - ref) / np.maximum(np.abs(ref), 2e-2)
+        assert err.mean() < 0.01 and err.max() < 0.5, (err.mean(), err.max())
+    prb = PRBIntegrator({"max_depth": 2})
+    params = traverse(ds); key = "plane.bsdf.reflectance.value"; params.keep([key])
+    params.set_tangent(key, np.ones(3, np.float32))             # theta is added to every channel (ConfigBase.update :95-102)
+    fwd = prb.render_forward(ds, params, seed=0, spp=1024).cpu().numpy()
+    err = np.abs(fwd - fref) / np.maximum(np.abs(fref), 2e-1)
+    assert err.mean() < 0.05 and err.max() < 0.5, (err.mean(), err.max())
+    grad_in = torch.full((32, 32, 3), 0.001, device="cuda:0")
+    params.zero_grad()
+    prb.render_backward(ds, params, grad_in, seed=0, spp=256)
+    grad, grad_ref = float(params.grad[key].sum()) / fref.size, float(fref.mean()) * 0.001
+    assert abs(grad - grad_ref) / max(abs(grad_ref), 1e-3) < 0.05, (grad, grad_ref)
