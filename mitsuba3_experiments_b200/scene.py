@@ -485,6 +485,21 @@ class SceneDesc:
             faces = np.array([[1, 2, 0], [1, 3, 2]], dtype=np.uint32)
         elif t == "cube":
             pos = _xf_points(m, _CUBE_V); nrm = _xf_normals(m, _CUBE_N); uv = _CUBE_UV.copy(); faces = _CUBE_F.copy()
+        elif t == "sphere":
+            # sphere.cpp: `center` / `radius` in object space, then to_world; parameterisation (sin t cos p, sin t sin p, cos t),
+            # uv = (p / 2 pi, t / pi).  The hot path is triangles-only (SURVEY 8f rank 4 allows tessellation): a UV sphere with
+            # exact vertex normals, `tessellation` rings x 2 * `tessellation` segments (chord error r (1 - cos(pi / 2n)) = 7.5e-5 r).
+            nt = int(spec.get("tessellation", 64)); nph = 2 * nt
+            c0 = np.asarray(spec.get("center", [0.0, 0.0, 0.0]), np.float64); r0 = float(spec.get("radius", 1.0))
+            th, ph = np.meshgrid(np.linspace(0.0, np.pi, nt + 1), np.linspace(0.0, 2.0 * np.pi, nph + 1), indexing="ij")
+            loc = np.stack([np.sin(th) * np.cos(ph), np.sin(th) * np.sin(ph), np.cos(th)], axis=-1).reshape(-1, 3)
+            pos = _xf_points(m, c0 + r0 * loc); nrm = _xf_normals(m, loc)
+            uv = np.stack([ph / (2.0 * np.pi), th / np.pi], axis=-1).reshape(-1, 2).astype(np.float32)
+            i, j = np.meshgrid(np.arange(nt), np.arange(nph), indexing="ij")
+            v00 = (i * (nph + 1) + j).reshape(-1); v01 = v00 + 1; v10 = v00 + nph + 1; v11 = v10 + 1
+            upper = np.stack([v00, v10, v01], axis=1)[(i > 0).reshape(-1)]           # degenerate at the north pole
+            lower = np.stack([v10, v11, v01], axis=1)[(i < nt - 1).reshape(-1)]      # degenerate at the south pole
+            faces = np.concatenate([upper, lower]).astype(np.uint32)
         elif t == "obj":
             path = spec["filename"]
             if not os.path.isabs(path):
@@ -497,7 +512,7 @@ class SceneDesc:
             uv = np.asarray(spec["texcoords"], dtype=np.float32).reshape(-1, 2) if spec.get("texcoords") is not None else None
             faces = np.asarray(spec["faces"], dtype=np.uint32).reshape(-1, 3)
         else:
-            raise ValueError(f"unsupported shape type {t!r} (hot-path scope: rectangle, cube, obj, mesh)")
+            raise ValueError(f"unsupported shape type {t!r} (hot-path scope: rectangle, cube, sphere (tessellated), obj, mesh)")
         bsdf_spec = spec.get("bsdf")
         if bsdf_spec is None:
             bsdf_spec = {"type": "diffuse"}
@@ -622,7 +637,7 @@ class SceneDesc:
             if not isinstance(v, dict):
                 continue
             t = v.get("type")
-            if t in ("rectangle", "cube", "obj", "mesh"):
+            if t in ("rectangle", "cube", "sphere", "obj", "mesh"):
                 self._add_shape(name, v)
             elif t in ("envmap", "constant"):
                 if self.env is not None:

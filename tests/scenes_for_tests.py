@@ -119,3 +119,36 @@ def crop_window_scene(filter_type="gaussian"):
                        "film": {"type": "hdrfilm", "rfilter": rf, "width": 64, "height": 64, "sample_border": True,
                                 "crop_width": 32, "crop_height": 32, "crop_offset_x": 32, "crop_offset_y": 20,
                                 "pixel_format": "rgb", "component_format": "float32"}}}
+
+
+def ad_config_scene(name, res=128):
+    """The basic configs of the reference's PRB acceptance tests (test_ad_integrators.py:116-277) that stay inside the hot
+    path's scope -> (scene dict, max_depth, differentiated parameter key | None).  Spheres are tessellated (scene.py)."""
+    film = {"type": "hdrfilm", "rfilter": {"type": "gaussian", "stddev": 0.5}, "width": res, "height": res, "sample_border": True,
+            "pixel_format": "rgb", "component_format": "float32"}
+    d = {"type": "scene",
+         "sensor": {"type": "perspective", "to_world": T().look_at(origin=[0, 0, 4], target=[0, 0, 0], up=[0, 1, 0]), "film": film}}
+    side = T().translate([1.25, 0.0, 1.0]) @ T().rotate([0, 1, 0], -90)
+    if name == "crop_window":
+        return crop_window_scene(), 2, "plane.bsdf.reflectance.value"
+    if name == "diffuse_albedo":
+        d.update(plane={"type": "rectangle", "bsdf": {"type": "diffuse"}}, sphere={"type": "sphere", "to_world": T().scale(0.25)},
+                 light={"type": "constant"})
+        return d, 2, "plane.bsdf.reflectance.value"
+    if name == "diffuse_albedo_g_i":
+        d.update(plane={"type": "rectangle"}, sphere={"type": "sphere", "to_world": T().scale(0.25)},
+                 green={"type": "rectangle", "bsdf": {"type": "diffuse", "reflectance": {"type": "rgb", "value": [0.1, 1.0, 0.1]}}, "to_world": side},
+                 light={"type": "constant", "radiance": 3.0})
+        return d, 3, "green.bsdf.reflectance.value"
+    if name == "area_light_radiance":
+        d.update(plane={"type": "rectangle", "bsdf": {"type": "diffuse", "reflectance": {"type": "rgb", "value": [1.0, 1.0, 1.0]}}},
+                 sphere={"type": "sphere", "to_world": T().scale(0.25)},
+                 light={"type": "rectangle", "to_world": side, "emitter": {"type": "area", "radiance": {"type": "rgb", "value": [3.0, 3.0, 3.0]}}})
+        return d, 2, None
+    if name == "directly_visible_area_light_radiance":
+        d.update(light={"type": "rectangle", "emitter": {"type": "area", "radiance": {"type": "rgb", "value": [1.0, 1.0, 1.0]}}})
+        return d, 2, None
+    raise KeyError(name)
+
+
+AD_CONFIGS = ["crop_window", "diffuse_albedo", "diffuse_albedo_g_i", "area_light_radiance", "directly_visible_area_light_radiance"]
