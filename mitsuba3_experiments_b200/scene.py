@@ -5,7 +5,7 @@ as ``mi.cornell_box()``, mitsuba3/src/python/python/util.py:568-703).  Our CUDA 
 Mitsuba plugins, so this module understands the same dictionary schema for the plugin types on the hot path
  and flattens it:
 
-* shapes ``rectangle`` (rectangle.cpp:102-176), ``cube`` (cube.cpp:105-163), ``obj`` (obj.cpp subset) and a raw
+* shapes ``rectangle`` (rectangle.cpp:102-176), ``cube`` (cube.cpp:105-163), ``sphere`` (tessellated), ``obj`` (obj.cpp subset) and a raw
   ``mesh`` (explicit arrays) -> world-space vertex/normal/uv/face buffers (Mesh layout, mesh.h:564-568)
 * bsdfs ``diffuse``, ``roughconductor``, ``conductor``, ``dielectric``, ``roughdielectric``, ``roughplastic``, ``twosided`` (single nested BRDF), ``mask`` (constant opacity, outermost), ``ref``
 * textures ``rgb`` / plain lists, ``bitmap`` (filename | data array; fp16 storage rule of bitmap.cpp:231-246)

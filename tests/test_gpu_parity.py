@@ -472,28 +472,34 @@ def test_sample_border_crop_window_parity(kernel, filter_type):
     check_image(ds.develop(film).cpu().numpy(), ref, 0.999, 1e-4)
 
 
-def test_reference_prb_goldens_crop_window_cuda():
+@pytest.mark.parametrize("name", ["crop_window", "diffuse_albedo", "diffuse_albedo_g_i", "area_light_radiance",
+                                  "directly_visible_area_light_radiance"])
+def test_reference_prb_goldens_cuda(name):
     """The reference's own stored PRB images (tests/golden/ref_ad_integrators.npz <- resources/data/tests/integrators/
-    test_crop_window_image_{primal,fwd}_ref.exr) under the reference's own acceptance criteria (test_ad_integrators.py:750-864),
-    through the public integrator API: primal, render_forward and render_backward."""
+    test_<config>_image_{primal,fwd}_ref.exr) under the reference's own acceptance criteria and sample counts
+    (test_ad_integrators.py:750-864), through the public integrator API: primal with the path and prb integrators,
+    render_forward and render_backward for the configs that differentiate a reflectance."""
     import os
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
     from mitsuba3_experiments_b200.integrator import PRBIntegrator, Path, traverse
-    from scenes_for_tests import crop_window_scene
+    from scenes_for_tests import ad_config_scene
     refs = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_ad_integrators.npz"))
-    ds = DeviceScene(crop_window_scene())
-    ref, fref = refs["crop_window_primal"], refs["crop_window_fwd"]
-    for integ in (Path({"max_depth": 2}), PRBIntegrator({"max_depth": 2})):
+    d, max_depth, key = ad_config_scene(name)
+    ds = DeviceScene(d)
+    ref, fref = refs[f"{name}_primal"], refs[f"{name}_fwd"]
+    for integ in (Path({"max_depth": max_depth}), PRBIntegrator({"max_depth": max_depth})):
         img = integ.render(ds, seed=0, spp=1024).cpu().numpy()
         err = np.abs(img - ref) / np.maximum(np.abs(ref), 2e-2)
-        assert err.mean() < 0.01 and err.max() < 0.5, (err.mean(), err.max())
-    prb = PRBIntegrator({"max_depth": 2})
-    params = traverse(ds); key = "plane.bsdf.reflectance.value"; params.keep([key])
+        assert err.mean() < 0.01 and err.max() < 0.5, (err.mean(), err.max())     # reference thresholds: 0.05 / 0.5
+    if key is None:
+        return
+    prb = PRBIntegrator({"max_depth": max_depth})
+    params = traverse(ds); params.keep([key])
     params.set_tangent(key, np.ones(3, np.float32))             # theta is added to every channel (ConfigBase.update :95-102)
     fwd = prb.render_forward(ds, params, seed=0, spp=1024).cpu().numpy()
     err = np.abs(fwd - fref) / np.maximum(np.abs(fref), 2e-1)
     assert err.mean() < 0.05 and err.max() < 0.5, (err.mean(), err.max())
-    grad_in = torch.full((32, 32, 3), 0.001, device="cuda:0")
+    grad_in = torch.full(fref.shape, 0.001, device="cuda:0")
     params.zero_grad()
     prb.render_backward(ds, params, grad_in, seed=0, spp=256)
     grad, grad_ref = float(params.grad[key].sum()) / fref.size, float(fref.mean()) * 0.001
