@@ -19,6 +19,27 @@ struct WfCtl {                       // device-side queue bookkeeping, slot = it
     uint32_t n_class[4][8];          // hits of iteration it per shading class (queues qc[cls])
 };
 
+// Lane-state accessor.  Experiment (B2_STATE_CS=1): every stream element is read once and written once per bounce and a chunk's
+// state (GBs) is far larger than L2, so the accesses could carry the evict-first hint (ld.global.cs / st.global.cs) and leave L2
+// to the data that is reused (nodes, triangles, per-face records, textures).  Measured on the bedroom stand-in: trace 44.4 ->
+// 43.6 ms but shade 24.0 -> 25.8 ms (what a shade kernel writes is what classify / trace read next, and evict-first loses the
+// part of it that still sat in L2), net 789 -> 775 Msamples/s: off.  The L2 node pin of capi.cu gets the trace gain alone.
+#ifndef B2_STATE_CS
+#define B2_STATE_CS 0
+#endif
+template <class T> struct StateRef {
+    T *p;
+#if B2_STATE_CS
+    B2_DEV operator T() const { return __ldcs(p); }
+    B2_DEV const StateRef &operator=(const T &v) const { __stcs(p, v); return *this; }
+#else
+    B2_DEV operator T() const { return *p; }
+    B2_DEV const StateRef &operator=(const T &v) const { *p = v; return *this; }
+#endif
+    B2_DEV const StateRef &operator=(const StateRef &o) const { return *this = (T) o; }
+    B2_DEV T *ptr() const { return p; }
+};
+
 struct WfState {                     // `capacity` lane slots (slot = lane - chunk_begin)
     // Lane state = four streams of 32-byte elements (two 16-byte words each, grouped by which kernel touches them
     // together).  A 32-byte element is exactly one DRAM/L2 sector, so a lane costs whole sectors however sparse or
@@ -33,20 +54,20 @@ struct WfState {                     // `capacity` lane slots (slot = lane - chu
     float4 *s1;                      //               factor a            , factor b   (L <- fma(a, b, L) on arrival)
     float4 *dl;                      // PRB adjoint: dL (adjoint radiance of the lane's splat), xyz
     uint8_t *cls_q;                  // shading class of the hit of queue entry i of the current iteration (trace -> classify)
-    B2_DEV float4 &ray_o(uint32_t s) const { return p0[(size_t) s * 2]; }
-    B2_DEV float4 &ray_d(uint32_t s) const { return p0[(size_t) s * 2 + 1]; }
-    B2_DEV float4 &hit(uint32_t s) const { return p1[(size_t) s * 2]; }
-    B2_DEV uint32_t &hit_mesh(uint32_t s) const { return ((uint32_t *) (p1 + (size_t) s * 2 + 1))[0]; }
-    B2_DEV uint32_t &vis(uint32_t s) const { return ((uint32_t *) (p1 + (size_t) s * 2 + 1))[1]; }
-    B2_DEV float2 &pos(uint32_t s) const { return ((float2 *) (p1 + (size_t) s * 2 + 1))[1]; }
-    B2_DEV uint4 &rng(uint32_t s) const { return ((uint4 *) p2)[(size_t) s * 2]; }
-    B2_DEV float4 &thr(uint32_t s) const { return p2[(size_t) s * 2 + 1]; }
-    B2_DEV float4 &rad(uint32_t s) const { return p3[(size_t) s * 2]; }
-    B2_DEV float4 &prev(uint32_t s) const { return p3[(size_t) s * 2 + 1]; }
-    B2_DEV float4 &sh_o(uint32_t s) const { return s0[(size_t) s * 2]; }
-    B2_DEV float4 &sh_d(uint32_t s) const { return s0[(size_t) s * 2 + 1]; }
-    B2_DEV float4 &sh_a(uint32_t s) const { return s1[(size_t) s * 2]; }
-    B2_DEV float4 &sh_b(uint32_t s) const { return s1[(size_t) s * 2 + 1]; }
+    B2_DEV StateRef<float4> ray_o(uint32_t s) const { return StateRef<float4>{ &p0[(size_t) s * 2] }; }
+    B2_DEV StateRef<float4> ray_d(uint32_t s) const { return StateRef<float4>{ &p0[(size_t) s * 2 + 1] }; }
+    B2_DEV StateRef<float4> hit(uint32_t s) const { return StateRef<float4>{ &p1[(size_t) s * 2] }; }
+    B2_DEV StateRef<uint32_t> hit_mesh(uint32_t s) const { return StateRef<uint32_t>{ &((uint32_t *) (p1 + (size_t) s * 2 + 1))[0] }; }
+    B2_DEV StateRef<uint32_t> vis(uint32_t s) const { return StateRef<uint32_t>{ &((uint32_t *) (p1 + (size_t) s * 2 + 1))[1] }; }
+    B2_DEV StateRef<float2> pos(uint32_t s) const { return StateRef<float2>{ &((float2 *) (p1 + (size_t) s * 2 + 1))[1] }; }
+    B2_DEV StateRef<uint4> rng(uint32_t s) const { return StateRef<uint4>{ &((uint4 *) p2)[(size_t) s * 2] }; }
+    B2_DEV StateRef<float4> thr(uint32_t s) const { return StateRef<float4>{ &p2[(size_t) s * 2 + 1] }; }
+    B2_DEV StateRef<float4> rad(uint32_t s) const { return StateRef<float4>{ &p3[(size_t) s * 2] }; }
+    B2_DEV StateRef<float4> prev(uint32_t s) const { return StateRef<float4>{ &p3[(size_t) s * 2 + 1] }; }
+    B2_DEV StateRef<float4> sh_o(uint32_t s) const { return StateRef<float4>{ &s0[(size_t) s * 2] }; }
+    B2_DEV StateRef<float4> sh_d(uint32_t s) const { return StateRef<float4>{ &s0[(size_t) s * 2 + 1] }; }
+    B2_DEV StateRef<float4> sh_a(uint32_t s) const { return StateRef<float4>{ &s1[(size_t) s * 2] }; }
+    B2_DEV StateRef<float4> sh_b(uint32_t s) const { return StateRef<float4>{ &s1[(size_t) s * 2 + 1] }; }
     uint32_t *q[2];                  // closest-ray queues (lane slots), double buffered by iteration parity
     uint32_t *q_shadow[2];           // shadow-ray queues, by iteration parity
     uint32_t *qc[5];                 // closest hits of the current iteration sorted by shading class (CLS_*)

@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
             if (r.any) {
                 if (!r.found) {         // the emitter sample arrives: L <- fma(a, b, L)
                     if (r.tex) cnt.add(C_TEX);
-                    if (w.vis_bit != 0xffffffffu) st.vis(r.slot) |= 1u << w.vis_bit;
+                    if (w.vis_bit != 0xffffffffu) st.vis(r.slot) = (uint32_t) st.vis(r.slot) | (1u << w.vis_bit);
                     const float4 a = st.sh_a(r.slot), b = st.sh_b(r.slot); float4 L = st.rad(r.slot);
                     L.x = fma_(a.x, b.x, L.x); L.y = fma_(a.y, b.y, L.y); L.z = fma_(a.z, b.z, L.z);
                     st.rad(r.slot) = L;

@@ -99,7 +99,31 @@ def test_parse_fov_and_filters():
     with pytest.raises(ValueError):
         SceneDesc({"type": "scene", "sensor": {"type": "thinlens", "fov": 45}})
     with pytest.raises(ValueError):
-        SceneDesc({"type": "scene", "s": {"type": "sphere"}, "sensor": {"type": "perspective", "fov": 45}})
+        SceneDesc({"type": "scene", "s": {"type": "cylinder"}, "sensor": {"type": "perspective", "fov": 45}})
+    # default focal length 50 mm over the 36 x 24 mm diagonal (sensor.cpp:163-177)
+    assert parse_fov({}, 1.0) == pytest.approx(34.0221, abs=1e-3) and parse_fov({"focal_length": "50mm"}, 1.5) == pytest.approx(39.5978, abs=1e-3)
+    with pytest.raises(ValueError):
+        parse_fov({"fov": 45, "focal_length": "35mm"}, 1.0)
+
+
+def test_tessellated_sphere_and_lane_grid():
+    """sphere.cpp (center / radius / to_world, uv = (phi / 2 pi, theta / pi)) as a closed, outward-oriented UV sphere with
+    exact vertex normals; film.sample_border widens the lane grid by rfilter.border_size (rfilter.cpp:25)."""
+    film = {"type": "hdrfilm", "width": 8, "height": 6, "sample_border": True, "rfilter": {"type": "tent"}}
+    d = {"type": "scene", "s": {"type": "sphere", "center": [1, 2, 3], "radius": 0.5, "tessellation": 16},
+         "sensor": {"type": "perspective", "fov": 45, "film": film}}
+    sd = SceneDesc(d)
+    pos, nrm, faces = sd.positions.reshape(-1, 3), sd.normals.reshape(-1, 3), sd.faces.reshape(-1, 3)
+    assert len(faces) == 2 * 16 * 32 - 2 * 32
+    c = np.array([1, 2, 3], np.float32)
+    assert np.allclose(np.linalg.norm(pos - c, axis=1), 0.5, atol=1e-6) and np.allclose(nrm, (pos - c) / 0.5, atol=1e-5)
+    p0, p1, p2 = pos[faces[:, 0]], pos[faces[:, 1]], pos[faces[:, 2]]
+    ng = np.cross(p1 - p0, p2 - p0)
+    assert (np.einsum("ij,ij->i", ng, (p0 + p1 + p2) / 3 - c) > 0).all()              # outward orientation, no degenerate faces
+    assert 0.5 * np.linalg.norm(ng, axis=1).sum() == pytest.approx(4 * np.pi * 0.25, rel=2e-2)
+    assert sd.film_shape == (6, 8) and sd.lane_grid == (8, 10)
+    film["rfilter"] = {"type": "box"}
+    assert SceneDesc(d).lane_grid == (6, 8)
 
 
 def test_integrator_props_and_registry():
