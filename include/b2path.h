@@ -55,7 +55,8 @@ enum { B2_MF_BECKMANN = 0, B2_MF_GGX = 1 };   /* MicrofacetType (microfacet.h) *
 enum { B2_TEX_F32 = 0, B2_TEX_F16 = 1 };      /* storage (bitmap.cpp:231-246) */
 enum { B2_WRAP_REPEAT = 0, B2_WRAP_MIRROR = 1, B2_WRAP_CLAMP = 2 };
 enum { B2_FILTER_BILINEAR = 0, B2_FILTER_NEAREST = 1 };
-enum { B2_EMITTER_AREA = 0, B2_EMITTER_ENVMAP = 1, B2_EMITTER_CONSTANT = 2 };
+enum { B2_EMITTER_AREA = 0, B2_EMITTER_ENVMAP = 1, B2_EMITTER_CONSTANT = 2,
+       B2_EMITTER_POINT = 3 /* emitters/point.cpp: position = translation of to_world, intensity in `radiance` */ };
 enum { B2_SHAPE_RECTANGLE = 0, B2_SHAPE_MESH = 1 }; /* how an area light is sampled (rectangle.cpp:182-200 | mesh.cpp:758-812) */
 enum { B2_RFILTER_BOX = 0, B2_RFILTER_TENT = 1, B2_RFILTER_GAUSSIAN = 2 };
 enum { B2_MESH_HAS_NORMALS = 1, B2_MESH_HAS_UV = 2, B2_MESH_FLIP_NORMALS = 4 };

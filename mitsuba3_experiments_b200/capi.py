@@ -22,7 +22,7 @@ MF_BECKMANN, MF_GGX = 0, 1
 TEX_F32, TEX_F16 = 0, 1
 WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = 0, 1, 2
 FILTER_BILINEAR, FILTER_NEAREST = 0, 1
-EMITTER_AREA, EMITTER_ENVMAP, EMITTER_CONSTANT = 0, 1, 2
+EMITTER_AREA, EMITTER_ENVMAP, EMITTER_CONSTANT, EMITTER_POINT = 0, 1, 2, 3
 SHAPE_RECTANGLE, SHAPE_MESH = 0, 1
 RFILTER_BOX, RFILTER_TENT, RFILTER_GAUSSIAN = 0, 1, 2
 MESH_HAS_NORMALS, MESH_HAS_UV, MESH_FLIP_NORMALS = 1, 2, 4

@@ -633,6 +633,14 @@ B2_DEV void emitter_sample_direction(const DScene &sc, int em, f3 ref_p, f2 samp
         ds.pdf = active ? pdf * inv_sin_theta * (1.f / (2.f * sqr(kPi))) : 0.f;
         ds.d = dir; ds.dist = dist;
         if (active) spec = env_eval_uv(env, uv) / ds.pdf;
+    } else if (e.type == B2_EMITTER_POINT) {
+        // PointLight::sample_direction (emitters/point.cpp:119-148): delta position, pdf 1, intensity / dist^2
+        cnt.add(C_NEE_AREA);
+        ds.p = f3(e.to_world[3], e.to_world[7], e.to_world[11]); ds.n = f3(0.f); ds.pdf = 1.f; ds.delta = true;
+        ds.d = ds.p - ref_p;
+        const float dist2 = dot(ds.d, ds.d), inv_dist = 1.f / sqrtf(dist2);
+        ds.dist = sqrtf(dist2); ds.d = ds.d * inv_dist;
+        spec = f3(e.radiance[0], e.radiance[1], e.radiance[2]) * sqr(inv_dist);
     } else {
         cnt.add(C_NEE_ENV);
         const DEnvmap &env = sc.env;

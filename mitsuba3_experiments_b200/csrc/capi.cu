@@ -160,7 +160,9 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
         o.type = e.type; o.mesh = e.mesh; o.shape_kind = e.shape_kind; o.cdf_offset = e.cdf_offset; o.inv_area = e.inv_area; o.pad = 0.f;
         for (int k = 0; k < 3; ++k) { o.radiance[k] = e.radiance[k]; o.normal[k] = e.normal[k]; }
         m3x4(e.to_world, o.to_world);
-        if (e.type != B2_EMITTER_AREA) d.env_emitter = (int) i;
+        if (e.type == B2_EMITTER_ENVMAP || e.type == B2_EMITTER_CONSTANT) d.env_emitter = (int) i;
+        else if (e.type == B2_EMITTER_POINT) { o.mesh = -1; }
+        else if (e.type != B2_EMITTER_AREA) return fail(-2, "b2_scene_create: unknown emitter type");
         else if (e.mesh < 0 || (uint32_t) e.mesh >= desc->n_meshes) return fail(-2, "b2_scene_create: area emitter without a mesh");
     }
     DEmitter *em_dev; CUDA_OK(s->upload(ems.data(), ems.size(), em_dev)); d.emitters = em_dev; d.n_emitters = desc->n_emitters;

@@ -9,7 +9,7 @@ Mitsuba plugins, so this module understands the same dictionary schema for the p
   ``mesh`` (explicit arrays) -> world-space vertex/normal/uv/face buffers (Mesh layout, mesh.h:564-568)
 * bsdfs ``diffuse``, ``roughconductor``, ``conductor``, ``dielectric``, ``roughdielectric``, ``roughplastic``, ``twosided`` (single nested BRDF), ``mask`` (constant opacity, outermost), ``ref``
 * textures ``rgb`` / plain lists, ``bitmap`` (filename | data array; fp16 storage rule of bitmap.cpp:231-246)
-* emitters ``area``, ``envmap`` (Hierarchical2D pyramid, distr_2d.h:403-509), ``constant``
+* emitters ``area``, ``envmap`` (Hierarchical2D pyramid, distr_2d.h:403-509), ``constant``, ``point``
 * sensor ``perspective`` (perspective.cpp:173-199, sensor.h:229-265, sensor.cpp:147-200), ``hdrfilm``,
   rfilters ``gaussian`` / ``tent`` / ``box``, sampler ``independent``
 
@@ -554,6 +554,19 @@ class SceneDesc:
         self.meshes.append(mesh); self.mesh_names.append(name)
         self._nv += len(pos); self._nf += len(faces)
 
+    # ------------------------------------------------------------------ point emitters
+    def _add_point(self, name, spec):
+        """emitters/point.cpp:66-85: `position` or the translation of `to_world` (not both), `intensity` (default 1)."""
+        if "position" in spec and "to_world" in spec:
+            raise ValueError("Only one of the parameters 'position' and 'to_world' can be specified at the same time!")
+        pos = np.asarray(spec["position"], np.float64) if "position" in spec else _as_matrix(spec.get("to_world"))[:3, 3]
+        e = capi.Emitter(); e.type = capi.EMITTER_POINT; e.mesh = -1; e.shape_kind = 0; e.inv_area = 0.0; e.cdf_offset = 0
+        e.normal[:] = [0, 0, 0]
+        m = np.eye(4, dtype=np.float32); m[:3, 3] = pos
+        e.to_world[:] = m.reshape(-1).tolist()
+        e.radiance[:] = _rgb(spec.get("intensity"), 1.0).tolist()
+        self.emitters.append(e); self.emitter_names.append(name)
+
     # ------------------------------------------------------------------ environment emitters
     def _add_env(self, name, spec):
         e = capi.Emitter(); e.mesh = -1; e.shape_kind = 0; e.inv_area = 0.0; e.cdf_offset = 0
@@ -639,6 +652,8 @@ class SceneDesc:
             t = v.get("type")
             if t in ("rectangle", "cube", "sphere", "obj", "mesh"):
                 self._add_shape(name, v)
+            elif t == "point":
+                self._add_point(name, v)
             elif t in ("envmap", "constant"):
                 if self.env is not None:
                     raise ValueError("Only one environment emitter can be specified per scene.")

@@ -78,7 +78,7 @@ struct Scene {
         for (uint32_t m = 0; m < d->n_meshes; ++m)
             for (uint32_t f = 0; f < d->meshes[m].n_faces; ++f) face_mesh[d->meshes[m].first_face + f] = (int) m;
         for (uint32_t e = 0; e < d->n_emitters; ++e)
-            if (d->emitters[e].type != B2_EMITTER_AREA) env_emitter = (int) e;
+            if (d->emitters[e].type == B2_EMITTER_ENVMAP || d->emitters[e].type == B2_EMITTER_CONSTANT) env_emitter = (int) e;
         rough.reserve(d->n_bsdfs + 1);
         for (uint32_t i = 0; i < d->n_bsdfs; ++i) if (d->bsdfs[i].type == B2_BSDF_ROUGHPLASTIC) rough_of(d->bsdfs[i]);
         build();
@@ -874,6 +874,14 @@ struct EmitterSys {
             ds.pdf = active ? pdf * inv_sin_theta * (1.f / (2.f * sqr(Pi))) : 0.f;
             ds.d = dir; ds.dist = dist;
             if (active) spec = env_eval_uv(env, uv) / ds.pdf;
+        } else if (e.type == B2_EMITTER_POINT) {
+            // PointLight::sample_direction (emitters/point.cpp:119-148): delta position, pdf 1, intensity / dist^2
+            c.nee_area++;
+            ds.p = V3(e.to_world[3], e.to_world[7], e.to_world[11]); ds.n = V3(0.f); ds.pdf = 1.f; ds.delta = true;
+            ds.d = ds.p - ref.p;
+            float dist2 = dot(ds.d, ds.d), inv_dist = 1.f / sqrtf(dist2);
+            ds.dist = sqrtf(dist2); ds.d = ds.d * inv_dist;
+            spec = V3(e.radiance[0], e.radiance[1], e.radiance[2]) * sqr(inv_dist);
         } else { // constant environment (emitters/constant.cpp): uniform sphere
             c.nee_env++;
             const b2_envmap *env = d().envmap;

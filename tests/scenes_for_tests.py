@@ -152,3 +152,52 @@ def ad_config_scene(name, res=128):
 
 
 AD_CONFIGS = ["crop_window", "diffuse_albedo", "diffuse_albedo_g_i", "area_light_radiance", "directly_visible_area_light_radiance"]
+
+
+def bsdf_sphere_scene(name, fx, light_scale=1.0, spp=64):
+    """bsdf_spheres/test_<name>_path.xml over fragments/single_sphere.xml of the reference's render tests, rebuilt from the
+    fixture `fx` (tests/golden/ref_bsdf_spheres.npz): unit spheres (meshes/sphere.obj -> the tessellated sphere, both within
+    1e-4 of the analytic one), the rotated 4x4 area light, museum.exr and the point light; 48x48 box-filtered film."""
+    def rp(alpha, y, z, nonlinear):
+        return {"type": "sphere", "tessellation": 127, "to_world": T().translate([4, y, z]),
+                "bsdf": {"type": "roughplastic", "distribution": "ggx", "alpha": alpha, "int_ior": "bk7", "ext_ior": "air",
+                         "nonlinear": nonlinear, "diffuse_reflectance": {"type": "rgb", "value": [0.02, 0.2, 0.1]}}}
+    d = {"type": "scene", "integrator": {"type": "path", "max_depth": 2}}
+    if name.startswith("roughplastic"):
+        nl = name.endswith("nonlinear")
+        d.update(s0=rp(0.01, 1.2, 1.2, nl), s1=rp(0.1, -1.2, 1.2, nl), s2=rp(0.4, 1.2, -1.2, nl), s3=rp(1.0, -1.2, -1.2, nl))
+    elif name == "roughdielectric":
+        d["s0"] = {"type": "sphere", "tessellation": 127,
+                   "bsdf": {"type": "roughdielectric", "distribution": "beckmann", "alpha": 0.02, "int_ior": "bk7", "ext_ior": "air"}}
+    else:
+        raise KeyError(name)
+    d["sensor"] = {"type": "perspective", "near_clip": 1, "far_clip": 1000,
+                   "to_world": T().look_at(origin=[-4, 0, 0], target=[0, 0, 0], up=[0, 0, 1]),
+                   "film": {"type": "hdrfilm", "rfilter": {"type": "box"}, "width": 48, "height": 48},
+                   "sampler": {"type": "independent", "sample_count": spp}}
+    # <rotate y=1 angle=120/> <scale 2/> <translate -4 0 6/>: applied in document order
+    to_world = T().translate([-4, 0, 6]) @ T().scale([2, 2, 2]) @ T().rotate([0, 1, 0], 120)
+    d["light"] = {"type": "mesh", "positions": [[-1, -1, 0], [1, -1, 0], [-1, 1, 0], [1, 1, 0]], "faces": [[1, 2, 0], [1, 3, 2]],
+                  "to_world": to_world,
+                  "bsdf": {"type": "diffuse", "reflectance": {"type": "rgb", "value": np.asarray(fx["light_reflectance"]).tolist()}},
+                  "emitter": {"type": "area", "radiance": {"type": "rgb", "value": (np.asarray(fx["light_radiance"]) * light_scale).tolist()}}}
+    d["env"] = {"type": "envmap", "data": np.asarray(fx["envmap"], np.float32)}
+    d["point"] = {"type": "point", "position": [-4, 0, -6], "intensity": {"type": "rgb", "value": [300, 300, 300]}}
+    return d
+
+
+def render_z_test(img_rgb, spp, ref_rgb, ref_var_rgb, significance_level=0.01):
+    """The acceptance test of the reference's render tests (src/render/tests/test_renders.py:158-226): per-value Z-test of the
+    rendered mean against the stored reference mean / variance in XYZ, Sidak-corrected, passes when >= 99.75 % of the pixels
+    accept the null hypothesis.  Returns (passed, fraction of accepted values)."""
+    from math import erf, sqrt
+    m = np.array([[0.412453, 0.357580, 0.180423], [0.212671, 0.715160, 0.072169], [0.019334, 0.119193, 0.950227]], np.float32)
+    img, ref, var = (np.asarray(a, np.float32) @ m.T for a in (img_rgb, ref_rgb, ref_var_rgb))
+    var = np.maximum(var, 1e-4)
+    z = np.abs(img - ref) * np.sqrt(spp / var)
+    cdf = np.vectorize(lambda x: (1.0 - erf(-x / sqrt(2.0))) * 0.5)(z.astype(np.float64))
+    p_value = 2.0 * (1.0 - cdf)
+    pixel_count = img.shape[0] * img.shape[1]
+    alpha = 1.0 - (1.0 - significance_level) ** (1.0 / pixel_count)
+    success = p_value > alpha
+    return (np.count_nonzero(success) / 3) >= 0.9975 * pixel_count, np.count_nonzero(success) / success.size

@@ -504,3 +504,25 @@ def test_reference_prb_goldens_cuda(name):
     prb.render_backward(ds, params, grad_in, seed=0, spp=256)
     grad, grad_ref = float(params.grad[key].sum()) / fref.size, float(fref.mean()) * 0.001
     assert abs(grad - grad_ref) / max(abs(grad_ref), 1e-3) < 0.05, (grad, grad_ref)
+
+
+@pytest.mark.parametrize("name", ["roughplastic_linear", "roughplastic_nonlinear", "roughdielectric"])
+def test_reference_render_z_tests_bsdf_spheres_cuda(name):
+    """The reference's render Z-tests (test_renders.py:158-226, stored mean + variance images of bsdf_spheres/
+    test_<name>_path.xml, 868 spp) through the CUDA path, both launch modes; and CUDA == oracle per pixel on the same scene
+    (rough plastic / rough dielectric + area light + envmap + point light)."""
+    import os
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    from scenes_for_tests import bsdf_sphere_scene, render_z_test
+    fx = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_bsdf_spheres.npz"))
+    ds = DeviceScene(bsdf_sphere_scene(name, fx))
+    for kernel in (0, 1):
+        img, _ = ds.render(seed=0, spp=868, max_depth=2, variant=0, kernel=kernel)
+        ok, frac = render_z_test(img.cpu().numpy(), 868, fx[f"{name}_mean"], fx[f"{name}_var"])
+        assert ok and frac > 0.999, (kernel, frac)
+    kw = dict(seed=2, spp=16, max_depth=4, rr_depth=2, variant=1)
+    img, cnt = ds.render(counters=True, all_shadow_rays=True, **kw)
+    ref, rcnt = OracleScene(ds.desc).render(**kw)
+    check_image(img.cpu().numpy(), ref, 0.99, 2e-3)
+    for k in ("closest_rays", "shadow_rays", "nee_area", "nee_env"):
+        assert abs(cnt[k] - rcnt[k]) <= 1e-3 * max(rcnt[k], 1), (k, cnt[k], rcnt[k])
