@@ -1,6 +1,6 @@
 """Fixtures for the reference's render Z-tests of the rough-plastic / rough-dielectric spheres
 (mitsuba3/resources/data/tests/scenes/bsdf_spheres/test_{roughplastic_linear,roughplastic_nonlinear,roughdielectric}_path.xml
-over fragments/single_sphere.xml; procedure: src/render/tests/test_renders.py:158-226).
+over fragments/single_sphere.xml, and scenes/infinite_mirrors/scene_path.xml; procedure: src/render/tests/test_renders.py:158-226).
 
 Written to tests/golden/ref_bsdf_spheres.npz:
 * `<scene>_mean`, `<scene>_var`: the stored reference image and its per-sample variance (refs/*_ref_rgb{,_var}.exr);
@@ -75,5 +75,9 @@ if __name__ == "__main__":
         out[f"{s}_mean"] = exr_min.read_rgb(f"{refs}/test_{s}_ref_rgb.exr")
         out[f"{s}_var"] = exr_min.read_rgb(f"{refs}/test_{s}_ref_rgb_var.exr")
         print(s, out[f"{s}_mean"].shape, float(out[f"{s}_mean"].mean()), float(out[f"{s}_var"].mean()))
+    # scenes/infinite_mirrors/scene_path.xml: three touching conductor spheres under the same envmap, max_depth 8, 32x32
+    mirrors = f"{MI}/resources/data/tests/scenes/infinite_mirrors/refs"
+    out["infinite_mirrors_mean"] = exr_min.read_rgb(f"{mirrors}/scene_ref_rgb.exr")
+    out["infinite_mirrors_var"] = exr_min.read_rgb(f"{mirrors}/scene_ref_rgb_var.exr")
     np.savez_compressed(OUT, **out)
     print("wrote", OUT, os.path.getsize(OUT), "bytes")

@@ -162,6 +162,15 @@ def bsdf_sphere_scene(name, fx, light_scale=1.0, spp=64):
         return {"type": "sphere", "tessellation": 127, "to_world": T().translate([4, y, z]),
                 "bsdf": {"type": "roughplastic", "distribution": "ggx", "alpha": alpha, "int_ior": "bk7", "ext_ior": "air",
                          "nonlinear": nonlinear, "diffuse_reflectance": {"type": "rgb", "value": [0.02, 0.2, 0.1]}}}
+    if name == "infinite_mirrors":       # scenes/infinite_mirrors/scene_path.xml: 8 bounces between three conductor spheres
+        def mirror(y, z):
+            return {"type": "sphere", "tessellation": 127, "to_world": T().translate([0, y, z]), "bsdf": {"type": "conductor", "eta": 0.789, "k": 6.15}}
+        return {"type": "scene", "integrator": {"type": "path", "max_depth": 8}, "s0": mirror(-1.05, -0.9), "s1": mirror(1.05, -0.9), "s2": mirror(0.0, 0.9),
+                "env": {"type": "envmap", "data": np.asarray(fx["envmap"], np.float32)},
+                "sensor": {"type": "perspective", "near_clip": 1, "far_clip": 1000,
+                           "to_world": T().look_at(origin=[-5, 0, 0], target=[0, 0, 0], up=[0, 0, 1]),
+                           "film": {"type": "hdrfilm", "rfilter": {"type": "box"}, "width": 32, "height": 32},
+                           "sampler": {"type": "independent", "sample_count": spp}}}
     d = {"type": "scene", "integrator": {"type": "path", "max_depth": 2}}
     if name.startswith("roughplastic"):
         nl = name.endswith("nonlinear")

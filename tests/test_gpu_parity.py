@@ -506,7 +506,7 @@ def test_reference_prb_goldens_cuda(name):
     assert abs(grad - grad_ref) / max(abs(grad_ref), 1e-3) < 0.05, (grad, grad_ref)
 
 
-@pytest.mark.parametrize("name", ["roughplastic_linear", "roughplastic_nonlinear", "roughdielectric"])
+@pytest.mark.parametrize("name", ["roughplastic_linear", "roughplastic_nonlinear", "roughdielectric", "infinite_mirrors"])
 def test_reference_render_z_tests_bsdf_spheres_cuda(name):
     """The reference's render Z-tests (test_renders.py:158-226, stored mean + variance images of bsdf_spheres/
     test_<name>_path.xml, 868 spp) through the CUDA path, both launch modes; and CUDA == oracle per pixel on the same scene
@@ -515,10 +515,12 @@ def test_reference_render_z_tests_bsdf_spheres_cuda(name):
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
     from scenes_for_tests import bsdf_sphere_scene, render_z_test
     fx = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_bsdf_spheres.npz"))
-    ds = DeviceScene(bsdf_sphere_scene(name, fx))
+    d = bsdf_sphere_scene(name, fx)
+    ds = DeviceScene(d)
+    ref = fx[f"{name}_mean"]; spp = int(2e6) // (ref.shape[0] * ref.shape[1])
     for kernel in (0, 1):
-        img, _ = ds.render(seed=0, spp=868, max_depth=2, variant=0, kernel=kernel)
-        ok, frac = render_z_test(img.cpu().numpy(), 868, fx[f"{name}_mean"], fx[f"{name}_var"])
+        img, _ = ds.render(seed=0, spp=spp, max_depth=d["integrator"]["max_depth"], variant=0, kernel=kernel)
+        ok, frac = render_z_test(img.cpu().numpy(), spp, ref, fx[f"{name}_var"])
         assert ok and frac > 0.999, (kernel, frac)
     kw = dict(seed=2, spp=16, max_depth=4, rr_depth=2, variant=1)
     img, cnt = ds.render(counters=True, all_shadow_rays=True, **kw)
