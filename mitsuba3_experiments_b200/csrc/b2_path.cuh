@@ -312,7 +312,7 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
             // supported BSDF is linear in its reflectance, so the derivative is the value with reflectance := 1.
             // forward mode (render_forward, common.py:495-621): the same coefficient with dL := 1, contracted with the
             // parameter tangent at this vertex and accumulated in s.dL (the lane's d L, splatted after the replay)
-            const f3 dLw = p.forward ? f3(1.f) : s.dL;
+            const f3 dLw = B2_FWD(p) ? f3(1.f) : s.dL;
             f3 g(0.f);
             if (active_em) {
                 f3 unit; float dummy; bsdf_eval_pdf<CLS>(bsdf, si.wi, wo, ones, unit, dummy);
@@ -330,7 +330,7 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
                     if (p.targets[t].bsdf != si.bsdf) continue;
                     float *gp = p.targets[t].grad;
                     if (p.targets[t].kind == 0) {
-                        if (p.forward) s.dL += g * f3(__ldg(gp), __ldg(gp + 1), __ldg(gp + 2));
+                        if (B2_FWD(p)) s.dL += g * f3(__ldg(gp), __ldg(gp + 1), __ldg(gp + 2));
                         else {
                             atomicAdd(gs.s_const + 3 * t, g.x); atomicAdd(gs.s_const + 3 * t + 1, g.y); atomicAdd(gs.s_const + 3 * t + 2, g.z);
                             cnt.add(C_GRAD, 3);
@@ -338,7 +338,7 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
                     } else {
                         uint32_t idx[4]; float w[4]; Counters<false> none;
                         tex_eval(sc, bsdf.tex, si.uv, idx, w, none);
-                        if (p.forward) {
+                        if (B2_FWD(p)) {
                             f3 tan(0.f);
 #pragma unroll
                             for (int q = 0; q < 4; ++q) tan += f3(__ldg(gp + 3 * (size_t) idx[q]), __ldg(gp + 3 * (size_t) idx[q] + 1), __ldg(gp + 3 * (size_t) idx[q] + 2)) * w[q];

@@ -2,6 +2,13 @@
 #pragma once
 #include "b2_scene.cuh"
 
+// experiment switch: -DB2_NO_FORWARD compiles the forward-mode (render_forward) branches out of the adjoint kernels
+#ifdef B2_NO_FORWARD
+#define B2_FWD(p) false
+#else
+#define B2_FWD(p) ((p).forward != 0)
+#endif
+
 namespace b2 {
 
 constexpr int kMaxGradTargets = 8;

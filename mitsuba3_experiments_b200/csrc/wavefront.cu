@@ -324,7 +324,7 @@ __global__ void __launch_bounds__(256, (CLS == CLS_DIFFUSE || CLS == CLS_MISS) ?
             }
             alive = path_step<V, ADJ, COUNT, true, CLS>(p, s, gs, cnt, &h, &so);
             if (ADJ && !alive) cnt.add(C_SAMPLES);
-            if (ADJ && p.forward) st.dl[slot] = make_float4(s.dL.x, s.dL.y, s.dL.z, 0.f);
+            if (ADJ && B2_FWD(p)) st.dl[slot] = make_float4(s.dL.x, s.dL.y, s.dL.z, 0.f);
             wf_store_path(st, slot, s, alive);
             shadow = so.valid;
             if (shadow) {
@@ -376,7 +376,7 @@ __global__ void __launch_bounds__(256) k_wf_generate_adj(const __grid_constant__
         start_path<B2_VARIANT_PRB>(p, s);
         s.L = f3(l.x, l.y, l.z);
         f3 dL(0.f);
-        if (!p.forward) film_taps(p, s.pos, [&](int x, int y, float wgt) {
+        if (!B2_FWD(p)) film_taps(p, s.pos, [&](int x, int y, float wgt) {
             const size_t pix = (size_t) y * sn.crop_width + x;
             float W = __ldg(p.wfilm + 4 * pix + 3); W = W == 0.f ? 1.f : W;
             const float k = wgt / W;
@@ -609,7 +609,7 @@ static long wf_render_backward_t(RenderParams p, WfState &st, int sm_count, cuda
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<V, COUNT, false>, 256, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_adj, k_wf_shade<V, COUNT, true>, 256, 0);
     int occ_splat = 1; const size_t smem_splat = sizeof(float4) * (size_t) p.tile_cols * p.tile_rows;
-    if (p.forward) {
+    if (B2_FWD(p)) {
         cudaFuncSetAttribute(k_wf_splat<V, COUNT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem_splat);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_splat, k_wf_splat<V, COUNT, false>, 256, smem_splat);
         if (occ_splat <= 0) { *err = "wavefront: the splat kernel cannot be resident"; return -1; }
@@ -647,7 +647,7 @@ static long wf_render_backward_t(RenderParams p, WfState &st, int sm_count, cuda
             tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, true><<<g_adj, 256, 0, stream>>>(p, w); tm_end(stream); launches++;
             ++it;
         }
-        if (p.forward) {
+        if (B2_FWD(p)) {
             // forward mode: splat the lanes' d L (accumulated in the dL stream) like a render splats L (common.py:585-600)
             const DSensor &sn = p.sc.sensor; const uint32_t W = (uint32_t) sn.grid_w, P = p.unit_pixels;
             tm_begin(WF_K_OTHER, stream); k_wf_dl_to_rad<<<g_gen, 256, 0, stream>>>(w); tm_end(stream); launches++;

@@ -3,7 +3,8 @@
 Follows the reference's parser where the hot-path scenes exercise it (mitsuba3/src/core/xml.cpp): ``<default name value>``
 with ``$name`` substitution in every attribute (xml.cpp: parameter substitution happens before interpretation), plugin
 elements (``scene integrator sensor sampler film rfilter bsdf texture shape emitter``) with ``type`` / ``id`` / ``name``,
-property elements (``float integer boolean string rgb spectrum point vector``), ``<ref id name>``, and ``<transform>`` with
+property elements (``float integer boolean string rgb spectrum point vector``), ``<ref id name>``, ``<include filename>``,
+``<path value>`` search directories, and ``<transform>`` with
 ``matrix translate rotate scale lookat`` composed left to right as ``T = op_n ... op_2 op_1`` (each new operation is applied
 after the previous ones, xml.cpp transform handling).  The result has the schema of ``mi.load_dict`` / ``mi.cornell_box()``
 (util.py:568-703) and goes straight into ``SceneDesc`` / ``load_dict``.
@@ -107,6 +108,9 @@ class _Parser:
         if t == "spectrum":
             if "filename" in a:
                 raise XMLError("<spectrum filename=...> is not supported")
+            if ":" in a["value"]:
+                raise XMLError("<spectrum value=\"wavelength:value, ...\">: wavelength lists need the CIE observer tables "
+                               "(spectrum_list_to_srgb); give the colour as <rgb> instead")
             v = _floats(a["value"])
             if len(v) != 1:
                 raise XMLError("<spectrum>: only uniform values are supported in the rgb variants")
@@ -139,8 +143,10 @@ class _Parser:
         d = {"type": a.get("type", "scene")}
         for ch in el:
             if ch.tag in ("default", "alias", "include", "path"):
-                if ch.tag in ("include", "alias"):
-                    raise XMLError(f"<{ch.tag}> is not supported")
+                if ch.tag == "include":
+                    raise XMLError("<include> needs a base directory: use load_file, or load_string(..., base_dir=...)")
+                if ch.tag == "alias":
+                    raise XMLError("<alias> is not supported")
                 continue
             key = self.child_key(ch, el.tag, d)
             if key in d:
@@ -154,13 +160,56 @@ class _Parser:
         return d
 
 
-def load_string(text: str, **overrides) -> dict:
+def _expand_includes(root, base_dir, subst, depth=0):
+    """<include filename="..."/> (xml.cpp: the included file's <scene> children are spliced in place; nested includes
+    resolve against the included file's own directory)."""
+    if depth > 16:
+        raise XMLError("<include>: nesting too deep (cycle?)")
+    out = []
+    for ch in list(root):
+        if ch.tag != "include":
+            out.append(ch); continue
+        if base_dir is None:
+            raise XMLError("<include> needs a base directory: use load_file, or load_string(..., base_dir=...)")
+        fname = subst(ch.attrib["filename"])
+        path = fname if os.path.isabs(fname) else os.path.join(base_dir, fname)
+        if not os.path.exists(path):
+            raise XMLError(f"<include>: file {path!r} not found")
+        inc = ET.parse(path).getroot()
+        if inc.tag != "scene":
+            raise XMLError(f"<include>: root element of {path!r} must be <scene>")
+        _expand_includes(inc, os.path.dirname(path), subst, depth + 1)
+        out.extend(list(inc))
+    root[:] = out
+
+
+def _resolve_filenames(d, base_dir, search):
+    """<path value="..."/> search directories (xml.cpp / FileResolver): a relative ``filename`` that does not exist next to
+    the scene file but does under a search path becomes absolute."""
+    for k, v in d.items():
+        if isinstance(v, dict):
+            _resolve_filenames(v, base_dir, search)
+        elif k == "filename" and isinstance(v, str) and not os.path.isabs(v) and not os.path.exists(os.path.join(base_dir, v)):
+            for sp in search:
+                if os.path.exists(os.path.join(sp, v)):
+                    d[k] = os.path.abspath(os.path.join(sp, v)); break
+
+
+def load_string(text: str, base_dir: str | None = None, **overrides) -> dict:
     """Parses scene XML into a scene dictionary; keyword arguments override ``<default>`` parameters (as ``mi.load_file`` does)."""
     root = ET.fromstring(text)
     if root.tag != "scene":
         raise XMLError("root element must be <scene>")
-    d = _Parser(root, overrides).plugin(root)
+    # includes may use $parameters declared before them; fragments may declare further defaults
+    pre = _Parser(root, {})
+    pre.defaults.update({k: str(v) for k, v in overrides.items()})
+    _expand_includes(root, base_dir, pre.subst)
+    parser = _Parser(root, overrides)
+    d = parser.plugin(root)
     d["type"] = "scene"
+    if base_dir is not None:
+        search = [parser.subst(el.attrib["value"]) for el in root.iter("path")]
+        _resolve_filenames(d, base_dir, [p if os.path.isabs(p) else os.path.join(base_dir, p) for p in search])
     return d
 
 
@@ -168,4 +217,4 @@ def load_file(path: str, **overrides) -> dict:
     """``mi.load_file(path, **params)`` for the supported subset; relative filenames stay relative to ``dirname(path)``
     (pass it as ``base_path`` to ``SceneDesc`` / ``load_dict``)."""
     with open(path, "r", encoding="utf-8") as f:
-        return load_string(f.read(), **overrides)
+        return load_string(f.read(), base_dir=os.path.dirname(os.path.abspath(path)), **overrides)

@@ -267,3 +267,55 @@ def test_xml_scene_renders_like_its_dictionary(tmp_path):
     d2["Lamp"] = dict(d["Lamp"]); d2["Lamp"]["bsdf"] = dict(d["LampGlassBSDF"])          # inline instead of <ref>
     img2, _ = OracleScene(SceneDesc(d2, base_path=str(tmp_path))).render(seed=0, spp=8, max_depth=5, rr_depth=3, variant=1)
     assert np.array_equal(img, img2)
+
+
+def test_xml_include_search_path_and_moment(tmp_path):
+    """xml.cpp subset, continued: <include> splices a fragment (its <default>s included), <path> adds a search directory for
+    relative filenames, the render tests' `moment` wrapper resolves to the nested integrator, wavelength-list spectra raise."""
+    from mitsuba3_experiments_b200.scene import SceneDesc
+    from mitsuba3_experiments_b200.xml_loader import XMLError, load_file, load_string
+    (tmp_path / "common" / "meshes").mkdir(parents=True)
+    (tmp_path / "common" / "meshes" / "quad.obj").write_text("v -1 -1 0\nv 1 -1 0\nv -1 1 0\nv 1 1 0\nf 2 3 1\nf 2 4 3\n")
+    (tmp_path / "scenes" / "fragments").mkdir(parents=True)
+    (tmp_path / "scenes" / "fragments" / "camera.xml").write_text("""<scene version='2.0.0'>
+        <default name="spp" value="16"/>
+        <integrator type="moment"><integrator type="path"><integer name="max_depth" value="3"/></integrator></integrator>
+        <sensor type="perspective"><float name="fov" value="40"/>
+            <transform name="to_world"><lookat origin="0, 0, 4" target="0, 0, 0" up="0, 1, 0"/></transform>
+            <film type="hdrfilm"><integer name="width" value="8"/><integer name="height" value="8"/></film>
+            <sampler type="independent"><integer name="sample_count" value="$spp"/></sampler></sensor>
+        </scene>""")
+    main = tmp_path / "scenes" / "main.xml"
+    main.write_text("""<scene version='2.0.0'><path value="../common"/>
+        <shape type="obj"><string name="filename" value="meshes/quad.obj"/><bsdf type="diffuse"/></shape>
+        <emitter type="constant"/>
+        <include filename="fragments/camera.xml"/></scene>""")
+    d = load_file(str(main), spp=4)
+    shape = next(v for v in d.values() if isinstance(v, dict) and v.get("type") == "obj")
+    assert os.path.isabs(shape["filename"]) and shape["filename"].endswith(os.path.join("common", "meshes", "quad.obj"))
+    sd = SceneDesc(d, base_path=str(tmp_path / "scenes"))
+    assert sd.integrator_props == {"max_depth": 3, "type": "path"} and sd.spp == 4 and len(sd.faces) == 2
+    with pytest.raises(XMLError):
+        load_string("<scene version='2.0.0'><include filename='x.xml'/></scene>")
+    with pytest.raises(XMLError):
+        load_string("<scene version='2.0.0'><bsdf type='diffuse'><spectrum name='reflectance' value='400:0.5, 700:0.5'/></bsdf></scene>")
+
+
+REF_SCENES = "/root/reference/mitsuba3/resources/data/tests/scenes"
+
+
+@pytest.mark.skipif(not os.path.exists(REF_SCENES), reason="the reference tree is only present in the build container")
+def test_reference_scene_file_passes_its_own_render_test():
+    """End to end in the build container: the reference's infinite_mirrors/scene_path.xml through load_file (its <path>,
+    the `moment` wrapper, meshes/sphere.obj, textures/museum.exr) and the oracle passes the reference's own Z-test."""
+    from mitsuba3_experiments_b200.scene import SceneDesc
+    from mitsuba3_experiments_b200.xml_loader import load_file
+    from oracle.oracle_py import OracleScene
+    from scenes_for_tests import render_z_test
+    path = os.path.join(REF_SCENES, "infinite_mirrors", "scene_path.xml")
+    sd = SceneDesc(load_file(path, spp=8), base_path=os.path.dirname(path))
+    assert len(sd.faces) == 3 * 32512 and sd.integrator_props["max_depth"] == 8
+    fx = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_bsdf_spheres.npz"))
+    img, _ = OracleScene(sd).render(seed=0, spp=1953, max_depth=8, variant=0)
+    ok, frac = render_z_test(img, 1953, fx["infinite_mirrors_mean"], fx["infinite_mirrors_var"])
+    assert ok and frac > 0.999
