@@ -111,8 +111,9 @@ def cpu_oracle_rate(scene_dict, kw, label_spp=1, threads=None):
     from oracle.oracle_py import OracleScene, lib
     desc = SceneDesc(scene_dict)
     orc = OracleScene(desc)
-    if threads:
-        lib().orc_set_num_threads(threads)
+    # all host threads this process may run on: torchrun exports OMP_NUM_THREADS=1 to every rank, which would otherwise
+    # silently turn the "all host threads" baseline into a single-thread one at N > 1
+    lib().orc_set_num_threads(threads or len(os.sched_getaffinity(0)))
     t0 = time.perf_counter()
     _, cnt = orc.render_film(seed=0, spp=label_spp, **kw)
     dt = time.perf_counter() - t0
@@ -128,6 +129,7 @@ def run_reference(args, rank):
     from mitsuba3_experiments_b200.scene import SceneDesc
     from oracle.oracle_py import OracleScene, lib
     orc = OracleScene(SceneDesc(d))
+    lib().orc_set_num_threads(len(os.sched_getaffinity(0)))     # torchrun sets OMP_NUM_THREADS=1 per rank; use every host thread
     sample_spp = 2
     times, n = [], 0
     for i in range(args.warmup + args.steps):
