@@ -319,3 +319,26 @@ def test_reference_scene_file_passes_its_own_render_test():
     img, _ = OracleScene(sd).render(seed=0, spp=1953, max_depth=8, variant=0)
     ok, frac = render_z_test(img, 1953, fx["infinite_mirrors_mean"], fx["infinite_mirrors_var"])
     assert ok and frac > 0.999
+
+
+def test_minimal_exr_reader_matches_openexr(tmp_path):
+    """tests/golden/exr_min.py (the reader that extracted the reference's stored images) against OpenCV's bundled OpenEXR:
+    PIZ, ZIP and uncompressed files, float32 and half, sizes that are not multiples of the 32-line PIZ chunk or of 2."""
+    os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
+    cv2 = pytest.importorskip("cv2")
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import exr_min
+    rng = np.random.RandomState(0)
+    yy, xx = np.mgrid[0:71, 0:53]
+    smooth = np.stack([np.sin(xx * 0.11) * np.cos(yy * 0.07), (xx + yy) / 120.0, np.exp(-((xx - 20) ** 2 + (yy - 30) ** 2) / 300.0)], -1)
+    img = (smooth + 0.01 * rng.standard_normal(smooth.shape)).astype(np.float32)
+    img[5:9, 7:30] = 0.0                                           # runs of equal values exercise the Huffman run-length symbol
+    cases = [(cv2.IMWRITE_EXR_COMPRESSION_PIZ, cv2.IMWRITE_EXR_TYPE_FLOAT), (cv2.IMWRITE_EXR_COMPRESSION_PIZ, cv2.IMWRITE_EXR_TYPE_HALF),
+             (cv2.IMWRITE_EXR_COMPRESSION_ZIP, cv2.IMWRITE_EXR_TYPE_FLOAT), (cv2.IMWRITE_EXR_COMPRESSION_NO, cv2.IMWRITE_EXR_TYPE_FLOAT)]
+    for i, (comp, typ) in enumerate(cases):
+        path = str(tmp_path / f"t{i}.exr")
+        if not cv2.imwrite(path, img[:, :, ::-1], [cv2.IMWRITE_EXR_COMPRESSION, comp, cv2.IMWRITE_EXR_TYPE, typ]):
+            pytest.skip("this OpenCV build cannot write EXR")
+        want = cv2.imread(path, cv2.IMREAD_UNCHANGED)[:, :, ::-1]
+        got = exr_min.read_rgb(path)
+        assert got.shape == want.shape and np.array_equal(got, want), (comp, typ)
