@@ -12,7 +12,7 @@
 //   w2: qlo_x[8] | qlo_y[8]     w3: qlo_z[8] | qhi_x[8]     w4: qhi_y[8] | qhi_z[8]
 // meta: 0 = empty; internal child = 0x20 | (24 + slot); leaf = (unary tri count) << 5 | offset from tri_base.
 // Child slots were assigned at build time so that slot ^ ray-octant orders the children front to back.
-// Triangle record = 3 x float4: (p0, face index) (e1 = p1 - p0, mesh index) (e2 = p2 - p0, 0).
+// Triangle record = 3 x float4: (p0, face index) (e1 = p1 - p0, mesh index | shading class << 28) (e2 = p2 - p0, 0).
 #pragma once
 #include "b2_scene.cuh"
 
@@ -20,7 +20,6 @@ namespace b2 {
 
 struct Hit { float t, u, v; uint32_t face, mesh; B2_DEV bool valid() const { return face != 0xffffffffu; } };
 
-constexpr int kStackSize = 48;
 
 B2_DEV uint32_t byte_of(uint32_t lo, uint32_t hi, int s) { return ((s < 4 ? lo : hi) >> ((s & 3) * 8)) & 0xffu; }
 
@@ -141,7 +140,7 @@ B2_DEV bool bvh_trace(const DScene &sc, f3 o, f3 d, float tmax, Hit &hit, Counte
                 if (ANY) { hit.t = t; hit.face = __float_as_uint(r0.w); return true; }
                 const uint32_t face = __float_as_uint(r0.w);
                 if (!found || t < hit.t || (t == hit.t && face < hit.face)) {
-                    found = true; hit.t = t; hit.u = u; hit.v = v; hit.face = face; hit.mesh = __float_as_uint(r1.w);
+                    found = true; hit.t = t; hit.u = u; hit.v = v; hit.face = face; hit.mesh = __float_as_uint(r1.w) & 0x0fffffffu;
                 }
             }
         }

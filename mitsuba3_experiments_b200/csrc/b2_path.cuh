@@ -148,14 +148,21 @@ B2_DEV uint32_t film_taps_group(const RenderParams &p, f2 pos, f3 L, bool valid,
     return valid ? nx * ny : 0u;
 }
 
-template <int V>
-B2_DEV void start_path(const RenderParams &p, Path &s) {
+// jitter + sensor ray of a lane (SamplingIntegrator::render_sample, integrator.cpp:419-436): consumes the first two draws of
+// the lane's stream.  Shared by the trace kernel of bounce 0 and the first shade launch, which must derive the identical ray.
+B2_DEV Ray primary_ray(const RenderParams &p, uint32_t lane, Pcg32 &rng, f2 &pos) {
     const DSensor &sn = p.sc.sensor;
     int px, py;
-    const f2 sample_pos = lane_sample_pos(p, s.lane, s.rng, px, py);
+    const f2 sample_pos = lane_sample_pos(p, lane, rng, px, py);
     const f2 adjusted{ fma_(sample_pos.x, sn.scale_x, sn.offset_x), fma_(sample_pos.y, sn.scale_y, sn.offset_y) };
-    s.ray = camera_ray(sn, adjusted);
-    s.pos = sn.rfilter == B2_RFILTER_BOX ? f2{ (float) px, (float) py } : sample_pos;
+    pos = sn.rfilter == B2_RFILTER_BOX ? f2{ (float) px, (float) py } : sample_pos;
+    return camera_ray(sn, adjusted);
+}
+B2_DEV Ray primary_ray(const RenderParams &p, uint32_t lane, Pcg32 &rng) { f2 pos; return primary_ray(p, lane, rng, pos); }
+
+template <int V>
+B2_DEV void start_path(const RenderParams &p, Path &s) {
+    s.ray = primary_ray(p, s.lane, s.rng, s.pos);
     s.f = f3(1.f); s.L = f3(0.f); s.eta = 1.f;
     s.depth = (V == B2_VARIANT_PATH) ? 1u : 0u;
     s.prev_p = f3(0.f); s.prev_pdf = 1.f; s.prev_delta = true; s.first = true;
@@ -198,8 +205,10 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
     bool active_next;
     if (V == B2_VARIANT_PATH) {
         if (s.first) {
-            s.L += emitter_eval(sc, si.emitter, si, cnt);                                   // path.py:238-239
             active_next = s.depth < max_depth;
+            // path.py:235-239: `si.emitter(scene, active).eval(si, active)` with active = depth < max_depth -- with
+            // max_depth <= 1 neither the first intersection nor the primary emission is evaluated (L = 0)
+            if (active_next) s.L += emitter_eval(sc, si.emitter, si, cnt);
             if (active_next && !si.valid) { s.rng.skip(6); return false; }                  // body runs once with a null BSDF
         } else {
             DS ds2; direction_sample(si, s.prev_p, ds2);
@@ -225,8 +234,16 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
         }
         active_next = (s.depth + 1 < max_depth) && si.valid;
         if (!active_next) {
-            if (V == B2_VARIANT_PATH_MIS) { if (si.valid) s.valid_ray = true; }
-            else s.L = ADJ ? (s.L - Le) : (s.L + Le);
+            if (V == B2_VARIANT_PATH_MIS) {
+                // path-mis.py:129-133 also runs on the terminating iteration: the BSDF is still sampled and
+                // valid_ray |= si.is_valid() & ~Null(sampled_type).  Only an opacity mask can sample a null lobe
+                // (mask.cpp:123-160: sample1 >= opacity), so only there the third draw of the iteration is looked at.
+                if (si.valid) {
+                    const DBsdf &bl = sc.bsdfs[si.bsdf];
+                    if (bl.flags & B2_BSDF_FLAG_MASK) { s.rng.skip(2); const float s1 = s.rng.next_1d(); if (s1 < bl.opacity) s.valid_ray = true; s.rng.skip(3); return false; }
+                    s.valid_ray = true;
+                }
+            } else s.L = ADJ ? (s.L - Le) : (s.L + Le);
             s.rng.skip(6);
             return false;
         }

@@ -12,6 +12,10 @@
 
 namespace b2 {
 
+// Capacity of every traversal stack (b2_bvh.cuh, wf_trace.cu): one node group per level of the wide tree.  b2_scene_build_accel
+// refuses trees deeper than this, so a push can never be dropped.
+constexpr int kStackSize = 48;
+
 struct alignas(16) DBsdf {          // 64 B
     int32_t type, flags, tex, distribution;
     float refl[3]; int32_t sample_visible;

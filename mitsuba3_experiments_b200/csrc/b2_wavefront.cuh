@@ -3,8 +3,15 @@
 // The reference records `sample()` once and lets Dr.Jit compile one megakernel over a wavefront of W*H*spp lanes
 // (src/render/integrator.cpp:246-360); lanes that finish early idle inside dr.while_loop.  Here the wavefront is
 // explicit: per bounce one TRACE launch (closest rays of the live lanes and the shadow rays of the previous bounce,
-// persistent warps with dynamic ray fetch) and one SHADE launch (path_step<WF>), with the live lanes compacted into the
-// next queue by warp ballot + prefix sums.  Lane state lives in HBM as streams of 32-byte elements between launches.
+// persistent warps with a prefetched ray pipeline, wf_trace.cu) and one SHADE launch (path_step<WF>), with the live lanes
+// compacted into the next queue by warp ballot + prefix sums.  Lane state lives in HBM as streams of 32-byte elements
+// between launches; every element is moved by ONE 256-bit load / store (LDG.E.256 / STG.E.256, sm_100).
+//
+// There is no generate kernel: the trace launch of bounce 0 derives the camera ray from the lane index (sampler seed,
+// jitter, sensor), and the first shade launch re-derives the same ray and seeds the lane state.
+// Deferred next-event estimation: shade(k) writes the shadow ray and the two factors of the contribution (L <- fma(a, b, L)),
+// trace(k + 1) only flags the rays that arrive, and the addition happens where the lane's radiance is loaded next
+// (shade(k + 1), or the splat for lanes that ended) -- the trace kernel's epilogue is stores only.
 #pragma once
 #include "b2_render.cuh"
 #include "b2_math.cuh"
@@ -12,71 +19,48 @@
 
 namespace b2 {
 
-struct WfCtl {                       // device-side queue bookkeeping, slot = iteration & 3
+struct WfCtl {                       // device-side queue bookkeeping, slot = iteration & 3; zeroed at the start of a pass
     uint32_t n_closest[4];           // live lanes entering iteration it (queue q[it & 1])
     uint32_t n_shadow[4];            // shadow rays emitted by shade(it)
     uint32_t fetch[4];               // persistent-warp work counter of trace(it)
     uint32_t n_class[4][8];          // hits of iteration it per shading class (queues qc[cls])
 };
 
-// Lane-state accessor.  Experiment (B2_STATE_CS=1): every stream element is read once and written once per bounce and a chunk's
-// state (GBs) is far larger than L2, so the accesses could carry the evict-first hint (ld.global.cs / st.global.cs) and leave L2
-// to the data that is reused (nodes, triangles, per-face records, textures).  Measured on the bedroom stand-in: trace 44.4 ->
-// 43.6 ms but shade 24.0 -> 25.8 ms (what a shade kernel writes is what classify / trace read next, and evict-first loses the
-// part of it that still sat in L2), net 789 -> 775 Msamples/s: off.  The L2 node pin of capi.cu gets the trace gain alone.
-#ifndef B2_STATE_CS
-#define B2_STATE_CS 0
-#endif
-template <class T> struct StateRef {
-    T *p;
-#if B2_STATE_CS
-    B2_DEV operator T() const { return __ldcs(p); }
-    B2_DEV const StateRef &operator=(const T &v) const { __stcs(p, v); return *this; }
-#else
-    B2_DEV operator T() const { return *p; }
-    B2_DEV const StateRef &operator=(const T &v) const { *p = v; return *this; }
-#endif
-    B2_DEV const StateRef &operator=(const StateRef &o) const { return *this = (T) o; }
-    B2_DEV T *ptr() const { return p; }
-};
+// One 32-byte state element = one DRAM / L2 sector, moved by a single 256-bit access.
+struct alignas(32) Elem { float4 a, b; };
+B2_DEV Elem ld256(const Elem *p) {
+    Elem e;
+    asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(e.a.x), "=f"(e.a.y), "=f"(e.a.z), "=f"(e.a.w), "=f"(e.b.x), "=f"(e.b.y), "=f"(e.b.z), "=f"(e.b.w) : "l"(p));
+    return e;
+}
+B2_DEV void st256(Elem *p, const Elem &e) {
+    asm volatile("st.global.v8.f32 [%8], {%0,%1,%2,%3,%4,%5,%6,%7};"
+                 :: "f"(e.a.x), "f"(e.a.y), "f"(e.a.z), "f"(e.a.w), "f"(e.b.x), "f"(e.b.y), "f"(e.b.z), "f"(e.b.w), "l"(p) : "memory");
+}
 
 struct WfState {                     // `capacity` lane slots (slot = lane - chunk_begin)
-    // Lane state = four streams of 32-byte elements (two 16-byte words each, grouped by which kernel touches them
-    // together).  A 32-byte element is exactly one DRAM/L2 sector, so a lane costs whole sectors however sparse or
-    // permuted the live lanes are (16-byte SoA streams moved 3x the useful bytes in late, class-sorted bounces), while
-    // dense warps still touch only 8 cache lines per request (a 128-byte record per lane touched 32: measured +30 % on
-    // the coherent Cornell / PRB workloads).
-    float4 *p0;                      // ray o.xyz | maxt          , ray d.xyz | eta                     (trace reads)
-    float4 *p1;                      // hit t, u, v | face        , hit mesh, vis bits, splat pos xy    (trace writes)
-    float4 *p2;                      // PCG32 state, inc          , throughput f.xyz | prev_bsdf_pdf
-    float4 *p3;                      // L.xyz | depth + flags     , prev_p.xyz | -
-    float4 *s0;                      // deferred NEE: shadow ray o | maxt , d | tex flag                (trace reads)
-    float4 *s1;                      //               factor a            , factor b   (L <- fma(a, b, L) on arrival)
+    // A 32-byte element is exactly one sector, so a lane costs whole sectors however sparse or permuted the live lanes are
+    // (16-byte SoA streams moved 3x the useful bytes in late, class-sorted bounces), while dense warps still touch only 8
+    // cache lines per request.
+    Elem *ray;                       // o.xyz | maxt          , d.xyz | eta                        shade -> trace, shade
+    Elem *hit;                       // t, u, v | face        , mesh, class, -, -                  trace -> shade
+    Elem *rng;                       // PCG32 state, inc      , throughput f.xyz | prev_bsdf_pdf   shade -> shade
+    Elem *rad;                       // L.xyz | depth + flags , prev_p.xyz | visibility bits (PRB) shade -> shade, splat
+    Elem *shr;                       // deferred NEE: shadow ray o | maxt , d | tex flag           shade -> trace
+    Elem *shf;                       //   factor a | arrived (set by trace), factor b | bounce     shade -> shade / splat
     float4 *dl;                      // PRB adjoint: dL (adjoint radiance of the lane's splat), xyz
+    float2 *pos;                     // splat position, only for multi-pass renders (a single pass re-derives it from (seed, lane))
     uint8_t *cls_q;                  // shading class of the hit of queue entry i of the current iteration (trace -> classify)
-    B2_DEV StateRef<float4> ray_o(uint32_t s) const { return StateRef<float4>{ &p0[(size_t) s * 2] }; }
-    B2_DEV StateRef<float4> ray_d(uint32_t s) const { return StateRef<float4>{ &p0[(size_t) s * 2 + 1] }; }
-    B2_DEV StateRef<float4> hit(uint32_t s) const { return StateRef<float4>{ &p1[(size_t) s * 2] }; }
-    B2_DEV StateRef<uint32_t> hit_mesh(uint32_t s) const { return StateRef<uint32_t>{ &((uint32_t *) (p1 + (size_t) s * 2 + 1))[0] }; }
-    B2_DEV StateRef<uint32_t> vis(uint32_t s) const { return StateRef<uint32_t>{ &((uint32_t *) (p1 + (size_t) s * 2 + 1))[1] }; }
-    B2_DEV StateRef<float2> pos(uint32_t s) const { return StateRef<float2>{ &((float2 *) (p1 + (size_t) s * 2 + 1))[1] }; }
-    B2_DEV StateRef<uint4> rng(uint32_t s) const { return StateRef<uint4>{ &((uint4 *) p2)[(size_t) s * 2] }; }
-    B2_DEV StateRef<float4> thr(uint32_t s) const { return StateRef<float4>{ &p2[(size_t) s * 2 + 1] }; }
-    B2_DEV StateRef<float4> rad(uint32_t s) const { return StateRef<float4>{ &p3[(size_t) s * 2] }; }
-    B2_DEV StateRef<float4> prev(uint32_t s) const { return StateRef<float4>{ &p3[(size_t) s * 2 + 1] }; }
-    B2_DEV StateRef<float4> sh_o(uint32_t s) const { return StateRef<float4>{ &s0[(size_t) s * 2] }; }
-    B2_DEV StateRef<float4> sh_d(uint32_t s) const { return StateRef<float4>{ &s0[(size_t) s * 2 + 1] }; }
-    B2_DEV StateRef<float4> sh_a(uint32_t s) const { return StateRef<float4>{ &s1[(size_t) s * 2] }; }
-    B2_DEV StateRef<float4> sh_b(uint32_t s) const { return StateRef<float4>{ &s1[(size_t) s * 2 + 1] }; }
     uint32_t *q[2];                  // closest-ray queues (lane slots), double buffered by iteration parity
-    uint32_t *q_shadow[2];           // shadow-ray queues, by iteration parity
+    uint32_t *q_shadow;              // shadow-ray queue
     uint32_t *qc[5];                 // closest hits of the current iteration sorted by shading class (CLS_*)
     uint32_t class_mask;             // classes present in the scene
     WfCtl *ctl;
     uint32_t capacity;
 };
 
-enum { WF_FLAG_PREV_DELTA = 1u << 24, WF_FLAG_FIRST = 1u << 25, WF_FLAG_VALID_RAY = 1u << 26, WF_DEPTH_MASK = 0x00ffffffu };
+enum { WF_FLAG_PREV_DELTA = 1u << 24, WF_FLAG_FIRST = 1u << 25, WF_FLAG_VALID_RAY = 1u << 26, WF_FLAG_PENDING = 1u << 27, WF_DEPTH_MASK = 0x00ffffffu };
 
 struct WfLaunch {
     WfState st;
@@ -84,10 +68,13 @@ struct WfLaunch {
     uint32_t n;                      // lanes in this chunk
     uint32_t it;                     // global iteration counter (slot = it & 3)
     uint32_t pass;                   // > 0: continue each lane's PCG32 stream (integrator.cpp:319-328)
-    uint32_t slice;                  // trace: traversal micro-steps between two refill points
-    uint32_t vis_bit;                // trace: bit to set in vis[] for arriving shadow rays; shade<ADJ>: bit to read; ~0u = off
+    uint32_t first;                  // bounce 0 of a pass: every lane of the chunk is live, rays come from the sensor
+    uint32_t no_hit;                 // shade: no trace ran for this bounce (path.py with max_depth <= 1): every lane is a miss
+    uint32_t bounce;                 // bounce index of this launch (PRB: the visibility bit a shadow record belongs to)
+    uint32_t record_vis;             // PRB primal pass of render_backward: keep the visibility of every emitter sample
     uint32_t tri_thresh;             // trace: lanes with pending leaf triangles that trigger a triangle step
-    uint32_t prefetch;               // trace: bit 0 = prefetch parked leaf triangles into L1
+    uint32_t refill_thresh;          // trace: idle lanes that trigger a refill from the staged rays
+    uint32_t store_pos;              // multi-pass render: keep the splat position in st.pos
 };
 
 // per-kernel-kind timing (host side)
@@ -95,6 +82,12 @@ enum { WF_K_TRACE = 0, WF_K_SHADE = 1, WF_K_SPLAT = 2, WF_K_OTHER = 3, WF_K_COUN
 struct WfTiming { std::vector<cudaEvent_t> ev; std::vector<int> kind; size_t used = 0; };
 void wf_set_timing(WfTiming *t);          // nullptr = off (default)
 void wf_collect_timing(WfTiming &t, double ms[WF_K_COUNT], uint64_t n[WF_K_COUNT]);   // after the stream has been synchronised
+void wf_tm_begin(int kind, cudaStream_t st);
+void wf_tm_end(cudaStream_t st);
+
+// trace launches (wf_trace.cu).  primary: rays of bounce 0 come from the sensor (needs the full RenderParams).
+int wf_trace_blocks(bool count, int sm_count);          // resident grid of the persistent trace kernel (0 = cannot be resident)
+void wf_launch_trace(bool count, bool primary, const RenderParams &p, const WfLaunch &w, int blocks, cudaStream_t stream);
 
 // host entry points (wavefront.cu)
 size_t wf_state_bytes(uint32_t capacity);

@@ -98,6 +98,7 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
         float *rec_dev; CUDA_OK(s->upload(rec.data(), rec.size(), rec_dev)); d.shade = (const float4 *) rec_dev;
     }
     // meshes + face -> mesh table
+    if (desc->n_meshes >= (1u << 28)) return fail(-2, "b2_scene_create: more than 2^28 meshes");
     std::vector<DMesh> meshes(desc->n_meshes); std::vector<uint32_t> face_mesh(desc->n_faces, 0);
     for (uint32_t i = 0; i < desc->n_meshes; ++i) {
         const b2_mesh &m = desc->meshes[i];
@@ -107,7 +108,8 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
         const uint32_t cls = mb.type == B2_BSDF_DIFFUSE ? (mb.reflectance_tex >= 0 ? 1u : 0u) : ((mb.type == B2_BSDF_ROUGHCONDUCTOR || mb.type == B2_BSDF_ROUGHDIELECTRIC || mb.type == B2_BSDF_ROUGHPLASTIC) ? 2u : 3u);   // CLS_* of b2_shade.cuh: glossy | delta
         s->class_mask |= 1u << cls;
         meshes[i] = DMesh{ m.bsdf, m.emitter, m.flags, m.first_face, m.n_faces, cls, { 0, 0 } };
-        for (uint32_t f = 0; f < m.n_faces; ++f) face_mesh[m.first_face + f] = i;
+        // the triangle records carry mesh | class << 28 (the trace kernel's epilogue needs both and nothing else of the mesh)
+        for (uint32_t f = 0; f < m.n_faces; ++f) face_mesh[m.first_face + f] = i | (cls << 28);
     }
     DMesh *meshes_dev; CUDA_OK(s->upload(meshes.data(), meshes.size(), meshes_dev)); d.meshes = meshes_dev;
     CUDA_OK(s->upload(face_mesh.data(), face_mesh.size(), s->face_mesh_dev));
@@ -230,6 +232,14 @@ int b2_scene_build_accel(b2_scene *s, int builder, uintptr_t stream, b2_build_st
     CUDA_OK(cudaSetDevice(s->ctx->device));
     bvh_free(s->bvh);
     std::string err;
+    // The traversal stacks hold kStackSize entries (one node group per level of the wide tree below the root, b2_bvh.cuh /
+    // wf_trace.cu); a deeper tree would have to drop subtrees, so it is never handed to the kernels: AUTO falls back to
+    // the other builder, an explicitly requested builder fails.
+    // B2_MAX_BVH_DEPTH lowers the limit (test hook for this guard)
+    const char *e_depth = getenv("B2_MAX_BVH_DEPTH");
+    const uint32_t depth_limit = e_depth ? (uint32_t) std::min(std::max(atoi(e_depth), 0), kStackSize) : (uint32_t) kStackSize;
+    auto too_deep = [depth_limit](const Bvh &t) { return t.depth > depth_limit; };
+    auto deep_msg = [depth_limit](const Bvh &t) { return "b2_scene_build_accel: wide-tree depth " + std::to_string(t.depth) + " exceeds the traversal stack (" + std::to_string(depth_limit) + " levels)"; };
     if (builder == B2_BUILDER_AUTO) {
         // build both trees and keep the one the SAH model prefers (the build is a few ms; the render traces it for seconds)
         Bvh a, b;
@@ -238,11 +248,16 @@ int b2_scene_build_accel(b2_scene *s, int builder, uintptr_t stream, b2_build_st
         // PLOC's clusters are not octant-shaped, so the slot ^ octant child order is less strictly front to back than on
         // the radix tree: it has to win the SAH estimate by 10 % (bedroom stand-in: 0.78 -> PLOC, +13 % Msamples/s;
         // 10 M random triangles: 0.98 -> LBVH, where PLOC measured 11 % slower; profiles/README.md)
-        const bool keep_a = !(b.sah_cost < 0.9f * a.sah_cost);
+        bool keep_a = !(b.sah_cost < 0.9f * a.sah_cost);
+        if (too_deep(a) && too_deep(b)) { const std::string m = deep_msg(a); bvh_free(a); bvh_free(b); return fail(-11, m); }
+        if (too_deep(a)) keep_a = false; else if (too_deep(b)) keep_a = true;
         const float ms = a.ms_total + b.ms_total;
         if (keep_a) { bvh_free(b); s->bvh = a; } else { bvh_free(a); s->bvh = b; }
         s->bvh.ms_total = ms;
-    } else if (!bvh_build(s->d.pos, s->d.faces, s->face_mesh_dev, s->d.n_faces, builder, (cudaStream_t) stream, s->bvh, err)) return fail(-11, err);
+    } else {
+        if (!bvh_build(s->d.pos, s->d.faces, s->face_mesh_dev, s->d.n_faces, builder, (cudaStream_t) stream, s->bvh, err)) return fail(-11, err);
+        if (too_deep(s->bvh)) { const std::string m = deep_msg(s->bvh); bvh_free(s->bvh); return fail(-11, m); }
+    }
     s->d.nodes = s->bvh.nodes; s->d.tris = s->bvh.tris; s->d.n_nodes = s->bvh.n_nodes;
     if (stats) {
         stats->ms_morton_sort = s->bvh.ms_morton_sort; stats->ms_lbvh = s->bvh.ms_lbvh; stats->ms_collapse = s->bvh.ms_collapse; stats->ms_total = s->bvh.ms_total;
@@ -445,7 +460,6 @@ int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_i
     uint32_t spp_per_pass, n_passes; uint64_t wavefront;
     if (int rc = derive_passes(s, a, spp_per_pass, n_passes, wavefront)) return rc;
     if (n_passes != 1) return fail(-2, "render_backward: wavefront exceeds 2^32 lanes (common.py:358-363)");
-    if (a->sample_count) return fail(-2, "render_backward: sample shards are a render-only split (shard the adjoint by lane ranges)");
     const size_t film_bytes = sizeof(float) * 4 * (size_t) s->d.sensor.crop_width * s->d.sensor.crop_height;
     if (!s->wfilm) { CUDA_OK(cudaMalloc((void **) &s->wfilm, film_bytes)); s->allocs.push_back(s->wfilm); }
     const bool count = counters != nullptr;
@@ -454,7 +468,8 @@ int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_i
     //     args->reserved bit 0: the weight film of an earlier call with the same (seed, spp) is still valid (sharded bands)
     if (!(a->reserved & 1u)) {
         RenderParams p; int blocks; size_t smem;
-        if (int rc = setup_params(s, a, MODE_WEIGHTS, false, p, blocks, smem, 0, 0)) return rc;
+        b2_render_args wa = *a; wa.sample_begin = 0; wa.sample_count = 0;      // W of the WHOLE sample set, also for a sample shard
+        if (int rc = setup_params(s, &wa, MODE_WEIGHTS, false, p, blocks, smem, 0, 0)) return rc;
         p.film = s->wfilm;
         CUDA_OK(cudaMemsetAsync(s->wfilm, 0, film_bytes, st));
         CUDA_OK(cudaMemsetAsync(s->unit_counter, 0, 16, st));
@@ -509,7 +524,6 @@ int b2_render_forward(b2_scene *s, const b2_render_args *a, const b2_grad_target
     if (!s || !a || !film_rgbw_dev || (n_targets && !tangents)) return fail(-1, "b2_render_forward: null argument");
     if (n_targets < 0 || n_targets > kMaxGradTargets) return fail(-2, "b2_render_forward: too many tangent targets");
     if (a->kernel != B2_KERNEL_WAVEFRONT || a->max_depth > 32) return fail(-2, "b2_render_forward: wavefront kernel with max_depth <= 32 only");
-    if (a->sample_count) return fail(-2, "b2_render_forward: sample shards are a render-only split (shard by lane ranges)");
     CUDA_OK(cudaSetDevice(s->ctx->device));
     cudaStream_t st = (cudaStream_t) stream;
     L2Pin pin(s, st);

@@ -1,0 +1,259 @@
+// wf_trace.cu -- k_wf_trace: Scene::ray_intersect_preliminary + Scene::ray_test of the wavefront (scene.cpp:191-235;
+// Embree / OptiX in the reference, scene_embree.inl:245-433, scene_optix.inl:602-743).
+//
+// Persistent warps.  Each warp owns a three-stage ray pipeline so that a lane whose ray ends can be refilled within a
+// few instructions instead of a dependent global-load chain:
+//   stage A   lane 0 reserves the next 32 queue entries (atomicAdd on the launch's fetch counter)
+//   stage B   the 32 lane slots of that batch are loaded from the queue (closest queue first, then the shadow queue)
+//   stage C   the 32 rays are copied global -> shared with cp.async (bounce 0: computed from the lane index, there is
+//             no generate kernel: sampler seed, jitter, sensor ray -- integrator.cpp:293-310,419-436, sampler.cpp:129-148,
+//             perspective.cpp:239-280)
+// Every stage runs one batch ahead of the next, so the latencies of the atomic, of the queue read and of the ray read
+// overlap traversal; idle lanes take their next ray from shared memory as soon as `refill_thresh` of them are idle.
+//
+// Traversal: vote-scheduled micro-steps.  Per micro-step the warp does either a NODE step (pop a child, five 128-bit
+// loads, eight branch-free slab tests, b2_bvh.cuh) for the lanes that have node work, or a TRIANGLE step (one
+// Moeller-Trumbore test per lane, mesh.h:469-492) once `tri_thresh` lanes hold parked leaf triangles; leaf hits found by a
+// node step are parked in a per-lane queue in shared memory.  The traversal stack lives in shared memory ([depth][thread],
+// conflict free; entries beyond kSmemStack spill to local memory, which the depth guard of b2_scene_build_accel bounds
+// at kStackSize).  Per-ray values that are touched once per ray (lane slot, queue index, u, v, face, mesh) live in
+// shared memory, which keeps the kernel at 64 registers without spills.
+//
+// Epilogue = stores only: a closest ray writes its 32-byte hit record with one 256-bit store (+ the class byte for the
+// counting sort); a shadow ray that arrives sets the `arrived` word of the lane's deferred-NEE record.
+#include "b2_path.cuh"
+#include "b2_wavefront.cuh"
+
+namespace b2 {
+
+constexpr int kTraceThreads = 256;
+constexpr int kTraceWarps = kTraceThreads / 32;
+constexpr int kSmemStack = 8;                       // stack entries per thread held in shared memory
+constexpr int kLocalStack = kStackSize - kSmemStack; // overflow entries in local memory (never reached on the benchmark trees)
+constexpr int kTriQueue = 4;                        // parked leaf-triangle groups per thread (shared memory)
+#ifndef B2_TRACE_MINBLOCKS
+#define B2_TRACE_MINBLOCKS 4
+#endif
+
+// lane flag word
+enum : uint32_t { TF_OCT = 7u, TF_ANY = 8u, TF_TEX = 16u, TF_FOUND = 32u, TF_NQ_SHIFT = 8, TF_NQ_ONE = 1u << 8, TF_NQ_MASK = 7u << 8, TF_HAVE = 1u << 31 };
+
+B2_DEV void cp_async16(void *smem, const void *gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"((uint32_t) __cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+B2_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+B2_DEV void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+template <bool COUNT>
+B2_DEV void trace_flush_counters(const Counters<COUNT> &cnt, unsigned long long *out) {
+    if constexpr (COUNT) {
+        if (out) {
+#pragma unroll 1
+            for (int k = 0; k < C_N; ++k) {
+                unsigned long long v = cnt.v[k];
+                for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if ((threadIdx.x & 31) == 0 && v) atomicAdd(out + k, v);
+            }
+        }
+    }
+}
+
+template <bool COUNT, bool PRIMARY>
+__global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
+    __shared__ uint2 s_stack[kSmemStack][kTraceThreads];
+    __shared__ uint2 s_pend[kTriQueue][kTraceThreads];
+    __shared__ float4 s_so[kTraceWarps][2][32], s_sd[kTraceWarps][2][32];     // staged rays: o | maxt, d | flag word
+    __shared__ uint32_t s_ss[kTraceWarps][2][32];                             // staged lane slot | any << 31
+    __shared__ float2 s_uv[kTraceThreads];                                    // closest hit so far: u, v
+    __shared__ uint2 s_fm[kTraceThreads], s_id[kTraceThreads];                // face, mesh | class << 28 ; lane slot, queue index
+    const DScene &sc = p.sc; const WfState &st = w.st;
+    const uint32_t nc = PRIMARY ? w.n : st.ctl->n_closest[w.it & 3u], ns = PRIMARY ? 0u : st.ctl->n_shadow[(w.it + 3u) & 3u], total = nc + ns;
+    const uint32_t *qc = st.q[w.it & 1u], *qs = st.q_shadow;
+    uint32_t *fetch = &st.ctl->fetch[w.it & 3u];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t lt_mask = (1u << lane) - 1u, full = 0xffffffffu;
+    Counters<COUNT> cnt;
+    uint2 l_stack[kLocalStack];
+
+    // ---- ray pipeline (all warp-uniform except pend_a / slot_b)
+    uint32_t pend_a = 0;                    // lane 0: result of the stage-A atomic, not yet broadcast
+    uint32_t base_b = 0, nb_b = 0, slot_b = 0;   // batch whose lane slots are (being) loaded into slot_b
+    uint32_t base_n = 0, cnt_n = 0;         // batch staged in buffer cur ^ 1 (rays in flight)
+    uint32_t base_c = 0, cnt_c = 0, cons = 0, cur = 1;   // batch being consumed from buffer cur
+    bool exhausted = total == 0;
+
+    auto stage_a = [&]() { if (lane == 0) pend_a = atomicAdd(fetch, 32u); };
+    auto stage_b = [&]() {               // consumes pend_a
+        base_b = __shfl_sync(full, pend_a, 0);
+        nb_b = base_b < total ? min(32u, total - base_b) : 0u;
+        if ((uint32_t) lane < nb_b) {
+            const uint32_t e = base_b + lane;
+            if (PRIMARY) slot_b = e;
+            else slot_b = e >= nc ? (qs[e - nc] | 0x80000000u) : qc[e];
+        }
+    };
+    auto stage_c = [&]() {               // consumes slot_b into buffer cur ^ 1
+        base_n = base_b; cnt_n = nb_b;
+        if ((uint32_t) lane < nb_b) {
+            const uint32_t nb = cur ^ 1u;
+            if (PRIMARY) {
+                Pcg32 rng;
+                const uint32_t ln = (uint32_t) (w.chunk_begin + slot_b);
+                if (w.pass == 0) rng.seed_lane(p.seed, global_lane(p, ln));
+                else { const float4 r = __ldg(&st.rng[slot_b].a); rng.state = (uint64_t) __float_as_uint(r.x) | ((uint64_t) __float_as_uint(r.y) << 32); rng.inc = (uint64_t) __float_as_uint(r.z) | ((uint64_t) __float_as_uint(r.w) << 32); }
+                const Ray ray = primary_ray(p, ln, rng);
+                s_so[warp][nb][lane] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
+                s_sd[warp][nb][lane] = make_float4(ray.d.x, ray.d.y, ray.d.z, 0.f);
+            } else {
+                const Elem *src = (slot_b >> 31) ? &st.shr[slot_b & 0x7fffffffu] : &st.ray[slot_b];
+                cp_async16(&s_so[warp][nb][lane], &src->a);
+                cp_async16(&s_sd[warp][nb][lane], &src->b);
+            }
+            s_ss[warp][nb][lane] = slot_b;
+        }
+        if (!PRIMARY) cp_async_commit();
+    };
+    // prime: batch 0 staged, batch 1 slots loading, batch 2 reserved
+    if (!exhausted) { stage_a(); stage_b(); stage_a(); stage_c(); stage_b(); stage_a(); }
+
+    f3 o, d; float idx = 0.f, idy = 0.f, idz = 0.f, tbest = 0.f;
+    uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u);
+    int sp = 0; uint32_t fl = 0;
+
+    for (;;) {
+        // ---- refill idle lanes from the staged rays (warp converged here)
+        const uint32_t idle = __ballot_sync(full, !(fl & TF_HAVE));
+        if (idle && !exhausted) {
+            const uint32_t k = __popc(idle);
+            if (k >= w.refill_thresh || idle == full) {
+                if (cons == cnt_c) {            // advance the pipeline: the staged batch becomes current
+                    if (!PRIMARY) cp_async_wait_all();
+                    __syncwarp();
+                    cur ^= 1u; cons = 0; base_c = base_n; cnt_c = cnt_n;
+                    stage_c(); stage_b(); stage_a();
+                    if (cnt_c == 0u) exhausted = true;
+                }
+                const uint32_t take = min(k, cnt_c - cons), rank = __popc(idle & lt_mask);
+                if (!(fl & TF_HAVE) && rank < take) {
+                    const uint32_t e = cons + rank;
+                    const float4 o4 = s_so[warp][cur][e], d4 = s_sd[warp][cur][e];
+                    const uint32_t sl = s_ss[warp][cur][e];
+                    o = f3(o4.x, o4.y, o4.z); d = f3(d4.x, d4.y, d4.z); tbest = o4.w;
+                    const float tiny = kTinyDir;
+                    idx = 1.f / (fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x));
+                    idy = 1.f / (fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y));
+                    idz = 1.f / (fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z));
+                    const uint32_t octinv = (d.x >= 0.f ? 1u : 0u) | (d.y >= 0.f ? 2u : 0u) | (d.z >= 0.f ? 4u : 0u);
+                    const bool any = !PRIMARY && (sl >> 31) != 0u;
+                    fl = TF_HAVE | octinv | (any ? TF_ANY : 0u) | ((any && d4.w != 0.f) ? TF_TEX : 0u);
+                    s_id[tid] = make_uint2(sl & 0x7fffffffu, base_c + e);
+                    s_fm[tid] = make_uint2(0xffffffffu, 0u); s_uv[tid] = make_float2(0.f, 0.f);
+                    ng = sc.n_nodes ? make_uint2(0u, (1u << (24 + octinv)) | 1u) : make_uint2(0u, 0u);
+                    tg = make_uint2(0u, 0u); sp = 0;
+                    cnt.add(any ? C_SHADOW : C_CLOSEST);
+                }
+                cons += take;
+            }
+        }
+        const uint32_t smask = __ballot_sync(full, (fl & TF_HAVE) != 0u);
+        if (smask == 0u) { if (exhausted) break; else continue; }
+
+        if (fl & TF_HAVE) {
+            // ---- one micro-step: the lanes with a ray vote for a NODE step or a TRIANGLE step
+            const bool node_work = (ng.y & 0xff000000u) != 0u || sp > 0;
+            const bool can_node = node_work && (tg.y == 0u || (fl & TF_NQ_MASK) < ((uint32_t) kTriQueue << TF_NQ_SHIFT));
+            const uint32_t P = __ballot_sync(smask, tg.y != 0u), N = __ballot_sync(smask, can_node);
+            if (N == 0u || (uint32_t) __popc(P) >= w.tri_thresh) {
+                if (tg.y) {
+                    const int i = __ffs(tg.y) - 1;
+                    tg.y &= tg.y - 1;
+                    const float4 *tp = sc.tris + (size_t) (tg.x + i) * 3;
+                    const float4 r0 = __ldg(tp), r1 = __ldg(tp + 1), r2 = __ldg(tp + 2);
+                    cnt.add(C_TRIS);
+                    // Mesh::moeller_trumbore (mesh.h:469-492)
+                    const f3 e1(r1.x, r1.y, r1.z), e2(r2.x, r2.y, r2.z);
+                    const f3 pvec = cross(d, e2);
+                    const float inv_det = rcp(dot(e1, pvec));
+                    const f3 tvec = o - f3(r0.x, r0.y, r0.z);
+                    const float u = dot(tvec, pvec) * inv_det;
+                    bool ok = u >= 0.f && u <= 1.f;
+                    const f3 qvec = cross(tvec, e1);
+                    const float v = dot(d, qvec) * inv_det;
+                    ok = ok && v >= 0.f && u + v <= 1.f;
+                    const float t = dot(e2, qvec) * inv_det;
+                    // tbest starts as the ray's maxt and only shrinks: t <= maxt is implied; equal t resolves to the lowest face
+                    ok = ok && t >= 0.f && t <= tbest;
+                    if (ok) {
+                        const uint32_t face = __float_as_uint(r0.w);
+                        if (fl & TF_ANY) { fl = (fl | TF_FOUND) & ~TF_NQ_MASK; tg.y = 0u; ng.y = 0u; sp = 0; }
+                        else if (t < tbest || face < s_fm[tid].x) {
+                            tbest = t; s_uv[tid] = make_float2(u, v); s_fm[tid] = make_uint2(face, __float_as_uint(r1.w));
+                        }
+                    }
+                    if (tg.y == 0u && (fl & TF_NQ_MASK)) { fl -= TF_NQ_ONE; tg = s_pend[(fl & TF_NQ_MASK) >> TF_NQ_SHIFT][tid]; }
+                }
+            } else if (can_node) {
+                if ((ng.y & 0xff000000u) == 0u) { --sp; ng = sp < kSmemStack ? s_stack[sp][tid] : l_stack[sp - kSmemStack]; }
+                const int bit = 31 - __clz(ng.y);
+                ng.y &= ~(1u << bit);
+                if (ng.y & 0xff000000u) {       // siblings left: push the group (depth <= kStackSize, guarded at build time)
+                    if (sp < kSmemStack) s_stack[sp][tid] = ng; else l_stack[sp - kSmemStack] = ng;
+                    sp++;
+                }
+                const uint32_t octinv = fl & TF_OCT;
+                const uint32_t cslot = (uint32_t) (bit - 24) ^ octinv;
+                const uint32_t rel = __popc(ng.y & 0xffu & ~(0xffffffffu << cslot));
+                const uint4 *np = sc.nodes + (size_t) (ng.x + rel) * 5;
+                const uint4 w0 = __ldg(np), w1 = __ldg(np + 1), w2 = __ldg(np + 2), w3 = __ldg(np + 3), w4 = __ldg(np + 4);
+                cnt.add(C_NODES);
+                const uint32_t imask = w0.w >> 24;
+                const uint32_t hitmask = node_slab_hits(w0, w1, w2, w3, w4, o, idx, idy, idz, octinv, tbest, sc.qmagic);
+                ng = make_uint2(w1.x, (permute_octant(hitmask, octinv) << 24) | imask);
+                const uint32_t thits = hitmask & 0x00ffffffu;
+                if (thits) {
+                    if (tg.y == 0u) tg = make_uint2(w1.y, thits);
+                    else { s_pend[(fl & TF_NQ_MASK) >> TF_NQ_SHIFT][tid] = make_uint2(w1.y, thits); fl += TF_NQ_ONE; }
+                }
+            }
+            // ---- epilogue of a finished ray: stores only
+            if ((ng.y & 0xff000000u) == 0u && sp == 0 && tg.y == 0u && (fl & TF_NQ_MASK) == 0u) {
+                const uint2 id = s_id[tid];
+                if (fl & TF_ANY) {
+                    if (!(fl & TF_FOUND)) {         // the emitter sample arrives: the lane's next shade (or the splat) adds fma(a, b, L)
+                        if (fl & TF_TEX) cnt.add(C_TEX);
+                        st.shf[id.x].a.w = 1.f;
+                    }
+                } else {
+                    const uint2 fm = s_fm[tid]; const float2 uv = s_uv[tid];
+                    const bool found = fm.x != 0xffffffffu;
+                    const uint32_t cls = found ? (fm.y >> 28) : (uint32_t) CLS_MISS;
+                    Elem h;
+                    h.a = make_float4(tbest, uv.x, uv.y, __uint_as_float(fm.x));
+                    h.b = make_float4(__uint_as_float(found ? (fm.y & 0x0fffffffu) : 0xffffffffu), __uint_as_float(cls), 0.f, 0.f);
+                    st256(&st.hit[id.x], h);
+                    st.cls_q[id.y] = (uint8_t) cls;                      // for classify(it), by queue position
+                }
+                fl = 0u;
+            }
+        }
+    }
+    trace_flush_counters(cnt, p.counters);
+}
+
+int wf_trace_blocks(bool count, int sm_count) {
+    int occ = 0;
+    if (count) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, false>, kTraceThreads, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<false, false>, kTraceThreads, 0);
+    static const int tune_blocks = getenv("B2_TRACE_BLOCKS") ? atoi(getenv("B2_TRACE_BLOCKS")) : 0;
+    if (tune_blocks > 0) occ = std::min(occ, tune_blocks);
+    return occ * sm_count;
+}
+
+void wf_launch_trace(bool count, bool primary, const RenderParams &p, const WfLaunch &w, int blocks, cudaStream_t stream) {
+    wf_tm_begin(WF_K_TRACE, stream);
+    if (count) { if (primary) k_wf_trace<true, true><<<blocks, kTraceThreads, 0, stream>>>(p, w); else k_wf_trace<true, false><<<blocks, kTraceThreads, 0, stream>>>(p, w); }
+    else { if (primary) k_wf_trace<false, true><<<blocks, kTraceThreads, 0, stream>>>(p, w); else k_wf_trace<false, false><<<blocks, kTraceThreads, 0, stream>>>(p, w); }
+    wf_tm_end(stream);
+}
+
+}  // namespace b2

@@ -78,13 +78,38 @@ def render_sharded(integrator, scene, seed=0, spp=0, rank=0, world=1, develop=Tr
     return ds.develop(film) if develop else film
 
 
-def render_backward_sharded(integrator, scene, params, grad_in, seed=0, spp=0, rank=0, world=1, bands_per_rank=8):
-    """PRB adjoint over this rank's bands; gradients are all-reduced into ``params.grad``.  The weight film of the
-    sample set is recomputed on every rank (it is cheap and keeps the pass free of a second collective)."""
+def render_sharded_samples(integrator, scene, seed=0, spp=0, rank=0, world=1, develop=True, film=None):
+    """The balanced split: every rank renders every pixel with its slice of the samples (``sample_shard``), one film
+    all-reduce.  Falls back to image bands when the samples per pass do not divide by the world size."""
+    ds = integrator._scene(scene)
+    spp = spp or ds.desc.spp
+    n = ds.wavefront_size(spp, integrator.samples_per_pass)
+    spp_pp = n // (ds.lane_grid[0] * ds.lane_grid[1])
+    sh = sample_shard(spp_pp, world, rank)
+    if world > 1 and sh is None:
+        return render_sharded(integrator, scene, seed, spp, rank, world, develop)
+    film = ds.new_film() if film is None else film
+    kw = dict(sample_begin=sh[0], sample_count=sh[1]) if sh else {}
+    integrator.render(ds, seed=seed, spp=spp, develop=False, evaluate=False, film=film, **kw)
+    merge_sum(film)
+    return ds.develop(film) if develop else film
+
+
+def render_backward_sharded(integrator, scene, params, grad_in, seed=0, spp=0, rank=0, world=1, bands_per_rank=8, split="samples"):
+    """PRB adjoint of this rank's shard; gradients are all-reduced into ``params.grad`` (RBIntegrator.render_backward,
+    common.py:623-781, over N devices).  The weight film of the WHOLE sample set is recomputed on every rank (positions
+    depend on (seed, lane) only; it is cheap and keeps the pass free of a second collective).  ``split``: "samples" =
+    every rank replays its slice of every pixel's samples (balanced), "bands" = image bands."""
     ds = integrator._scene(scene)
     spp = spp or ds.desc.spp
     n = ds.wavefront_size(spp, 0)
-    for i, (a, b) in enumerate(shard_plan(n, spp, ds.lane_grid[1], world, rank, bands_per_rank)):
-        integrator.render_backward(ds, params, grad_in, seed=seed, spp=spp, lane_begin=a, lane_end=b, reuse_weights=i > 0)
+    sh = sample_shard(spp, world, rank) if split == "samples" else None
+    if world <= 1:
+        integrator.render_backward(ds, params, grad_in, seed=seed, spp=spp)
+    elif sh is not None:
+        integrator.render_backward(ds, params, grad_in, seed=seed, spp=spp, sample_begin=sh[0], sample_count=sh[1])
+    else:
+        for i, (a, b) in enumerate(shard_plan(n, spp, ds.lane_grid[1], world, rank, bands_per_rank)):
+            integrator.render_backward(ds, params, grad_in, seed=seed, spp=spp, lane_begin=a, lane_end=b, reuse_weights=i > 0)
     for g in params.grad.values():
         merge_sum(g)

@@ -187,14 +187,16 @@ class B2Integrator:
                     variant=self.variant, spp_per_pass=self.samples_per_pass, env_warp=self.env_warp, kernel=self.kernel, **kw)
 
     def render(self, scene, sensor=0, seed=0, spp=0, develop=True, evaluate=True, film=None, lane_begin=0, lane_end=0,
-               counters=False):
+               counters=False, sample_begin=0, sample_count=0):
         """-> [H, W, 3] float32 torch tensor on the device (``develop=True``) or the RGBW film (``develop=False``).
 
-        ``lane_begin/lane_end`` restrict the render to a shard of the wavefront (multi-GPU, see ``dist.py``)."""
+        ``lane_begin/lane_end`` (image bands) or ``sample_begin/sample_count`` (a slice of every pixel's samples) restrict
+        the render to a shard of the wavefront (multi-GPU, see ``dist.py``)."""
         if sensor not in (0, None):
             raise RuntimeError("only sensor 0 is supported")
         ds = self._scene(scene)
-        film, cnt = ds.render_film(film=film, counters=counters, **self._args(ds, seed, spp, lane_begin=lane_begin, lane_end=lane_end))
+        film, cnt = ds.render_film(film=film, counters=counters, **self._args(ds, seed, spp, lane_begin=lane_begin, lane_end=lane_end,
+                                                                              sample_begin=sample_begin, sample_count=sample_count))
         self.last_counters = cnt
         out = ds.develop(film) if develop else film
         if evaluate:
@@ -221,10 +223,12 @@ class PRBIntegrator(B2Integrator):
     default_max_depth, default_rr_depth = 6, 5
 
     def render_backward(self, scene, params: SceneParameters, grad_in, sensor=0, seed=0, spp=0, lane_begin=0, lane_end=0,
-                        counters=False, reuse_weights=False):
-        """Accumulates d(loss)/d(param) into ``params.grad[key]`` (side effect, like ``dr.grad(params[key])``)."""
+                        counters=False, reuse_weights=False, sample_begin=0, sample_count=0):
+        """Accumulates d(loss)/d(param) into ``params.grad[key]`` (side effect, like ``dr.grad(params[key])``).
+        A shard (lane range or sample slice) adds its share; the weight film is always that of the whole sample set."""
         ds = self._scene(scene)
-        a = self._args(ds, seed, spp, lane_begin=lane_begin, lane_end=lane_end, reuse_weights=reuse_weights)
+        a = self._args(ds, seed, spp, lane_begin=lane_begin, lane_end=lane_end, reuse_weights=reuse_weights,
+                       sample_begin=sample_begin, sample_count=sample_count)
         a.pop("variant")
         self.last_counters = ds.render_backward(grad_in, params.targets(), counters=counters, **a)
         return None

@@ -158,10 +158,14 @@ _BEDROOM_ALBEDOS = [[0.483044, 0.384664, 0.301561], [0.558543, 0.558543, 0.55854
 _AL_ETA, _AL_K = [1.65746, 0.880369, 0.521229], [9.22387, 6.26952, 4.837]
 
 
-def bedroom_standin(width=1280, height=720, spp=64, n_tris=1_800_000, seed=1, envmap=True, tex_res=1024):
+def bedroom_standin(width=1280, height=720, spp=64, n_tris=1_800_000, seed=1, envmap=True, tex_res=1024, palette="north_star"):
     """Bedroom *stand-in* (the reference's meshes/textures are git-LFS pointers): camera, film, filter and the two area
     lights are verbatim from data/bedroom/scene.xml:10-25,706-731; room shell + procedural furniture of ~n_tris
-    triangles with the scene's BSDF palette (65 % diffuse, 10 % textured diffuse, 15 % rough conductor, 10 % dielectric)."""
+    triangles.  ``palette="north_star"`` (BASELINE config C2 as SURVEY.md 8d restates it): 65 % diffuse, 10 % textured diffuse,
+    15 % rough conductor, 10 % dielectric.  ``palette="scene_xml"``: the BSDF definitions of data/bedroom/scene.xml:26-217
+    themselves -- nonlinear rough plastic with a bitmap diffuse_reflectance on the floor and the wooden furniture (WoodFloorBSDF,
+    WoodFurnitureBSDF), smooth conductor mirrors, rough conductors (ggx 0.2 / 0.1, beckmann 0.1), a rough dielectric lamp glass,
+    smooth glass, a 0.53-opacity curtain mask and the diffuse albedos, by object in roughly the file's proportions."""
     rng = np.random.RandomState(seed)
     cam = np.array([[-0.653592, -0.0128556, -0.756738, 3.45558], [2.84986e-09, 0.999856, -0.0169858, 1.21244],
                     [0.756847, -0.0111018, -0.653498, 3.29897], [0, 0, 0, 1]])
@@ -184,6 +188,20 @@ def bedroom_standin(width=1280, height=720, spp=64, n_tris=1_800_000, seed=1, en
     d["metal_ggx"] = two({"type": "roughconductor", "distribution": "ggx", "alpha": 0.2, "eta": _AL_ETA, "k": _AL_K})
     d["metal_beckmann"] = two({"type": "roughconductor", "distribution": "beckmann", "alpha": 0.1, "eta": _AL_ETA, "k": _AL_K})
     d["glass"] = {"type": "dielectric", "int_ior": 1.5, "ext_ior": 1.0}
+    xml = palette == "scene_xml"
+    if palette not in ("north_star", "scene_xml"):
+        raise ValueError("palette: 'north_star' or 'scene_xml'")
+    if xml:     # data/bedroom/scene.xml:108-217
+        d["wood_floor"] = two({"type": "roughplastic", "alpha": 0.15, "distribution": "ggx", "int_ior": 1.5, "ext_ior": 1.0, "nonlinear": True,
+                               "diffuse_reflectance": {"type": "bitmap", "data": textures[0], "raw": True}})
+        d["wood_furniture"] = two({"type": "roughplastic", "alpha": 0.15, "distribution": "beckmann", "int_ior": 1.5, "ext_ior": 1.0, "nonlinear": True,
+                                   "diffuse_reflectance": {"type": "bitmap", "data": textures[1], "raw": True}})
+        d["mirror"] = two({"type": "conductor", "material": "none"})
+        d["lamp_metal"] = two({"type": "roughconductor", "distribution": "ggx", "alpha": 0.1, "eta": _AL_ETA, "k": _AL_K})
+        d["curtain_rod"] = two({"type": "roughconductor", "distribution": "ggx", "alpha": 0.1, "eta": _AL_ETA, "k": _AL_K,
+                                "specular_reflectance": {"type": "rgb", "value": [0.5, 0.5, 0.5]}})
+        d["lamp_glass"] = {"type": "roughdielectric", "alpha": 0.1, "distribution": "beckmann", "int_ior": 1.5, "ext_ior": 1.0}
+        d["curtains"] = {"type": "mask", "opacity": 0.531049, "nested": two({"type": "diffuse", "reflectance": {"type": "rgb", "value": [1, 1, 1]}})}
     def ref(n): return {"type": "ref", "id": n}
     # room shell x in [-2.6, 4], y in [0, 2.6], z in [-1.4, 4.2]; +x wall has a 1.2 x 1.2 window hole (y 0.9..2.1, z 0.8..2.0)
     X0, X1, Y0, Y1, Z0, Z1 = -2.6, 4.0, 0.0, 2.6, -1.4, 4.2
@@ -192,7 +210,7 @@ def bedroom_standin(width=1280, height=720, spp=64, n_tris=1_800_000, seed=1, en
         pos = np.stack([p0, p0 + e1, p0 + e1 + e2, p0 + e2]).astype(np.float32)
         uv = np.array([[0, 0], [1, 0], [1, 1], [0, 1]], np.float32) * 4.0
         d[name] = {"type": "mesh", "positions": pos, "texcoords": uv, "faces": np.array([[0, 1, 2], [0, 2, 3]], np.uint32), "bsdf": ref(bsdf)}
-    quad([X0, Y0, Z0], [X1 - X0, 0, 0], [0, 0, Z1 - Z0], "floor", "textured0")
+    quad([X0, Y0, Z0], [X1 - X0, 0, 0], [0, 0, Z1 - Z0], "floor", "wood_floor" if xml else "textured0")
     quad([X0, Y1, Z0], [0, 0, Z1 - Z0], [X1 - X0, 0, 0], "ceiling", "diffuse7")
     quad([X0, Y0, Z0], [0, Y1 - Y0, 0], [X1 - X0, 0, 0], "wall_back", "diffuse2")
     quad([X0, Y0, Z1], [X1 - X0, 0, 0], [0, Y1 - Y0, 0], "wall_front", "diffuse2")
@@ -218,12 +236,17 @@ def bedroom_standin(width=1280, height=720, spp=64, n_tris=1_800_000, seed=1, en
     mats = []
     for i in range(n_obj):
         u = (i * 0.6180339887 + 0.31) % 1.0
+        if xml:     # 34 BSDFs of the file: 22 diffuse, 4 rough conductor, 2 rough plastic, 2 conductor, 2 dielectric, 1 rough dielectric, 1 mask
+            mats.append(f"diffuse{i % len(_BEDROOM_ALBEDOS)}" if u < 0.56 else "wood_furniture" if u < 0.68 else
+                        ("metal_ggx", "lamp_metal", "metal_beckmann", "curtain_rod")[i % 4] if u < 0.80 else "mirror" if u < 0.86 else
+                        "glass" if u < 0.92 else "lamp_glass" if u < 0.96 else "curtains")
+            continue
         mats.append(f"diffuse{i % len(_BEDROOM_ALBEDOS)}" if u < 0.65 else (f"textured{i % 3}" if u < 0.75 else
                     (("metal_ggx" if i % 2 else "metal_beckmann") if u < 0.90 else "glass")))
     # placement on a jittered grid over the floor, away from the camera corner
     gx, gz = np.meshgrid(np.linspace(-2.0, 2.4, 7), np.linspace(-0.8, 2.6, 4), indexing="ij")
     slots = np.stack([gx.ravel(), gz.ravel()], 1)
-    order = rng.permutation(len(slots))[:n_obj]
+    order = np.resize(rng.permutation(len(slots)), n_obj)     # (more objects than slots only for tiny n_tris: slots are reused)
     for i, kind in enumerate(kinds):
         cx, cz = slots[order[i]] + rng.uniform(-0.12, 0.12, 2)
         rot = rng.uniform(0, 360)
@@ -276,10 +299,10 @@ def random_triangles(n_tris=10_000_000, width=1920, height=1080, spp=128, seed=3
 def woodfloor_texture() -> np.ndarray:
     """The reference's ``WoodFloor.jpg`` (960 x 870) as the fp32 linear-RGB tensor Mitsuba would hold for an optimised
     ``bitmap`` parameter (sRGB -> linear, bitmap.cpp:286-294; fp32 because it is a differentiable tensor, :208-218).
-    The pixels come from the committed fixture ``tests/golden/woodfloor_u8.npz`` (decoded from the reference checkout by
+    The pixels come from the package's data file ``data/woodfloor_u8.npz`` (decoded from the reference checkout by
     ``tests/golden/make_woodfloor.py``); without the fixture a procedural stand-in of the same shape is returned."""
     from .scene import srgb_to_linear
-    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "woodfloor_u8.npz")
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "woodfloor_u8.npz")
     if os.path.exists(path):
         rgb = np.load(path)["rgb"]
         return np.ascontiguousarray(srgb_to_linear(rgb.astype(np.float32) / np.float32(255.0)))

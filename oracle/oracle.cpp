@@ -116,7 +116,7 @@ struct Integrator {
         V3 L(0.f), f(1.f); float eta = 1.f; uint32_t depth = 1;
         bool active = depth < (uint32_t) max_depth;
         SI si = active ? sc.make_si(ray, sc.intersect(ray, c), c) : sc.make_si(ray, Hit{ 0, 0, 0, 0xffffffffu }, c);
-        L += em.eval(em.emitter_of(si), si, c);
+        if (active) L += em.eval(em.emitter_of(si), si, c);      // path.py:238-239: the emitter lookup and eval are masked by `active`
         while (active) {
             const b2_bsdf *bsdf = bsdf_of(si);
             bool active_em = active && bsdf && (bsdf_lobes(*bsdf) & LOBE_SMOOTH);
@@ -174,6 +174,9 @@ struct Integrator {
             V3 bsdf_val(0.f), bsdf_weight(0.f); float bsdf_pdf = 0.f; BS bs;
             // (eval_pdf is consumed only under active_em and the sample only when the loop continues: evaluated only there)
             if (bsdf) { if (active_em) bsdf_eval_pdf(sc, *bsdf, si, wo, bsdf_val, bsdf_pdf, false, c); if (active_next) bsdf_sample(sc, *bsdf, si, sample1, sample2, bs, bsdf_weight, c); }
+            // terminating iteration: the reference still samples the BSDF; only its sampled_type is consumed (valid_ray below),
+            // and only an opacity mask can return a null lobe (mask.cpp:123-160: sample1 >= opacity)
+            if (bsdf && !active_next && (bsdf->flags & B2_BSDF_FLAG_MASK) && !(sample1 < bsdf->opacity)) bs.type = LOBE_NULL;
             float mi_em = ds.delta ? 1.f : mis_weight_guard(ds.pdf, bsdf_pdf);
             if (active_em) result = fmadd(throughput, bsdf_val * em_weight * mi_em, result);
             if (si.valid) ray = Scene::spawn_ray(si.p, si.n, si.sh.to_world(bs.wo));

@@ -273,16 +273,81 @@ def test_prb_gradient_matches_finite_differences():
 
 
 def test_autograd_render_op():
+    """``render()`` (= mi.render, util.py:395-526) through torch.autograd: the gradient that reaches the parameter equals a
+    direct ``render_backward`` with grad_in = dLoss/dImage at ``seed_grad = sample_tea_32(seed, 1)[0]`` (util.py:504-509)."""
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
-    from mitsuba3_experiments_b200.integrator import PRBIntegrator, render, traverse
+    from mitsuba3_experiments_b200.integrator import PRBIntegrator, render, sample_tea_32, traverse
     ds = DeviceScene(cornell_box(24, 24, spp=8))
     params = traverse(ds); params.keep(["red.reflectance.value"])
     params["red.reflectance.value"].requires_grad_(True)
-    img = render(ds, params, integrator=PRBIntegrator({"max_depth": 4}), seed=0, spp=8)
+    integ = PRBIntegrator({"max_depth": 4})
+    img = render(ds, params, integrator=integ, seed=3, spp=8)
     loss = (img ** 2).mean()
     loss.backward()
     g = params["red.reflectance.value"].grad
     assert g is not None and torch.isfinite(g).all() and (g.abs() > 0).any()
+    # the same by hand
+    p2 = traverse(ds); p2.keep(["red.reflectance.value"])
+    primal = integ.render(ds, seed=3, spp=8)
+    assert torch.allclose(primal, img.detach(), rtol=2e-5, atol=1e-7)      # the film is summed with atomics: order varies
+    integ.render_backward(ds, p2, 2.0 * primal / primal.numel(), seed=sample_tea_32(3, 1)[0], spp=8)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(g.cpu().numpy(), p2.grad["red.reflectance.value"].cpu().numpy(), rtol=1e-5)
+    # and a different seed_grad gives a different (independent) estimate
+    p3 = traverse(ds); p3.keep(["red.reflectance.value"])
+    integ.render_backward(ds, p3, 2.0 * primal / primal.numel(), seed=3, spp=8)
+    torch.cuda.synchronize()
+    assert not np.allclose(g.cpu().numpy(), p3.grad["red.reflectance.value"].cpu().numpy(), rtol=1e-6)
+
+
+def test_prb_sample_shards_sum_to_the_full_gradient():
+    """The balanced multi-GPU split of the adjoint: render_backward on sample slices (b2_render_args.sample_begin / sample_count)
+    uses the weight film of the WHOLE sample set, so the shards' gradients add up to the single-call gradient."""
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    from mitsuba3_experiments_b200.integrator import PRBIntegrator, traverse
+    d = cornell_box(48, 48, spp=16)
+    rng = np.random.RandomState(0)
+    d["white"] = {"type": "diffuse", "reflectance": {"type": "bitmap", "data": rng.uniform(0.2, 0.9, (24, 32, 3)).astype(np.float32), "raw": True}}
+    ds = DeviceScene(d)
+    grad_in = torch.from_numpy(np.random.RandomState(1).normal(size=(48, 48, 3)).astype(np.float32) / (48 * 48 * 3))
+    keys = ["white.reflectance.data", "green.reflectance.value"]
+    prb = PRBIntegrator({"max_depth": 6, "rr_depth": 3})
+    full = traverse(ds); full.keep(keys)
+    prb.render_backward(ds, full, grad_in, seed=7, spp=16)
+    parts = traverse(ds); parts.keep(keys)
+    for r in range(4):
+        prb.render_backward(ds, parts, grad_in, seed=7, spp=16, sample_begin=4 * r, sample_count=4)
+    torch.cuda.synchronize()
+    for k in keys:
+        a, b = parts.grad[k].cpu().numpy(), full.grad[k].cpu().numpy()
+        assert np.abs(a - b).max() <= 1e-5 * np.abs(b).max(), (k, np.abs(a - b).max(), np.abs(b).max())
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_max_depth_one_edge_cases(kernel):
+    """path.py:235-239 masks the first intersection AND the primary emission with depth < max_depth: Path(max_depth = 1) is black,
+    also under an environment map and on a multi-class scene (no class bytes exist when the first trace is skipped).
+    path-mis.py:129-133 on its terminating iteration still samples the BSDF for valid_ray: an opacity mask reached at the last
+    depth without an environment keeps the sample with probability `opacity` only."""
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    from scenes_for_tests import mirror_scene
+    ds = DeviceScene(materials_scene(32, 24, 8, envmap=True, filter_type="box")); orc = OracleScene(ds.desc)
+    kw = dict(seed=1, spp=8, max_depth=1, rr_depth=3, variant=0)
+    img, cnt = ds.render(counters=True, kernel=kernel, **kw)
+    ref, rc = orc.render(**kw)
+    assert float(np.abs(img.cpu().numpy()).max()) == 0.0 and float(np.abs(ref).max()) == 0.0
+    assert cnt["closest_rays"] == rc["closest_rays"] == 0 and cnt["samples"] == 32 * 24 * 8
+    # mask at the final depth, no environment emitter: an emissive masked rectangle fills the view
+    d = mirror_scene(16, 16, 64, opacity=0.3); del d["env"]
+    d["plane"]["emitter"] = {"type": "area", "radiance": {"type": "rgb", "value": [2.0, 3.0, 4.0]}}
+    d["m"] = {"type": "mask", "opacity": 0.3, "nested": {"type": "twosided", "nested": {"type": "diffuse", "reflectance": {"type": "rgb", "value": [0.5, 0.5, 0.5]}}}}
+    dm = DeviceScene(d); om = OracleScene(dm.desc)
+    kw = dict(seed=2, spp=64, max_depth=1, rr_depth=3, variant=1)
+    img, _ = dm.render(kernel=kernel, **kw)
+    ref, _ = om.render(**kw)
+    check_image(img.cpu().numpy(), ref, 0.999, 1e-4)
+    m = img.cpu().numpy().mean(axis=(0, 1))
+    assert np.allclose(m, 0.3 * np.array([2.0, 3.0, 4.0]), rtol=0.08), m       # E[valid_ray] = opacity
 
 
 @pytest.mark.parametrize("kernel", KERNELS)
