@@ -171,16 +171,8 @@ class B2Integrator:
             return scene
         if isinstance(scene, (dict, SceneDesc)):
             return DeviceScene(scene)
-        cached = getattr(scene, "_b2_device_scene", None)
-        if cached is not None:
-            return cached
-        from .mitsuba_bridge import scene_to_dict   # live mi.Scene (only reachable when Mitsuba is installed)
-        ds = DeviceScene(scene_to_dict(scene))
-        try:
-            scene._b2_device_scene = ds
-        except Exception:
-            pass
-        return ds
+        from .mitsuba_bridge import device_scene_for    # live mi.Scene (only reachable when Mitsuba is installed): cached per scene,
+        return device_scene_for(scene)                  # reflectance parameters re-read on every call
 
     def _args(self, scene: DeviceScene, seed, spp, **kw):
         return dict(seed=seed, spp=spp or scene.desc.spp, max_depth=self.max_depth, rr_depth=self.rr_depth,

@@ -1,9 +1,3 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/pytest_gpu2.log; tail -3 gpurun_out/pytest_gpu2.log
-(
-echo "== greedy"; B2_BVH_COLLAPSE=greedy python tools/profile_render.py bedroom 3 64
-for cp in 0.2 0.3 0.45 0.7; do echo "== dp c_prim=$cp"; B2_BVH_CPRIM=$cp python tools/profile_render.py bedroom 3 64; done
-echo "== tris greedy"; B2_BVH_COLLAPSE=greedy python tools/profile_render.py tris 2 8
-echo "== tris dp"; python tools/profile_render.py tris 2 8
-echo "== e2e"; python tools/diag_e2e.py
-) > gpurun_out/sweep2.log 2>&1
-grep -E "==|launch 2|launch 1|wall" gpurun_out/sweep2.log
+# sweep of the trace kernel's vote / refill thresholds on the bedroom workload
+for r in 4 8 12 16 24; do echo "refill=$r tri=10 $(B2_REFILL_THRESH=$r B2_TRI_THRESH=10 python tools/profile_render.py bedroom 3 64 2>&1 | grep 'launch 2')"; done
+for t in 6 14 18 24; do echo "refill=12 tri=$t $(B2_REFILL_THRESH=12 B2_TRI_THRESH=$t python tools/profile_render.py bedroom 3 64 2>&1 | grep 'launch 2')"; done
