@@ -340,6 +340,7 @@ int orc_render(void *hp, const b2_render_args *a, float *film_rgbw, b2_counters 
     if (a->sample_count) { g_err = "the oracle renders whole pixels only (sample shards are a product-side split)"; return -2; }
     uint64_t lb = a->lane_begin, le = a->lane_end ? a->lane_end : wavefront;
     Film film(s); Integrator integ(h->scene, a->max_depth, a->rr_depth);
+    integ.em.env_warp = a->env_warp;
     Counters total;
 #pragma omp parallel
     {
@@ -577,6 +578,7 @@ void orc_texture_eval(const b2_texture *t, float u, float v, float *out3, uint32
 }
 void orc_env_sample(const b2_envmap *e, float u, float v, float *out3) { float pdf; V2 r = warp_sample(*e, V2{ u, v }, pdf); out3[0] = r.x; out3[1] = r.y; out3[2] = pdf; }
 float orc_env_warp_eval(const b2_envmap *e, float u, float v) { return warp_eval(*e, V2{ u, v }); }
+void orc_env_alias_sample(const b2_envmap *e, float u, float v, float *out3) { float pdf; V2 r = alias_sample(*e, V2{ u, v }, pdf); out3[0] = r.x; out3[1] = r.y; out3[2] = pdf; }
 void orc_env_eval_dir(const b2_envmap *e, const float *dir, float *out3) { V3 r = env_eval_dir(*e, V3(dir[0], dir[1], dir[2])); out3[0] = r.x; out3[1] = r.y; out3[2] = r.z; }
 // surface interaction of one ray against the scene (a5/a7 pins): out = valid,t,p3,n3,uv2,dp_du3,dp_dv3,sh_n3,wi3, prim_uv2, face
 void orc_surface_interaction(void *hp, const float *ray7, float *out) {

@@ -42,6 +42,7 @@ def lib():
         l.orc_fresnel.argtypes = [C.c_float, C.c_float, vp]; l.orc_fresnel.restype = None
         l.orc_env_warp_eval.argtypes = [C.POINTER(capi.Envmap), C.c_float, C.c_float]; l.orc_env_warp_eval.restype = C.c_float
         l.orc_env_sample.argtypes = [C.POINTER(capi.Envmap), C.c_float, C.c_float, vp]; l.orc_env_sample.restype = None
+        l.orc_env_alias_sample.argtypes = [C.POINTER(capi.Envmap), C.c_float, C.c_float, vp]; l.orc_env_alias_sample.restype = None
         l.orc_env_eval_dir.argtypes = [C.POINTER(capi.Envmap), vp, vp]; l.orc_env_eval_dir.restype = None
         l.orc_camera_ray.argtypes = [C.POINTER(capi.Sensor), C.c_float, C.c_float, vp]; l.orc_camera_ray.restype = None
         l.orc_warp.argtypes = [C.c_int, vp, vp]; l.orc_warp.restype = None
@@ -80,12 +81,13 @@ class OracleScene:
         if getattr(self, "h", None):
             lib().orc_scene_destroy(self.h); self.h = None
 
-    def make_args(self, seed=0, spp=None, max_depth=8, rr_depth=4, variant=0, spp_per_pass=0, lane_begin=0, lane_end=0, kernel=0, all_shadow_rays=False):
+    def make_args(self, seed=0, spp=None, max_depth=8, rr_depth=4, variant=0, spp_per_pass=0, lane_begin=0, lane_end=0, kernel=0, all_shadow_rays=False, env_warp=0):
         from mitsuba3_experiments_b200 import capi
         a = capi.RenderArgs()
         a.seed, a.spp, a.spp_per_pass = seed, spp or self.desc.spp, spp_per_pass
         a.max_depth, a.rr_depth, a.variant = max_depth, rr_depth, variant
         a.lane_begin, a.lane_end = lane_begin, lane_end
+        a.env_warp = env_warp
         return a
 
     def render_film(self, **kw):

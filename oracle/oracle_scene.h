@@ -787,6 +787,27 @@ static inline V2 warp_sample(const b2_envmap &e, V2 sample, float &pdf) {
     float psx = 1.f / (float) (e.width - 1), psy = 1.f / (float) (e.height - 1);
     return V2{ ((float) (int) ox + sample.x) * psx, ((float) (int) oy + sample.y) * psy };
 }
+// Alias-table mode (NOT in the reference, which only has Hierarchical2D; north_star asks for alias tables): restates the product's
+// alias_sample (b2_shade.cuh) so that the mode has a per-sample checker too.  The patch is drawn from a Vose table over the patch
+// masses, the position inside it by the same square_to_bilinear; the density is warp_eval's, which the chi^2 test of
+// tests/test_oracle_golden.py checks (style of mitsuba3/src/core/tests/test_distr_2d.py:test04).
+static inline V2 alias_sample(const b2_envmap &e, V2 sample, float &pdf) {
+    const uint32_t pw = (uint32_t) e.width - 1u, ph = (uint32_t) e.height - 1u, n = pw * ph;
+    sample.x = clipf(sample.x, 0.f, 1.f); sample.y = clipf(sample.y, 0.f, 1.f);
+    const float scaled = sample.x * (float) n;
+    uint32_t bin = std::min((uint32_t) scaled, n - 1u);
+    float u = scaled - (float) bin;
+    const float q = e.alias_prob[bin];
+    if (u < q) u = u / q;
+    else { u = (u - q) / (1.f - q); bin = e.alias_idx[bin]; }
+    u = clipf(u, 0.f, 1.f);
+    const uint32_t oy = bin / pw, ox = bin - oy * pw;
+    const float *l0 = e.warp_data + e.level_offset[0]; const uint32_t w0 = e.level_width[0];
+    const uint32_t i = ox + oy * w0;
+    V2 s = square_to_bilinear(l0[i], l0[i + 1], l0[i + w0], l0[i + w0 + 1], V2{ u, sample.y }, pdf);
+    const float psx = 1.f / (float) pw, psy = 1.f / (float) ph;
+    return V2{ ((float) (int) ox + s.x) * psx, ((float) (int) oy + s.y) * psy };
+}
 // Hierarchical2D::eval (distr_2d.h:695-726)
 static inline float warp_eval(const b2_envmap &e, V2 pos) {
     pos.x = clipf(pos.x, 0.f, 1.f); pos.y = clipf(pos.y, 0.f, 1.f);
@@ -800,6 +821,7 @@ static inline float warp_eval(const b2_envmap &e, V2 pos) {
 
 struct EmitterSys {
     const Scene &sc;
+    int env_warp = B2_ENV_WARP_HIERARCHICAL;          // B2_ENV_WARP_ALIAS: the product's fast mode (see alias_sample)
     EmitterSys(const Scene &s) : sc(s) {}
     const b2_scene_desc &d() const { return *sc.d; }
 
@@ -859,7 +881,7 @@ struct EmitterSys {
         } else if (e.type == B2_EMITTER_ENVMAP) {
             c.nee_env++;
             const b2_envmap &env = *d().envmap;
-            float pdf; V2 uv = warp_sample(env, sample, pdf);
+            float pdf; V2 uv = (env_warp == B2_ENV_WARP_ALIAS && env.alias_prob) ? alias_sample(env, sample, pdf) : warp_sample(env, sample, pdf);
             uv.x += .5f / (float) (env.width - 1);
             bool active = pdf > 0.f;
             float theta = uv.y * Pi, phi = uv.x * TwoPi;

@@ -150,6 +150,23 @@ def test_wavefront_equals_megakernel(variant):
     np.testing.assert_allclose(c.cpu().numpy(), d.cpu().numpy(), rtol=2e-5, atol=1e-6)
 
 
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_envmap_alias_mode_parity_with_the_oracle(kernel):
+    """The alias-table envmap mode against the oracle's restatement of it (oracle_scene.h alias_sample; the density is pinned by the
+    chi^2 test of tests/test_oracle_golden.py): same seeds => same image, same event counters."""
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    from mitsuba3_experiments_b200 import capi
+    ds = DeviceScene(materials_scene(64, 48, 16, envmap=True, filter_type="gaussian")); orc = OracleScene(ds.desc)
+    kw = dict(seed=4, spp=16, max_depth=6, rr_depth=3, variant=1, env_warp=capi.ENV_WARP_ALIAS)
+    img, cnt = ds.render(counters=True, kernel=kernel, all_shadow_rays=True, **kw)
+    ref, rc = orc.render(**kw)
+    check_image(img.cpu().numpy(), ref, 0.99, 2e-3)
+    for k in ("closest_rays", "shadow_rays", "vertices", "nee_env", "env_escapes"):
+        assert abs(cnt[k] - rc[k]) <= 2e-3 * max(rc[k], 1) + 2, (k, cnt[k], rc[k])
+    hier, _ = ds.render(kernel=kernel, **dict(kw, env_warp=capi.ENV_WARP_HIERARCHICAL))
+    assert not np.array_equal(hier.cpu().numpy(), img.cpu().numpy())      # a different sample -> direction map
+
+
 def test_envmap_alias_table_matches_hierarchical_in_expectation():
     """Fast envmap mode: a different (u1, u2) -> direction map with the SAME density, so only the converged image agrees
     (SURVEY.md section 0 fact 9).  1024 spp: mean relative difference of the two estimates <= 1.5 %, no bias in the mean."""
