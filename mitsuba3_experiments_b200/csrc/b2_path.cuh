@@ -253,7 +253,6 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
     const DBsdf &bsdf = sc.bsdfs[si.bsdf];
     ReflCache rc;
     auto refl = [&]() { return reflectance<CLS>(sc, bsdf, si, rc, cnt); };
-    auto ones = []() { return f3(1.f); };
     bool active_em = (bsdf_lobes<CLS>(bsdf) & LOBE_SMOOTH) != 0;
     DS ds; f3 em_weight;
     sample_emitter_direction(sc, si, s.rng.next_2d(), active_em, p.env_warp, ds, em_weight, cnt, [&](const Ray &sr) {
@@ -325,19 +324,19 @@ B2_DEV bool path_step(const RenderParams &p, Path &s, const GradSink &gs, Counte
         const bool rr_continue = s.rng.next_1d() < rr_prob;
         active = beta_max != 0.f && (!rr_active || rr_continue);                            // prb.py:188-200
         if (ADJ) {
-            // d/d(reflectance) of [ Lr_dir + L * bsdf_val / detach(bsdf_weight * pdf) ] (prb.py:202-250); every
-            // supported BSDF is linear in its reflectance, so the derivative is the value with reflectance := 1.
+            // d/d(reflectance) of [ Lr_dir + L * bsdf_val / detach(bsdf_weight * pdf) ] (prb.py:202-250): bsdf_eval_pdf in
+            // derivative mode (value at reflectance := 1 for the linear BSDFs, the closed form for rough plastic).
             // forward mode (render_forward, common.py:495-621): the same coefficient with dL := 1, contracted with the
             // parameter tangent at this vertex and accumulated in s.dL (the lane's d L, splatted after the replay)
             const f3 dLw = B2_FWD(p) ? f3(1.f) : s.dL;
             f3 g(0.f);
             if (active_em) {
-                f3 unit; float dummy; bsdf_eval_pdf<CLS>(bsdf, si.wi, wo, ones, unit, dummy);
+                f3 unit; float dummy; bsdf_eval_pdf<CLS>(bsdf, si.wi, wo, refl, unit, dummy, true);
                 g += dLw * (f_before * mis_em * unit * em_weight);
             }
             if (active) {
                 const f3 wo2 = si.sh.to_local(s.ray.d);
-                f3 unit; float dummy; bsdf_eval_pdf<CLS>(bsdf, si.wi, wo2, ones, unit, dummy);
+                f3 unit; float dummy; bsdf_eval_pdf<CLS>(bsdf, si.wi, wo2, refl, unit, dummy, true);
                 const f3 det = bsdf_weight * bs.pdf;
                 const f3 inv(det.x != 0.f ? rcp(det.x) : 0.f, det.y != 0.f ? rcp(det.y) : 0.f, det.z != 0.f ? rcp(det.z) : 0.f);
                 g += dLw * (s.L * (inv * unit));

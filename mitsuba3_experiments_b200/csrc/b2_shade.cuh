@@ -292,7 +292,7 @@ B2_DEV float lerp_gather(const float *__restrict__ data, float x, int size) {
 }
 // RoughPlastic::eval / pdf (roughplastic.cpp:301-341, 353-393); wi.z > 0 and wo.z > 0 are the caller's precondition
 template <class RF>
-B2_DEV void roughplastic_eval_pdf(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &val, float &pdf) {
+B2_DEV void roughplastic_eval_pdf(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &val, float &pdf, bool deriv = false) {
     const float ci = wi.z, co = wo.z;
     const Microfacet distr(b.distribution, b.alpha_u, b.alpha_u, b.sample_visible != 0);
     const f3 H = normalize(wo + wi);
@@ -302,9 +302,13 @@ B2_DEV void roughplastic_eval_pdf(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &v
     const f3 value = f3(F * D * G / (4.f * ci)) * f3(b.trans[0], b.trans[1], b.trans[2]);      // specular_reflectance
     const float t_i = lerp_gather(b.rough_table, ci, 64), t_o = lerp_gather(b.rough_table, co, 64);
     f3 diff = refl();
-    diff = diff / (f3(1.f) - (b.nonlinear ? diff * b.int_refl : f3(b.int_refl)));
+    if (deriv) {
+        // d/d rho of rho / (1 - rho r) = 1 / (1 - rho r)^2 (nonlinear), of rho / (1 - r) = 1 / (1 - r); the specular lobe does not depend on rho
+        const f3 den = f3(1.f) - (b.nonlinear ? diff * b.int_refl : f3(b.int_refl));
+        diff = b.nonlinear ? f3(1.f) / (den * den) : f3(1.f) / den;
+    } else diff = diff / (f3(1.f) - (b.nonlinear ? diff * b.int_refl : f3(b.int_refl)));
     const float inv_eta_2 = 1.f / (b.ior * b.ior);
-    val = value + diff * (kInvPi * inv_eta_2 * co * t_i * t_o);
+    val = (deriv ? f3(0.f) : value) + diff * (kInvPi * inv_eta_2 * co * t_i * t_o);
     float prob_specular = (1.f - t_i) * b.spec_weight, prob_diffuse = t_i * (1.f - b.spec_weight);
     prob_specular = prob_specular / (prob_specular + prob_diffuse); prob_diffuse = 1.f - prob_specular;
     float r = b.sample_visible ? D * distr.smith_g1(wi, H) / (4.f * ci) : distr.pdf(wi, H) / (4.f * dot(wo, H));
@@ -314,16 +318,18 @@ B2_DEV void roughplastic_eval_pdf(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &v
 }
 
 // eval_pdf.  `refl()` yields the (possibly textured) reflectance at si and is invoked exactly where the reference
-// evaluates it; pass a functor returning f3(1) to obtain the linear coefficient d value / d reflectance (PRB adjoint).
+// evaluates it.  deriv = true returns d value / d reflectance per channel instead of the value (PRB adjoint, prb.py:202-250): the
+// value at reflectance := 1 for the BSDFs that are linear in it (diffuse, rough conductor, the reflection lobe of the rough
+// dielectric -- its transmission lobe does not depend on specular_reflectance), the closed form for rough plastic.
 template <int CLS = CLS_GENERIC, class RF>
-B2_DEV void bsdf_eval_pdf_nested(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &val, float &pdf) {
+B2_DEV void bsdf_eval_pdf_nested(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &val, float &pdf, bool deriv = false) {
     val = f3(0.f); pdf = 0.f;
     if (b.flags & B2_BSDF_FLAG_TWOSIDED) { wo.z = mulsign(wo.z, wi.z); wi.z = fabsf(wi.z); }
     const float ci = wi.z, co = wo.z;
     const int type = cls_type<CLS>(b.type);
     if (type == B2_BSDF_DIFFUSE) {
         if (!(ci > 0.f && co > 0.f)) return;
-        val = refl() * kInvPi * co;
+        val = (deriv ? f3(1.f) : refl()) * kInvPi * co;
         pdf = kInvPi * co;
     } else if (type == B2_BSDF_ROUGHCONDUCTOR) {
         const f3 H = normalize(wo + wi);
@@ -333,12 +339,12 @@ B2_DEV void bsdf_eval_pdf_nested(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &va
         const float g1_wi = distr.smith_g1(wi, H), G = g1_wi * distr.smith_g1(wo, H);
         const float value = D * G / (4.f * ci);
         const f3 F = fresnel_conductor3(dot(wi, H), b);
-        const f3 v = f3(value) * refl();
+        const f3 v = f3(value) * (deriv ? f3(1.f) : refl());
         const float p = b.sample_visible ? D * g1_wi / (4.f * ci) : distr.pdf(wi, H) / (4.f * dot(wo, H));
         if (D != 0.f) { val = F * v; pdf = p; }
     } else if (type == B2_BSDF_ROUGHPLASTIC) {
         if (!(ci > 0.f && co > 0.f)) return;
-        roughplastic_eval_pdf(b, wi, wo, refl, val, pdf);
+        roughplastic_eval_pdf(b, wi, wo, refl, val, pdf, deriv);
     } else if (type == B2_BSDF_ROUGHDIELECTRIC) {
         // RoughDielectric::eval_pdf (roughdielectric.cpp:503-605)
         if (ci == 0.f) return;
@@ -354,11 +360,11 @@ B2_DEV void bsdf_eval_pdf_nested(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &va
         const float G = distr.G(wi, wo, m);
         if (reflect) {
             val = f3(F * D * G / (4.f * fabsf(ci)));
-            val = val * refl();
+            val = val * (deriv ? f3(1.f) : refl());
         } else {
             const float scale = sqr(inv_eta);
             val = f3(fabsf((scale * (1.f - F) * D * G * eta * eta * dwi * dwo) / (ci * sqr(dwi + eta * dwo))));
-            val = val * f3(b.trans[0], b.trans[1], b.trans[2]);
+            val = deriv ? f3(0.f) : val * f3(b.trans[0], b.trans[1], b.trans[2]);
         }
         if (!b.sample_visible) distr.scale_alpha(1.2f - .2f * sqrtf(fabsf(ci)));
         float p = distr.pdf(ci < 0.f ? -wi : wi, m);
@@ -370,8 +376,8 @@ B2_DEV void bsdf_eval_pdf_nested(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &va
 
 // OpacityMask::eval_pdf (mask.cpp:196-215): nested value and pdf scaled by the opacity
 template <int CLS = CLS_GENERIC, class RF>
-B2_DEV void bsdf_eval_pdf(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &val, float &pdf) {
-    bsdf_eval_pdf_nested<CLS>(b, wi, wo, refl, val, pdf);
+B2_DEV void bsdf_eval_pdf(const DBsdf &b, f3 wi, f3 wo, RF &&refl, f3 &val, float &pdf, bool deriv = false) {
+    bsdf_eval_pdf_nested<CLS>(b, wi, wo, refl, val, pdf, deriv);
     if (b.flags & B2_BSDF_FLAG_MASK) { val = val * b.opacity; pdf *= b.opacity; }
 }
 

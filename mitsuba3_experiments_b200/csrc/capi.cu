@@ -271,6 +271,13 @@ int b2_scene_set_param(b2_scene *s, const char *key, const void *dev_ptr, size_t
     if (!s || !key || !dev_ptr) return fail(-1, "b2_scene_set_param: null argument");
     CUDA_OK(cudaSetDevice(s->ctx->device));
     int idx = -1; char what[32] = { 0 };
+    if (std::sscanf(key, "%d.spec_sampling_weigh%1s", &idx, what) == 2 && idx >= 0 && idx < (int) s->bsdfs.size()) {
+        // RoughPlastic::parameters_changed (roughplastic.cpp:216-238) re-derives the lobe sampling weight from the texture means;
+        // the caller passes the new value after it changed the diffuse reflectance
+        if (bytes != sizeof(float) || s->bsdfs[idx].type != B2_BSDF_ROUGHPLASTIC) return fail(-2, "b2_scene_set_param: spec_sampling_weight is one float of a rough plastic BSDF");
+        CUDA_OK(cudaMemcpyAsync(&s->bsdfs_dev[idx].spec_weight, dev_ptr, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t) stream));
+        return 0;
+    }
     if (std::sscanf(key, "%d.reflectance.%31s", &idx, what) != 2 || idx < 0 || idx >= (int) s->bsdfs.size())
         return fail(-2, std::string("b2_scene_set_param: unknown key '") + key + "'");
     if (!std::strcmp(what, "value")) {
@@ -442,12 +449,13 @@ int b2_develop(b2_scene *s, const float *film, float *image, uintptr_t stream) {
     return 0;
 }
 
-// PRB differentiates through f(reflectance) with "value at reflectance := 1" (b2_path.cuh): valid for BSDFs that are linear in
-// the reflectance slot and carry it on every lobe -- diffuse and rough conductor
+// PRB differentiates d value / d reflectance in closed form (b2_shade.cuh, bsdf_eval_pdf in derivative mode): diffuse.reflectance,
+// roughconductor.specular_reflectance, roughplastic.diffuse_reflectance (linear and nonlinear, roughplastic.cpp:315-367) and
+// roughdielectric.specular_reflectance.  Delta lobes have no eval() and are not targets (detached PRB yields no gradient for them).
 static int check_grad_target(const b2_scene *s, const b2_grad_target &g, const char *who) {
     const int t = s->bsdfs[g.bsdf].type;
-    if (t == B2_BSDF_DIFFUSE || t == B2_BSDF_ROUGHCONDUCTOR) return 0;
-    return fail(-2, std::string(who) + ": the reflectance of this BSDF type (delta lobes, rough dielectric, rough plastic) is not a supported target");
+    if (t == B2_BSDF_DIFFUSE || t == B2_BSDF_ROUGHCONDUCTOR || t == B2_BSDF_ROUGHPLASTIC || t == B2_BSDF_ROUGHDIELECTRIC) return 0;
+    return fail(-2, std::string(who) + ": the reflectance of a delta BSDF (conductor, dielectric) is not a differentiable target");
 }
 
 int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_in, const b2_grad_target *targets, int n_targets,

@@ -47,17 +47,22 @@ class SceneParameters(dict):
         self.tangent: dict[str, "torch.Tensor"] = {}      # forward mode: d(param), see set_tangent / render_forward
         self._index: dict[str, tuple[int, str]] = {}
         d = scene.desc
+        # the differentiable reflectance slot of every BSDF type, under the name its plugin registers (diffuse.cpp:97,
+        # roughconductor.cpp:214, roughplastic.cpp:209, roughdielectric.cpp:232); delta BSDFs have no eval() and no PRB gradient
+        slots = {capi.BSDF_DIFFUSE: "reflectance", capi.BSDF_ROUGHCONDUCTOR: "reflectance", capi.BSDF_ROUGHPLASTIC: "diffuse_reflectance",
+                 capi.BSDF_ROUGHDIELECTRIC: "specular_reflectance"}
         for i, (name, b) in enumerate(zip(d.bsdf_names, d.bsdfs)):
-            if b.type not in (capi.BSDF_DIFFUSE, capi.BSDF_ROUGHCONDUCTOR):
-                continue                              # PRB differentiates reflectances that scale every lobe linearly
+            if b.type not in slots:
+                continue
+            slot = slots[b.type]
             if b.reflectance_tex >= 0:
                 arr = d.texture_arrays[b.reflectance_tex]
                 if arr.dtype != np.float32:
                     continue                          # fp16 storage is not a differentiable parameter (bitmap.cpp:208-218)
-                key, val = f"{name}.reflectance.data", torch.from_numpy(arr.copy())
+                key, val = f"{name}.{slot}.data", torch.from_numpy(arr.copy())
                 self._index[key] = (i, "data")
             else:
-                key, val = f"{name}.reflectance.value", torch.tensor(list(b.reflectance), dtype=torch.float32)
+                key, val = f"{name}.{slot}.value", torch.tensor(list(b.reflectance), dtype=torch.float32)
                 self._index[key] = (i, "value")
             super().__setitem__(key, val.to(scene.device))
 

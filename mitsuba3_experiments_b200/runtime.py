@@ -182,6 +182,15 @@ class DeviceScene:
 
     def set_param(self, bsdf_index: int, what: str, value):
         """what = 'value' (3 floats) | 'data' ([H, W, 3] fp32 texture)."""
-        t = as_device_tensor(value, self.device, _torch().float32)
+        torch = _torch()
+        t = as_device_tensor(value, self.device, torch.float32)
         key = f"{int(bsdf_index)}.reflectance.{what}".encode()
         capi.check(self.lib.b2_scene_set_param(self.handle, key, t.data_ptr(), t.numel() * 4, self._stream()))
+        b = self.desc.bsdfs[int(bsdf_index)]
+        if b.type == capi.BSDF_ROUGHPLASTIC:
+            # RoughPlastic::parameters_changed (roughplastic.cpp:216-238): the specular sampling weight follows the texture means
+            # (bitmap: mean luminance, bitmap.cpp:829-853; rgb: mean of the channels, srgb.cpp:117-122)
+            d_mean = (t.reshape(-1, 3) @ torch.tensor([0.212671, 0.715160, 0.072169], device=self.device)).mean() if what == "data" else t.mean()
+            s_mean = float(np.mean(np.asarray(b.transmittance[:], np.float32)))
+            w = (s_mean / (d_mean + s_mean)).to(torch.float32).reshape(1).contiguous()
+            capi.check(self.lib.b2_scene_set_param(self.handle, f"{int(bsdf_index)}.spec_sampling_weight".encode(), w.data_ptr(), 4, self._stream()))

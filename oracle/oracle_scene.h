@@ -548,8 +548,14 @@ static inline void roughplastic_eval_pdf(const Scene &sc, const b2_bsdf &b, cons
     const float G = distr.G(si.wi, wo, H);
     V3 value = V3(F * D * G / (4.f * ci)) * V3(b.transmittance[0], b.transmittance[1], b.transmittance[2]);   // specular_reflectance
     const float t_i = lerp_gather(tab.trans, ci, kRoughRes), t_o = lerp_gather(tab.trans, co, kRoughRes);
-    V3 diff = unit ? V3(1.f) : sc.reflectance(b, si, c);
-    diff = diff / (V3(1.f) - (b.nonlinear ? diff * tab.internal_reflectance : V3(tab.internal_reflectance)));
+    // unit = derivative mode (PRB adjoint): d/d rho of rho / (1 - rho r) = 1 / (1 - rho r)^2 (nonlinear), of rho / (1 - r) = 1 / (1 - r);
+    // the specular lobe does not depend on the diffuse reflectance
+    V3 diff = sc.reflectance(b, si, c);
+    if (unit) {
+        V3 den = V3(1.f) - (b.nonlinear ? diff * tab.internal_reflectance : V3(tab.internal_reflectance));
+        diff = b.nonlinear ? V3(1.f) / (den * den) : V3(1.f) / den;
+        value = V3(0.f);
+    } else diff = diff / (V3(1.f) - (b.nonlinear ? diff * tab.internal_reflectance : V3(tab.internal_reflectance)));
     const float inv_eta_2 = 1.f / (b.ior * b.ior);
     val = value + diff * (InvPi * inv_eta_2 * co * t_i * t_o);
     float prob_specular = (1.f - t_i) * b.spec_sampling_weight, prob_diffuse = t_i * (1.f - b.spec_sampling_weight);
@@ -609,7 +615,7 @@ static inline void bsdf_eval_pdf_nested(const Scene &sc, const b2_bsdf &b, const
         } else {
             const float scale = sqr(inv_eta);
             val = V3(fabsf((scale * (1.f - F) * D * G * eta * eta * dwi * dwo) / (ci * sqr(dwi + eta * dwo))));
-            val = val * V3(b.transmittance[0], b.transmittance[1], b.transmittance[2]);
+            val = unit ? V3(0.f) : val * V3(b.transmittance[0], b.transmittance[1], b.transmittance[2]);   // (no dependence on specular_reflectance)
         }
         if (!b.sample_visible) distr.scale_alpha(1.2f - .2f * sqrtf(fabsf(ci)));
         float p = distr.pdf(ci < 0.f ? -si.wi : si.wi, m);
