@@ -28,6 +28,7 @@
  *   b2_render_forward      <- RBIntegrator.render_forward  (mi3/src/python/python/ad/integrators/common.py:495-621)
  *   b2_kernel_times        <- dr.kernel_history() as printed by path.py:332-351
  *   b2_trace               <- Scene::ray_intersect_preliminary / ray_test (mi3/src/render/scene.cpp:191-235)
+ *   b2_debug_sampler       <- PCG32Sampler::seed + next_1d (mi3/src/render/sampler.cpp:129-148, samplers/independent.cpp:88-97)
  */
 #ifndef B2PATH_H
 #define B2PATH_H
@@ -244,8 +245,16 @@ int  b2_render_backward(b2_scene *scene, const b2_render_args *args, const float
    film_rgbw_dev (accumulated, like b2_render); b2_develop of that film is the gradient image. */
 int  b2_render_forward(b2_scene *scene, const b2_render_args *args, const b2_grad_target *tangents, int n_targets,
                        float *film_rgbw_dev, uintptr_t stream, b2_counters *counters);
-/* unit-test hook: rays_dev [n][8] = o.xyz, d.xyz, tmax, unused */
+/* unit-test hook: rays_dev [n][8] = o.xyz, d.xyz, tmax, unused.  any_hit bit 0: arrival test (Scene::ray_test) instead of the closest
+   hit; bit 1: trace with the megakernel's per-thread traversal instead of the wavefront trace kernel (the product default). */
 int  b2_trace(b2_scene *scene, const float *rays_dev, uint64_t n, int any_hit, b2_hit *hits_dev, uintptr_t stream);
+/* unit-test hook for the sampler (integer work, must be bit exact): out_dev [n_lanes][n_draws] = the first n_draws
+   next_float32() of lanes lane_begin .. lane_begin + n_lanes - 1, seeded exactly as the render kernels seed them
+   (PCG32Sampler::seed, sampler.cpp:129-148: TEA(seed, lane) -> PCG32, drjit random.h:60-79,211-213); the primary-ray
+   position of every lane (the first two draws through lane -> pixel, integrator.cpp:293-310) goes to pos_dev [n_lanes][2]
+   when it is not NULL.  `args` supplies seed / spp (lane -> pixel); nothing is rendered. */
+int  b2_debug_sampler(b2_scene *scene, const b2_render_args *args, uint64_t lane_begin, uint32_t n_lanes, uint32_t n_draws,
+                      float *out_dev, float *pos_dev, uintptr_t stream);
 /* host-buffer convenience entry points (what a reference-side binding with host arrays calls):
    upload/download happen inside; film_rgbw_host is accumulated into */
 int  b2_render_host(b2_scene *scene, const b2_render_args *args, float *film_rgbw_host, float *image_rgb_host, b2_counters *counters);

@@ -39,6 +39,7 @@ struct RenderParams {
 void launch_render(int variant, int mode, bool count, const RenderParams &p, int blocks, size_t smem, cudaStream_t st);
 int render_occupancy(int variant, int mode, bool count, size_t smem);
 void launch_develop(const float *film, float *image, uint32_t n_pixels, cudaStream_t st);
+void launch_debug_sampler(const RenderParams &p, uint64_t lane_begin, uint32_t n_lanes, uint32_t n_draws, float *out, float *pos, cudaStream_t st);
 void launch_trace(const DScene &sc, const float *rays, uint64_t n, int any_hit, b2_hit *hits, cudaStream_t st);
 
 }  // namespace b2

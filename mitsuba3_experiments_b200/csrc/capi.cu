@@ -591,7 +591,25 @@ int b2_trace(b2_scene *s, const float *rays, uint64_t n, int any_hit, b2_hit *hi
     if (!s || (n && (!rays || !hits))) return fail(-1, "b2_trace: null argument");
     if (!s->d.nodes && s->d.n_faces) return fail(-3, "b2_trace: b2_scene_build_accel has not been called");
     CUDA_OK(cudaSetDevice(s->ctx->device));
-    launch_trace(s->d, rays, n, any_hit, hits, (cudaStream_t) stream);
+    if (any_hit & 2) launch_trace(s->d, rays, n, any_hit & 1, hits, (cudaStream_t) stream);      // the megakernel's per-thread traversal (b2_bvh.cuh)
+    else if (n) {                                                                                   // the production kernel, k_wf_trace
+        if (int rc = wf_reserve(s, n, 0, (cudaStream_t) stream)) return rc;
+        RenderParams p{}; p.sc = s->d; p.counters = nullptr;
+        const char *err = nullptr;
+        const long l = wf_trace_rays(p, s->wf, rays, n, any_hit & 1, hits, s->ctx->sm_count, (cudaStream_t) stream, &err);
+        if (l < 0) return fail(-11, err ? err : "wavefront trace failed");
+        s->launches += (uint64_t) l;
+    }
+    CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int b2_debug_sampler(b2_scene *s, const b2_render_args *a, uint64_t lane_begin, uint32_t n_lanes, uint32_t n_draws, float *out, float *pos, uintptr_t stream) {
+    if (!s || !a || !out) return fail(-1, "b2_debug_sampler: null argument");
+    CUDA_OK(cudaSetDevice(s->ctx->device));
+    RenderParams p; int blocks; size_t smem;
+    if (int rc = setup_params(s, a, MODE_WEIGHTS, false, p, blocks, smem, 0, 0)) return rc;
+    launch_debug_sampler(p, lane_begin, n_lanes, n_draws, out, pos, (cudaStream_t) stream);
     CUDA_OK(cudaGetLastError());
     return 0;
 }

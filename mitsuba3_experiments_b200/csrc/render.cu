@@ -199,6 +199,19 @@ __global__ void k_trace(const __grid_constant__ DScene sc, const float *__restri
         hits[i] = b2_hit{ h.t, h.u, h.v, h.face };
     }
 }
+// unit-test hook of the sampler: the draws every render kernel makes for a lane come from Pcg32::seed_lane(seed, global lane)
+__global__ void k_debug_sampler(const __grid_constant__ RenderParams p, uint64_t lane_begin, uint32_t n_lanes, uint32_t n_draws, float *out, float *pos) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_lanes) return;
+    const uint32_t lane = (uint32_t) (lane_begin + i);
+    Pcg32 rng; rng.seed_lane(p.seed, global_lane(p, lane));
+    if (pos) { Pcg32 r2 = rng; int px, py; const f2 sp = lane_sample_pos(p, lane, r2, px, py); pos[2 * (size_t) i] = sp.x; pos[2 * (size_t) i + 1] = sp.y; }
+    for (uint32_t k = 0; k < n_draws; ++k) out[(size_t) i * n_draws + k] = rng.next_1d();
+}
+void launch_debug_sampler(const RenderParams &p, uint64_t lane_begin, uint32_t n_lanes, uint32_t n_draws, float *out, float *pos, cudaStream_t st) {
+    if (n_lanes) k_debug_sampler<<<(n_lanes + 127) / 128, 128, 0, st>>>(p, lane_begin, n_lanes, n_draws, out, pos);
+}
+
 void launch_trace(const DScene &sc, const float *rays, uint64_t n, int any_hit, b2_hit *hits, cudaStream_t st) {
     if (n) k_trace<<<(unsigned) ((n + 127) / 128), 128, 0, st>>>(sc, rays, n, any_hit, hits);
 }

@@ -538,6 +538,44 @@ long wf_weights(RenderParams p, int sm_count, cudaStream_t stream, const char **
     return 1;
 }
 
+// ------------------------------------------------------------------------------------------ b2_trace through the production kernel
+// The unit-test hook traces caller-supplied rays with k_wf_trace itself: the rays become the ray (closest) or shadow-ray (any hit)
+// stream of a wavefront chunk, the queues are the identity, and the hit records / arrival flags are converted back.
+__global__ void __launch_bounds__(256) k_wf_rays_in(const __grid_constant__ WfLaunch w, const float *rays, int any_hit) {
+    const WfState &st = w.st;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { if (any_hit) st.ctl->n_shadow[(w.it + 3u) & 3u] = w.n; else st.ctl->n_closest[w.it & 3u] = w.n; }
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < w.n; i += gridDim.x * blockDim.x) {
+        const float *r = rays + 8 * (size_t) i;
+        Elem e; e.a = make_float4(r[0], r[1], r[2], r[6]); e.b = make_float4(r[3], r[4], r[5], 0.f);
+        if (any_hit) { st256(&st.shr[i], e); Elem f; f.a = make_float4(0.f, 0.f, 0.f, 0.f); f.b = f.a; st256(&st.shf[i], f); st.q_shadow[i] = i; }
+        else { st256(&st.ray[i], e); st.q[w.it & 1u][i] = i; }
+    }
+}
+__global__ void __launch_bounds__(256) k_wf_hits_out(const __grid_constant__ WfLaunch w, const float *rays, int any_hit, b2_hit *hits) {
+    const WfState &st = w.st;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < w.n; i += gridDim.x * blockDim.x) {
+        if (any_hit) { const bool occ = st.shf[i].a.w == 0.f; hits[i] = b2_hit{ occ ? 0.f : rays[8 * (size_t) i + 6], 0.f, 0.f, occ ? 0u : 0xffffffffu }; }
+        else { const float4 h = st.hit[i].a; hits[i] = b2_hit{ h.x, h.y, h.z, __float_as_uint(h.w) }; }
+    }
+}
+long wf_trace_rays(RenderParams p, WfState &st, const float *rays, uint64_t n, int any_hit, b2_hit *hits, int sm_count, cudaStream_t stream, const char **err) {
+    const int g_trace = wf_trace_blocks(false, sm_count);
+    if (g_trace <= 0) { *err = "wavefront: the trace kernel cannot be resident"; return -1; }
+    long launches = 0;
+    for (uint64_t c0 = 0; c0 < n; c0 += st.capacity) {
+        const uint32_t m = (uint32_t) std::min<uint64_t>(st.capacity, n - c0);
+        WfLaunch w = wf_launch_defaults(st, c0, m); w.it = 0;
+        const int g = (int) std::min<uint64_t>((m + 255) / 256, (uint64_t) sm_count * 8);
+        cudaMemsetAsync(st.ctl, 0, sizeof(WfCtl), stream);
+        k_wf_rays_in<<<g, 256, 0, stream>>>(w, rays + 8 * c0, any_hit);
+        wf_launch_trace(false, false, p, w, g_trace, stream);
+        k_wf_hits_out<<<g, 256, 0, stream>>>(w, rays + 8 * c0, any_hit, hits + c0);
+        launches += 3;
+    }
+    if (cudaGetLastError() != cudaSuccess) { *err = "wavefront: kernel launch failed"; return -1; }
+    return launches;
+}
+
 long wf_render_backward(bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {
     return count ? wf_render_backward_t<true>(p, st, sm_count, stream, err) : wf_render_backward_t<false>(p, st, sm_count, stream, err);
 }

@@ -161,14 +161,27 @@ class DeviceScene:
                                               C.byref(cnt) if counters else None))
         return film, (cnt.as_dict() if counters else None)
 
-    def trace(self, rays, any_hit=False):
+    def trace(self, rays, any_hit=False, kernel=capi.KERNEL_WAVEFRONT):
+        """Unit-test hook: closest hits (or arrival tests) of caller-supplied rays, through the wavefront trace kernel (default)
+        or the megakernel's per-thread traversal."""
         torch = _torch()
         r = as_device_tensor(rays, self.device, torch.float32).reshape(-1, 8)
         hits = torch.empty((r.shape[0], 4), dtype=torch.float32, device=self.device)
-        capi.check(self.lib.b2_trace(self.handle, r.data_ptr(), r.shape[0], int(any_hit), hits.data_ptr(), self._stream()))
+        flags = int(bool(any_hit)) | (2 if kernel == capi.KERNEL_MEGAKERNEL else 0)
+        capi.check(self.lib.b2_trace(self.handle, r.data_ptr(), r.shape[0], flags, hits.data_ptr(), self._stream()))
         torch.cuda.synchronize(self.device)
         out = hits.cpu().numpy()
         return out.view(np.dtype([("t", "f4"), ("u", "f4"), ("v", "f4"), ("prim", "u4")])).reshape(-1)
+
+    def debug_sampler(self, lane_begin, n_lanes, n_draws, seed=0, spp=None):
+        """Unit-test hook: (draws [n_lanes, n_draws], sample positions [n_lanes, 2]) exactly as the render kernels derive them."""
+        torch = _torch()
+        a = self.make_args(seed=seed, spp=spp)
+        out = torch.empty((n_lanes, n_draws), dtype=torch.float32, device=self.device)
+        pos = torch.empty((n_lanes, 2), dtype=torch.float32, device=self.device)
+        capi.check(self.lib.b2_debug_sampler(self.handle, C.byref(a), int(lane_begin), int(n_lanes), int(n_draws), out.data_ptr(), pos.data_ptr(), self._stream()))
+        torch.cuda.synchronize(self.device)
+        return out.cpu().numpy(), pos.cpu().numpy()
 
     def set_kernel_timing(self, enabled: bool):
         """Kernel history (``dr.kernel_history`` analogue): bracket every wavefront launch with CUDA events."""

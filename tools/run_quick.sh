@@ -1,3 +1,1 @@
-echo "== default grid"; python tools/exp_overlap.py 2>&1 | tail -7
-echo "== trace blocks 2"; B2_TRACE_BLOCKS=2 python tools/exp_overlap.py 2>&1 | tail -7
-echo "== trace blocks 3"; B2_TRACE_BLOCKS=3 python tools/exp_overlap.py 2>&1 | tail -7
+python -m pytest tests/test_gpu_parity.py -m gpu -q -k "coplanar or rough_bsdf_gradient_targets_parity" 2>&1 | grep -E "^E  |assert|Error|passed|failed" | head -40
