@@ -96,7 +96,8 @@ void wf_bind(WfState &st, void *base, uint32_t capacity);
 // with `err` set.
 // PRB adjoint for lanes [p.lane_begin, p.lane_end): primal pass (records emitter-sample visibility), then the replay
 // with gradient scatter.  p.wfilm must hold the weight film of the sample set.  Needs max_depth <= 32.
-long wf_render_backward(bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err);
+// hit_history: nullptr, or max(max_depth, 1) x capacity 32-byte hit records (the adjoint replay then skips its closest-ray traces)
+long wf_render_backward(bool count, RenderParams p, WfState &st, void *hit_history, int sm_count, cudaStream_t stream, const char **err);
 // b2_trace through k_wf_trace: rays [n][8] (device) -> hits [n] (device); any_hit: arrival test of shadow rays
 long wf_trace_rays(RenderParams p, WfState &st, const float *rays, uint64_t n, int any_hit, b2_hit *hits, int sm_count, cudaStream_t stream, const char **err);
 long wf_weights(RenderParams p, int sm_count, cudaStream_t stream, const char **err);

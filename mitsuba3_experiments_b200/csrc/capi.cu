@@ -37,6 +37,7 @@ struct b2_scene {
     WfTiming timing; bool timing_on = false;     // kernel history (b2_kernel_times)
     uint32_t class_mask = 0;                    // shading classes present in the scene (bit = CLS_*)
     void *wf_mem = nullptr; uint32_t wf_capacity = 0; WfState wf{};   // wavefront lane state (grown on demand)
+    void *wf_hist = nullptr; size_t wf_hist_bytes = 0;                // PRB: closest hits of every bounce of the primal pass (replayed by the adjoint)
     uint64_t launches = 0;
 
     template <typename T> cudaError_t upload(const T *host, size_t n, T *&dev) {
@@ -45,7 +46,7 @@ struct b2_scene {
         if (n && host) e = cudaMemcpy(q, host, n * sizeof(T), cudaMemcpyHostToDevice);
         return e;
     }
-    ~b2_scene() { for (cudaEvent_t e : timing.ev) cudaEventDestroy(e); for (void *q : allocs) cudaFree(q); if (wf_mem) cudaFree(wf_mem); bvh_free(bvh); }
+    ~b2_scene() { for (cudaEvent_t e : timing.ev) cudaEventDestroy(e); for (void *q : allocs) cudaFree(q); if (wf_mem) cudaFree(wf_mem); if (wf_hist) cudaFree(wf_hist); bvh_free(bvh); }
 };
 
 extern "C" {
@@ -311,6 +312,21 @@ static int wf_reserve(b2_scene *s, uint64_t shard_lanes, uint32_t chunk_lanes, c
     return 0;
 }
 
+// PRB: room for the closest hit of every bounce of the primal pass (32 B x lanes x max_depth), so that the adjoint replay does not
+// trace the same closest rays again.  Optional: beyond B2_HIT_HISTORY_GB (default 32) the adjoint re-traces instead.
+static void *wf_reserve_history(b2_scene *s, int max_depth, cudaStream_t st) {
+    static const double limit_gb = getenv("B2_HIT_HISTORY_GB") ? atof(getenv("B2_HIT_HISTORY_GB")) : 32.0;
+    const size_t need = (size_t) std::max(max_depth, 1) * s->wf.capacity * 32;
+    if ((double) need > limit_gb * 1073741824.0) return nullptr;
+    if (need > s->wf_hist_bytes) {
+        if (cudaStreamSynchronize(st) != cudaSuccess) return nullptr;
+        if (s->wf_hist) { cudaFree(s->wf_hist); s->wf_hist = nullptr; s->wf_hist_bytes = 0; }
+        if (cudaMalloc(&s->wf_hist, need) != cudaSuccess) { cudaGetLastError(); s->wf_hist = nullptr; return nullptr; }
+        s->wf_hist_bytes = need;
+    }
+    return s->wf_hist;
+}
+
 // integrator.cpp:139-152,247-265
 static int derive_passes(const b2_scene *s, const b2_render_args *a, uint32_t &spp_per_pass, uint32_t &n_passes, uint64_t &wavefront) {
     if (a->spp == 0) return fail(-2, "render: spp must be > 0");
@@ -509,7 +525,7 @@ int b2_render_backward(b2_scene *s, const b2_render_args *a, const float *grad_i
                 if (int rc = wf_reserve(s, p.lane_end - p.lane_begin, a->chunk_lanes, st)) return rc;
                 const char *err = nullptr;
                 wf_set_timing(s->timing_on ? &s->timing : nullptr);
-                const long n = wf_render_backward(count, p, s->wf, s->ctx->sm_count, st, &err);
+                const long n = wf_render_backward(count, p, s->wf, wf_reserve_history(s, a->max_depth, st), s->ctx->sm_count, st, &err);
                 wf_set_timing(nullptr);
                 if (n < 0) return fail(-11, err ? err : "wavefront render_backward failed");
                 launches += (uint64_t) n;
@@ -557,7 +573,7 @@ int b2_render_forward(b2_scene *s, const b2_render_args *a, const b2_grad_target
         if (int rc = wf_reserve(s, p.lane_end - p.lane_begin, a->chunk_lanes, st)) return rc;
         const char *err = nullptr;
         wf_set_timing(s->timing_on ? &s->timing : nullptr);
-        const long n = wf_render_backward(count, p, s->wf, s->ctx->sm_count, st, &err);
+        const long n = wf_render_backward(count, p, s->wf, wf_reserve_history(s, a->max_depth, st), s->ctx->sm_count, st, &err);
         wf_set_timing(nullptr);
         if (n < 0) return fail(-11, err ? err : "wavefront render_forward failed");
         launches += (uint64_t) n;

@@ -460,8 +460,10 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
     return launches;
 }
 
+// hist: optional [n_iter][capacity] hit records.  With it, the primal pass keeps the closest hit of every bounce and the adjoint
+// replay (identical rays by construction) reads them back instead of tracing every closest ray a second time.
 template <bool COUNT>
-static long wf_render_backward_t(RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {
+static long wf_render_backward_t(RenderParams p, WfState &st, Elem *hist, int sm_count, cudaStream_t stream, const char **err) {
     constexpr int V = B2_VARIANT_PRB;
     long launches = 0;
     int occ_shade = 0, occ_adj = 0;
@@ -488,11 +490,12 @@ static long wf_render_backward_t(RenderParams p, WfState &st, int sm_count, cuda
         w.record_vis = 1u;
         for (uint32_t k = 0; k < n_iter; ++k) {
             w.it = it; w.bounce = k; w.first = k == 0 ? 1u : 0u;
+            if (hist) w.st.hit = hist + (size_t) k * st.capacity;
             wf_launch_trace(COUNT, k == 0, p, w, g_trace, stream); launches++;
             B2_SHADE_LAUNCH(V, COUNT, false);
             ++it;
         }
-        w.it = it; w.first = 0u;
+        w.it = it; w.first = 0u; w.st.hit = st.hit;
         wf_launch_trace(COUNT, false, p, w, g_trace, stream); launches++;
         ++it;
         // ---- adjoint pass (common.py:763-773): replay of the identical stream, closest-hit rays only
@@ -500,10 +503,12 @@ static long wf_render_backward_t(RenderParams p, WfState &st, int sm_count, cuda
         tm_begin(WF_K_OTHER, stream); k_wf_generate_adj<<<g_gen, 256, 0, stream>>>(p, w); tm_end(stream); launches++;
         for (uint32_t k = 0; k < n_iter; ++k) {
             w.it = it; w.bounce = k;
-            wf_launch_trace(COUNT, false, p, w, g_trace, stream); launches++;
+            if (hist) w.st.hit = hist + (size_t) k * st.capacity;               // the hits the primal pass recorded for this bounce
+            else { wf_launch_trace(COUNT, false, p, w, g_trace, stream); launches++; }
             tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, true><<<g_adj, 256, 0, stream>>>(p, w); tm_end(stream); launches++;
             ++it;
         }
+        w.st.hit = st.hit;
         if (B2_FWD(p)) {
             // forward mode: splat the lanes' d L (accumulated in the dL stream) like a render splats L (common.py:585-600)
             const DSensor &sn = p.sc.sensor; const uint32_t W = (uint32_t) sn.grid_w, P = p.unit_pixels;
@@ -576,8 +581,8 @@ long wf_trace_rays(RenderParams p, WfState &st, const float *rays, uint64_t n, i
     return launches;
 }
 
-long wf_render_backward(bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {
-    return count ? wf_render_backward_t<true>(p, st, sm_count, stream, err) : wf_render_backward_t<false>(p, st, sm_count, stream, err);
+long wf_render_backward(bool count, RenderParams p, WfState &st, void *hit_history, int sm_count, cudaStream_t stream, const char **err) {
+    return count ? wf_render_backward_t<true>(p, st, (Elem *) hit_history, sm_count, stream, err) : wf_render_backward_t<false>(p, st, (Elem *) hit_history, sm_count, stream, err);
 }
 
 long wf_render(int variant, bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err) {

@@ -71,6 +71,13 @@ struct Film {
             atomic_add(p[2], (double) (rgb.z * wgt)); atomic_add(p[3], (double) (1.f * wgt));
         }, c);
     }
+    // the same into a thread-private accumulator (no atomics; merged once per thread at the end of the render)
+    void put_private(double *priv, V2 pos, V3 rgb, Counters &c) const {
+        taps(pos, [&](size_t pix, float wgt) {
+            double *p = priv + pix * 4;
+            p[0] += (double) (rgb.x * wgt); p[1] += (double) (rgb.y * wgt); p[2] += (double) (rgb.z * wgt); p[3] += (double) (1.f * wgt);
+        }, c);
+    }
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -342,9 +349,12 @@ int orc_render(void *hp, const b2_render_args *a, float *film_rgbw, b2_counters 
     Film film(s); Integrator integ(h->scene, a->max_depth, a->rr_depth);
     integ.em.env_warp = a->env_warp;
     Counters total;
+    // thread-private double films (merged once) instead of one atomic per tap and channel, unless they would not fit in 4 GB
+    const bool priv_films = film.acc.size() * sizeof(double) * (size_t) orc_num_threads() <= ((size_t) 4 << 30);
 #pragma omp parallel
     {
         Counters c;
+        std::vector<double> priv(priv_films ? film.acc.size() : 0, 0.0);
 #pragma omp for schedule(dynamic, 1024)
         for (int64_t lane = (int64_t) lb; lane < (int64_t) le; ++lane) {
             Sampler smp; smp.rng = sampler_seed(a->seed, (uint32_t) lane);
@@ -357,11 +367,15 @@ int orc_render(void *hp, const b2_render_args *a, float *film_rgbw, b2_counters 
                      : a->variant == B2_VARIANT_PATH_MIS ? integ.sample_path_mis(smp, ray, c)
                      : integ.sample_prb(true, smp, ray, V3(0.f), V3(0.f), [](int, const SI &, V3) {}, c);
                 V2 splat = s.rfilter == B2_RFILTER_BOX ? V2{ (float) px, (float) py } : sample_pos;
-                film.put(splat, L, c); c.samples++;
+                if (priv_films) film.put_private(priv.data(), splat, L, c); else film.put(splat, L, c);
+                c.samples++;
             }
         }
 #pragma omp critical
-        total.add(c);
+        {
+            total.add(c);
+            if (priv_films) for (size_t i = 0; i < priv.size(); ++i) film.acc[i] += priv[i];
+        }
     }
     for (size_t i = 0; i < film.acc.size(); ++i) film_rgbw[i] += (float) film.acc[i];
     export_counters(total, counters);

@@ -287,8 +287,9 @@ def test_prb_backward_parity(textured, kernel):
         else:
             np.testing.assert_allclose(g, ref, rtol=1e-3)
     cnt = prb.last_counters
-    if kernel == "wavefront":        # the replay reuses the visibility bits recorded by the primal pass: half the shadow rays
-        cnt["shadow_rays"] *= 2
+    if kernel == "wavefront":        # the replay reuses the visibility bits AND the closest hits recorded by the primal pass:
+        cnt["shadow_rays"] *= 2      # it traces nothing, so the wavefront counts half the rays of the reference's two passes
+        cnt["closest_rays"] *= 2
     for k in ("samples", "closest_rays", "shadow_rays", "grad_atomics"):
         assert abs(cnt[k] - rc[k]) <= 1e-3 * max(rc[k], 1), (k, cnt[k], rc[k])
 
