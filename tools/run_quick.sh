@@ -1,1 +1,4 @@
-for l in base s6q3 s4q4 s4q2; do echo "$l bedroom: $(B2PATH_LIB=$PWD/tuning_libs/$l.so python tools/profile_render.py bedroom 3 64 2>&1 | grep 'launch 2')  soup8: $(B2PATH_LIB=$PWD/tuning_libs/$l.so python tools/profile_render.py tris 3 8 2>&1 | grep 'launch 2')"; done
+python tools/exp_kinds.py $PWD/tuning_libs/r1 soup 128 2>&1 | tail -1
+python tools/exp_kinds.py $PWD soup 128 2>&1 | tail -1
+python tools/exp_kinds.py $PWD/tuning_libs/r1 soup 32 2>&1 | tail -1
+python tools/exp_kinds.py $PWD soup 32 2>&1 | tail -1
