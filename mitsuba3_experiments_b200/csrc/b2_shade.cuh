@@ -25,10 +25,13 @@ enum { LOBE_DIFFUSE = 1, LOBE_GLOSSY = 2, LOBE_DELTA_R = 4, LOBE_DELTA_T = 8, LO
 // Shading classes: the wavefront sorts the hits of a bounce by class and runs one specialised shade kernel per class
 // (CLS >= 0 turns the BSDF-type switch and the textured/constant test into compile-time constants); CLS_GENERIC keeps
 // both at run time (megakernel, adjoint replay).
-enum { CLS_GENERIC = -1, CLS_DIFFUSE = 0, CLS_DIFFUSE_TEX = 1, CLS_CONDUCTOR = 2, CLS_DIELECTRIC = 3, CLS_MISS = 4, CLS_COUNT = 5 };
+// CLS_CONDUCTOR = rough conductor, CLS_PLASTIC = rough plastic, CLS_ROUGHDIEL = rough dielectric (one kernel each: the single "glossy"
+// kernel that switched between the three at run time was 15 520 SASS instructions and spent 86 % of its cycles waiting for
+// instruction fetch, profiles/README.md round 2), CLS_DIELECTRIC = the delta BSDFs (smooth dielectric, smooth conductor).
+enum { CLS_GENERIC = -1, CLS_DIFFUSE = 0, CLS_DIFFUSE_TEX = 1, CLS_CONDUCTOR = 2, CLS_DIELECTRIC = 3, CLS_MISS = 4, CLS_PLASTIC = 5, CLS_ROUGHDIEL = 6, CLS_COUNT = 7 };
 template <int CLS> B2_DEV int cls_type(int runtime_type) {
     return (CLS == CLS_DIFFUSE || CLS == CLS_DIFFUSE_TEX) ? B2_BSDF_DIFFUSE
-           : CLS == CLS_CONDUCTOR ? (runtime_type == B2_BSDF_ROUGHDIELECTRIC ? B2_BSDF_ROUGHDIELECTRIC : runtime_type == B2_BSDF_ROUGHPLASTIC ? B2_BSDF_ROUGHPLASTIC : B2_BSDF_ROUGHCONDUCTOR)   // the glossy class
+           : CLS == CLS_CONDUCTOR ? B2_BSDF_ROUGHCONDUCTOR : CLS == CLS_PLASTIC ? B2_BSDF_ROUGHPLASTIC : CLS == CLS_ROUGHDIEL ? B2_BSDF_ROUGHDIELECTRIC
            : CLS == CLS_DIELECTRIC ? (runtime_type == B2_BSDF_CONDUCTOR ? B2_BSDF_CONDUCTOR : B2_BSDF_DIELECTRIC)   // the delta class
            : runtime_type;
 }

@@ -54,7 +54,7 @@ struct WfState {                     // `capacity` lane slots (slot = lane - chu
     uint8_t *cls_q;                  // shading class of the hit of queue entry i of the current iteration (trace -> classify)
     uint32_t *q[2];                  // closest-ray queues (lane slots), double buffered by iteration parity
     uint32_t *q_shadow;              // shadow-ray queue
-    uint32_t *qc[5];                 // closest hits of the current iteration sorted by shading class (CLS_*)
+    uint32_t *qc[7];                 // closest hits of the current iteration sorted by shading class (CLS_*)
     uint32_t class_mask;             // classes present in the scene
     WfCtl *ctl;
     uint32_t capacity;

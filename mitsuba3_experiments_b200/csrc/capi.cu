@@ -106,7 +106,8 @@ int b2_scene_create(b2_ctx *ctx, const b2_scene_desc *desc, b2_scene **out) {
         if (m.bsdf < 0 || (uint32_t) m.bsdf >= desc->n_bsdfs) return fail(-2, "b2_scene_create: mesh references a missing BSDF");
         if ((uint64_t) m.first_face + m.n_faces > desc->n_faces) return fail(-2, "b2_scene_create: mesh face range out of bounds");
         const b2_bsdf &mb = desc->bsdfs[m.bsdf];
-        const uint32_t cls = mb.type == B2_BSDF_DIFFUSE ? (mb.reflectance_tex >= 0 ? 1u : 0u) : ((mb.type == B2_BSDF_ROUGHCONDUCTOR || mb.type == B2_BSDF_ROUGHDIELECTRIC || mb.type == B2_BSDF_ROUGHPLASTIC) ? 2u : 3u);   // CLS_* of b2_shade.cuh: glossy | delta
+        // CLS_* of b2_shade.cuh: 0 diffuse, 1 textured diffuse, 2 rough conductor, 3 delta (dielectric, conductor), 5 rough plastic, 6 rough dielectric
+        const uint32_t cls = mb.type == B2_BSDF_DIFFUSE ? (mb.reflectance_tex >= 0 ? 1u : 0u) : mb.type == B2_BSDF_ROUGHCONDUCTOR ? 2u : mb.type == B2_BSDF_ROUGHPLASTIC ? 5u : mb.type == B2_BSDF_ROUGHDIELECTRIC ? 6u : 3u;
         s->class_mask |= 1u << cls;
         meshes[i] = DMesh{ m.bsdf, m.emitter, m.flags, m.first_face, m.n_faces, cls, { 0, 0 } };
         // the triangle records carry mesh | class << 28 (the trace kernel's epilogue needs both and nothing else of the mesh)

@@ -424,7 +424,7 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
                 // and every lane is a miss; the generic kernel takes the whole queue)
                 const bool sort = !w.no_hit &&
                                   (tune_sort >= 0 ? tune_sort != 0     // default: sort when the BSDFs differ enough to diverge
-                                                  : (__builtin_popcount(cmask) >= 2 && (cmask & ((1u << CLS_CONDUCTOR) | (1u << CLS_DIELECTRIC))) != 0));
+                                                  : (__builtin_popcount(cmask) >= 2 && (cmask & ((1u << CLS_CONDUCTOR) | (1u << CLS_DIELECTRIC) | (1u << CLS_PLASTIC) | (1u << CLS_ROUGHDIEL))) != 0));
                 if (!sort && cmask == (1u << CLS_DIFFUSE)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_DIFFUSE, false);
                 else if (sort) {
                     tm_begin(WF_K_SHADE, stream); k_wf_classify<<<g_shade, 256, 0, stream>>>(w); tm_end(stream); launches++;
@@ -432,6 +432,8 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
                     if (cm & (1u << CLS_DIFFUSE)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_DIFFUSE);
                     if (cm & (1u << CLS_DIFFUSE_TEX)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_DIFFUSE_TEX);
                     if (cm & (1u << CLS_CONDUCTOR)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_CONDUCTOR);
+                    if (cm & (1u << CLS_PLASTIC)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_PLASTIC);
+                    if (cm & (1u << CLS_ROUGHDIEL)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_ROUGHDIEL);
                     if (cm & (1u << CLS_DIELECTRIC)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_DIELECTRIC);
                     B2_SHADE_LAUNCH(V, COUNT, false, CLS_MISS);
                 } else B2_SHADE_LAUNCH(V, COUNT);

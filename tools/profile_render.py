@@ -11,6 +11,8 @@ kernel = int(sys.argv[4]) if len(sys.argv) > 4 else 0   # 0 wavefront, 1 megaker
 chunk = int(sys.argv[5]) if len(sys.argv) > 5 else 0
 if wl == "bedroom":
     spp = spp or 64; d = scenes.bedroom_standin(1280, 720, spp); kw = dict(variant=1, max_depth=8, rr_depth=2)
+elif wl == "bedroom_xml":
+    spp = spp or 64; d = scenes.bedroom_standin(1280, 720, spp, palette="scene_xml"); kw = dict(variant=1, max_depth=8, rr_depth=2)
 elif wl == "cornell":
     spp = spp or 16; d = scenes.cornell_box(256, 256, spp); kw = dict(variant=0, max_depth=8, rr_depth=4)
 elif wl == "tris":

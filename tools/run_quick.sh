@@ -1,4 +1,3 @@
-python tools/exp_kinds.py $PWD/tuning_libs/r1 soup 128 2>&1 | tail -1
-python tools/exp_kinds.py $PWD soup 128 2>&1 | tail -1
-python tools/exp_kinds.py $PWD/tuning_libs/r1 soup 32 2>&1 | tail -1
-python tools/exp_kinds.py $PWD soup 32 2>&1 | tail -1
+python -m pytest tests -m gpu -q -x 2>&1 | tail -3
+python tools/profile_render.py bedroom_xml 3 64 2>&1 | grep -E "launch 2"
+python tools/profile_render.py bedroom 3 64 2>&1 | grep -E "launch 2"
