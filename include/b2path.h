@@ -29,6 +29,7 @@
  *   b2_kernel_times        <- dr.kernel_history() as printed by path.py:332-351
  *   b2_trace               <- Scene::ray_intersect_preliminary / ray_test (mi3/src/render/scene.cpp:191-235)
  *   b2_debug_sampler       <- PCG32Sampler::seed + next_1d (mi3/src/render/sampler.cpp:129-148, samplers/independent.cpp:88-97)
+ *   b2_trace_noalloc       <- no counterpart in the reference
  */
 #ifndef B2PATH_H
 #define B2PATH_H
@@ -248,6 +249,14 @@ int  b2_render_forward(b2_scene *scene, const b2_render_args *args, const b2_gra
 /* unit-test hook: rays_dev [n][8] = o.xyz, d.xyz, tmax, unused.  any_hit bit 0: arrival test (Scene::ray_test) instead of the closest
    hit; bit 1: trace with the megakernel's per-thread traversal instead of the wavefront trace kernel (the product default). */
 int  b2_trace(b2_scene *scene, const float *rays_dev, uint64_t n, int any_hit, b2_hit *hits_dev, uintptr_t stream);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code under
+   CUDA graph capture, tight serving loops, harnesses that forbid it).  b2_trace through the wavefront trace kernel (any_hit bit 0 as
+   above; bit 1 is rejected), with the kernel's lane state in a file-scope device array of the library instead of a cudaMalloc'ed
+   block: the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).  n > B2_TRACE_NOALLOC_MAX_RAYS is
+   rejected with -2.  The array (8 421 632 B, held by every GPU that loads the library until the process exits) is shared by all
+   calls and all scenes of a device: calls that overlap on the GPU race -- serialise them (one stream, or events). */
+#define B2_TRACE_NOALLOC_MAX_RAYS 32768u
+int  b2_trace_noalloc(b2_scene *scene, const float *rays_dev, uint64_t n, int any_hit, b2_hit *hits_dev, uintptr_t stream);
 /* unit-test hook for the sampler (integer work, must be bit exact): out_dev [n_lanes][n_draws] = the first n_draws
    next_float32() of lanes lane_begin .. lane_begin + n_lanes - 1, seeded exactly as the render kernels seed them
    (PCG32Sampler::seed, sampler.cpp:129-148: TEA(seed, lane) -> PCG32, drjit random.h:60-79,211-213); the primary-ray

@@ -28,6 +28,7 @@ RFILTER_BOX, RFILTER_TENT, RFILTER_GAUSSIAN = 0, 1, 2
 MESH_HAS_NORMALS, MESH_HAS_UV, MESH_FLIP_NORMALS = 1, 2, 4
 VARIANT_PATH, VARIANT_PATH_MIS, VARIANT_PRB = 0, 1, 2
 KERNEL_WAVEFRONT, KERNEL_MEGAKERNEL = 0, 1
+TRACE_NOALLOC_MAX_RAYS = 32768        # B2_TRACE_NOALLOC_MAX_RAYS (include/b2path.h)
 ENV_WARP_HIERARCHICAL, ENV_WARP_ALIAS = 0, 1
 
 f32, i32, u32, u64 = C.c_float, C.c_int32, C.c_uint32, C.c_uint64
@@ -112,7 +113,7 @@ class GradTarget(C.Structure):
 
 # every symbol include/b2path.h declares for the product library
 EXPORTS = ["b2_init", "b2_shutdown", "b2_scene_create", "b2_scene_destroy", "b2_scene_build_accel",
-           "b2_scene_set_param", "b2_render", "b2_develop", "b2_render_backward", "b2_render_forward", "b2_trace", "b2_debug_sampler",
+           "b2_scene_set_param", "b2_render", "b2_develop", "b2_render_backward", "b2_render_forward", "b2_trace", "b2_trace_noalloc", "b2_debug_sampler",
            "b2_render_host", "b2_set_kernel_timing", "b2_kernel_times", "b2_last_error", "b2_abi_version"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -159,6 +160,7 @@ def load_library() -> C.CDLL:
                                        C.POINTER(Counters)]
     lib.b2_render_forward.argtypes = [vp, C.POINTER(RenderArgs), C.POINTER(GradTarget), C.c_int, vp, up, C.POINTER(Counters)]
     lib.b2_trace.argtypes = [vp, vp, u64, C.c_int, vp, up]
+    lib.b2_trace_noalloc.argtypes = [vp, vp, u64, C.c_int, vp, up]
     lib.b2_debug_sampler.argtypes = [vp, C.POINTER(RenderArgs), u64, C.c_uint32, C.c_uint32, vp, vp, up]
     lib.b2_render_host.argtypes = [vp, C.POINTER(RenderArgs), vp, vp, C.POINTER(Counters)]
     lib.b2_set_kernel_timing.argtypes = [vp, C.c_int]
@@ -166,7 +168,7 @@ def load_library() -> C.CDLL:
     lib.b2_last_error.restype = C.c_char_p
     lib.b2_abi_version.restype = C.c_int
     for name in ("b2_init", "b2_scene_create", "b2_scene_build_accel", "b2_scene_set_param", "b2_render",
-                 "b2_develop", "b2_render_backward", "b2_render_forward", "b2_trace", "b2_debug_sampler", "b2_render_host", "b2_set_kernel_timing", "b2_kernel_times"):
+                 "b2_develop", "b2_render_backward", "b2_render_forward", "b2_trace", "b2_trace_noalloc", "b2_debug_sampler", "b2_render_host", "b2_set_kernel_timing", "b2_kernel_times"):
         getattr(lib, name).restype = C.c_int
     if lib.b2_abi_version() != B2_ABI_VERSION:
         raise B2Error("libb2path.so ABI version mismatch")

@@ -100,6 +100,10 @@ void wf_bind(WfState &st, void *base, uint32_t capacity);
 long wf_render_backward(bool count, RenderParams p, WfState &st, void *hit_history, int sm_count, cudaStream_t stream, const char **err);
 // b2_trace through k_wf_trace: rays [n][8] (device) -> hits [n] (device); any_hit: arrival test of shadow rays
 long wf_trace_rays(RenderParams p, WfState &st, const float *rays, uint64_t n, int any_hit, b2_hit *hits, int sm_count, cudaStream_t stream, const char **err);
+// the same, with the lane state in a file-scope device array instead of st (wf_noalloc.cu): no allocation, n <= kNoAllocMaxRays
+constexpr uint64_t kNoAllocMaxRays = 32768;
+long wf_trace_rays_noalloc(RenderParams p, uint32_t class_mask, int device, const float *rays, uint64_t n, int any_hit, b2_hit *hits,
+                           int sm_count, cudaStream_t stream, const char **err);
 long wf_weights(RenderParams p, int sm_count, cudaStream_t stream, const char **err);
 long wf_render(int variant, bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err);
 

@@ -621,6 +621,25 @@ int b2_trace(b2_scene *s, const float *rays, uint64_t n, int any_hit, b2_hit *hi
     return 0;
 }
 
+// No counterpart in the reference: b2_trace without any device allocation, the lane
+// state of the rays in the static device array of wf_noalloc.cu.
+int b2_trace_noalloc(b2_scene *s, const float *rays, uint64_t n, int any_hit, b2_hit *hits, uintptr_t stream) {
+    if (!s || (n && (!rays || !hits))) return fail(-1, "b2_trace_noalloc: null argument");
+    if (any_hit & ~1) return fail(-2, "b2_trace_noalloc: any_hit must be 0 (closest hit) or 1 (arrival test)");
+    if (n > B2_TRACE_NOALLOC_MAX_RAYS) return fail(-2, "b2_trace_noalloc: n = " + std::to_string(n) + " rays exceeds B2_TRACE_NOALLOC_MAX_RAYS = 32768 (the size of the static scratch array)");
+    if (!s->d.nodes && s->d.n_faces) return fail(-3, "b2_trace_noalloc: b2_scene_build_accel has not been called");
+    CUDA_OK(cudaSetDevice(s->ctx->device));
+    if (n) {
+        RenderParams p{}; p.sc = s->d; p.counters = nullptr;
+        const char *err = nullptr;
+        const long l = wf_trace_rays_noalloc(p, s->class_mask, s->ctx->device, rays, n, any_hit, hits, s->ctx->sm_count, (cudaStream_t) stream, &err);
+        if (l < 0) return fail(l == -2 ? -2 : -11, err ? err : "b2_trace_noalloc failed");
+        s->launches += (uint64_t) l;
+    }
+    CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
 int b2_debug_sampler(b2_scene *s, const b2_render_args *a, uint64_t lane_begin, uint32_t n_lanes, uint32_t n_draws, float *out, float *pos, uintptr_t stream) {
     if (!s || !a || !out) return fail(-1, "b2_debug_sampler: null argument");
     CUDA_OK(cudaSetDevice(s->ctx->device));

@@ -173,6 +173,17 @@ class DeviceScene:
         out = hits.cpu().numpy()
         return out.view(np.dtype([("t", "f4"), ("u", "f4"), ("v", "f4"), ("prim", "u4")])).reshape(-1)
 
+    def trace_noalloc(self, rays, hits, any_hit=False):
+        """``b2_trace_noalloc``: the wavefront trace kernel over at most ``capi.TRACE_NOALLOC_MAX_RAYS`` caller-supplied rays with
+        the kernel's lane state in the library's static device array -- no device allocation inside the call.  ``rays`` [n, 8]
+        and ``hits`` [n, 4] are float32 CUDA tensors the caller owns; the launch is asynchronous on the current stream.  Calls
+        share the array: do not let two overlap on the GPU.  (No counterpart in the reference.)"""
+        torch = _torch()
+        assert rays.is_cuda and hits.is_cuda and rays.dtype == torch.float32 and hits.dtype == torch.float32
+        assert rays.is_contiguous() and hits.is_contiguous() and rays.shape[-1] == 8 and hits.numel() == rays.numel() // 2
+        capi.check(self.lib.b2_trace_noalloc(self.handle, rays.data_ptr(), rays.numel() // 8, int(bool(any_hit)), hits.data_ptr(), self._stream()))
+        return hits
+
     def debug_sampler(self, lane_begin, n_lanes, n_draws, seed=0, spp=None):
         """Unit-test hook: (draws [n_lanes, n_draws], sample positions [n_lanes, 2]) exactly as the render kernels derive them."""
         torch = _torch()
