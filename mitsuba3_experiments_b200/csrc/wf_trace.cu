@@ -240,6 +240,196 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
     trace_flush_counters(cnt, p.counters);
 }
 
+// ------------------------------------------------------------------------------------------ bounce 0: packet traversal
+// The 32 primary rays of a warp are consecutive lanes, i.e. samples of one pixel (or of neighbouring pixels): they visit the same
+// nodes.  k_wf_trace_packet walks the tree ONCE per warp: the stack and the node / triangle groups are warp-uniform, lane c < 8
+// tests child c of the fetched node against the INTERVAL of the warp's rays (per axis: [min, max] of the origins and of the
+// reciprocal directions, outward-rounded, boxes padded), and every lane tests every triangle of the visited leaves against its own
+// ray with the same Moeller-Trumbore arithmetic as k_wf_trace.  The closest hit of a ray is the lexicographic minimum of (t, face)
+// over the triangles it intersects -- independent of the traversal -- so a traversal that visits a SUPERSET of each ray's nodes
+// returns bit-identical hit records.  Children are culled against the largest `tbest` of the warp.
+B2_DEV int f_ord(int i) { return i ^ ((i >> 31) & 0x7fffffff); }      // order-preserving float bits <-> int (an involution)
+B2_DEV float warp_min_f(float f) { return __int_as_float(f_ord(__reduce_min_sync(0xffffffffu, f_ord(__float_as_int(f))))); }
+B2_DEV float warp_max_f(float f) { return __int_as_float(f_ord(__reduce_max_sync(0xffffffffu, f_ord(__float_as_int(f))))); }
+
+constexpr int kPacketThreads = 256;
+constexpr float kPkInf = 3.402823466e38f;
+#ifndef B2_PACKET_RAYS
+#define B2_PACKET_RAYS 2                  // rays per lane: a packet is 32 * B2_PACKET_RAYS consecutive lanes
+#endif
+#ifndef B2_PACKET_MINBLOCKS
+#define B2_PACKET_MINBLOCKS 4
+#endif
+
+template <bool COUNT, int R>
+__global__ void __launch_bounds__(kPacketThreads, B2_PACKET_MINBLOCKS) k_wf_trace_packet(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
+    __shared__ uint2 s_pstack[kPacketThreads / 32][kStackSize];
+    const DScene &sc = p.sc; const WfState &st = w.st;
+    const uint32_t total = w.n, full = 0xffffffffu;
+    uint32_t *fetch = &st.ctl->fetch[w.it & 3u];
+    const int lane = threadIdx.x & 31;
+    uint2 *stack = s_pstack[threadIdx.x >> 5];      // every lane writes the same value: no ordering needed between the lanes
+    const uint32_t c = lane & 7u; const bool chi = c >= 4u;
+    const uint32_t psel = 0x4505u | ((c & 3u) << 4);          // byte c & 3 of a plane word -> mantissa bits 8..15 of 32768 + q (qbyte_biased)
+    const uint32_t csh = (c & 3u) * 8u;
+    Counters<COUNT> cnt;
+    uint32_t next = 0;
+    if (lane == 0) next = atomicAdd(fetch, 32u * R);
+    for (;;) {
+        const uint32_t base = __shfl_sync(full, next, 0);
+        if (base >= total) break;
+        if (lane == 0) next = atomicAdd(fetch, 32u * R);
+        // ---- the lane's rays (as stage C of k_wf_trace<., true>); lanes past the end repeat the last ray and store nothing
+        f3 o[R], d[R]; float tbest[R], bu[R], bv[R]; uint32_t bface[R], bmesh[R];
+        float ix0 = kPkInf, ix1 = -kPkInf, iy0 = kPkInf, iy1 = -kPkInf, iz0 = kPkInf, iz1 = -kPkInf;
+        float ox0 = kPkInf, ox1 = -kPkInf, oy0 = kPkInf, oy1 = -kPkInf, oz0 = kPkInf, oz1 = -kPkInf;
+        float tbest_w = 0.f;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const uint32_t e = min(base + 32u * r + lane, total - 1u);
+            Pcg32 rng;
+            const uint32_t ln = (uint32_t) (w.chunk_begin + e);
+            if (w.pass == 0) rng.seed_lane(p.seed, global_lane(p, ln));
+            else { const float4 q = __ldg(&st.rng[e].a); rng.state = (uint64_t) __float_as_uint(q.x) | ((uint64_t) __float_as_uint(q.y) << 32); rng.inc = (uint64_t) __float_as_uint(q.z) | ((uint64_t) __float_as_uint(q.w) << 32); }
+            const Ray ray = primary_ray(p, ln, rng);
+            o[r] = ray.o; d[r] = ray.d; tbest[r] = ray.maxt; bu[r] = 0.f; bv[r] = 0.f; bface[r] = 0xffffffffu; bmesh[r] = 0u;
+            const float tiny = kTinyDir;
+            const float idx = 1.f / (fabsf(ray.d.x) > tiny ? ray.d.x : copysignf(tiny, ray.d.x));
+            const float idy = 1.f / (fabsf(ray.d.y) > tiny ? ray.d.y : copysignf(tiny, ray.d.y));
+            const float idz = 1.f / (fabsf(ray.d.z) > tiny ? ray.d.z : copysignf(tiny, ray.d.z));
+            ix0 = fminf(ix0, idx); ix1 = fmaxf(ix1, idx); iy0 = fminf(iy0, idy); iy1 = fmaxf(iy1, idy); iz0 = fminf(iz0, idz); iz1 = fmaxf(iz1, idz);
+            ox0 = fminf(ox0, ray.o.x); ox1 = fmaxf(ox1, ray.o.x); oy0 = fminf(oy0, ray.o.y); oy1 = fmaxf(oy1, ray.o.y); oz0 = fminf(oz0, ray.o.z); oz1 = fmaxf(oz1, ray.o.z);
+            tbest_w = fmaxf(tbest_w, ray.maxt);
+        }
+        cnt.add(C_CLOSEST, min(total - base, 32u * R) > (uint32_t) lane ? (min(total - base, 32u * R) - lane + 31u) / 32u : 0u);
+        // ---- intervals of the packet
+        ix0 = warp_min_f(ix0); ix1 = warp_max_f(ix1); iy0 = warp_min_f(iy0); iy1 = warp_max_f(iy1); iz0 = warp_min_f(iz0); iz1 = warp_max_f(iz1);
+        ox0 = warp_min_f(ox0); ox1 = warp_max_f(ox1); oy0 = warp_min_f(oy0); oy1 = warp_max_f(oy1); oz0 = warp_min_f(oz0); oz1 = warp_max_f(oz1);
+        tbest_w = __uint_as_float(__reduce_max_sync(full, __float_as_uint(tbest_w)));       // maxt >= 0: the bit patterns order like the values
+        // per axis: all rays travel towards + (pos), all towards - (neg), or mixed (the interval of directions contains 0).  On a mixed
+        // axis the rays fan out from the origin: a box above the origins is entered no earlier than (lo - o) / (largest d), a box below
+        // them no earlier than (hi - o) / (most negative d), and the axis bounds no exit.  Coded as pos with both reciprocals = 1 / largest d
+        // (entry term 1) and m = 1 / most negative d (entry term 2, applied to the exit plane).
+        const bool negx = ix1 < 0.f, negy = iy1 < 0.f, negz = iz1 < 0.f, mixx = !negx && !(ix0 > 0.f), mixy = !negy && !(iy0 > 0.f), mixz = !negz && !(iz0 > 0.f);
+        float mx = 0.f, my = 0.f, mz = 0.f;
+        const bool anymix = mixx || mixy || mixz;
+        if (anymix) {
+            const float tiny = kTinyDir;
+            float px = kPkInf, py = kPkInf, pz = kPkInf, qx = -kPkInf, qy = -kPkInf, qz = -kPkInf;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float ax = 1.f / (fabsf(d[r].x) > tiny ? d[r].x : copysignf(tiny, d[r].x)), ay = 1.f / (fabsf(d[r].y) > tiny ? d[r].y : copysignf(tiny, d[r].y)),
+                            az = 1.f / (fabsf(d[r].z) > tiny ? d[r].z : copysignf(tiny, d[r].z));
+                if (ax > 0.f) px = fminf(px, ax); else qx = fmaxf(qx, ax);
+                if (ay > 0.f) py = fminf(py, ay); else qy = fmaxf(qy, ay);
+                if (az > 0.f) pz = fminf(pz, az); else qz = fmaxf(qz, az);
+            }
+            px = warp_min_f(px); py = warp_min_f(py); pz = warp_min_f(pz); qx = warp_max_f(qx); qy = warp_max_f(qy); qz = warp_max_f(qz);
+            if (mixx) { ix0 = px; ix1 = px; mx = qx; }
+            if (mixy) { iy0 = py; iy1 = py; my = qy; }
+            if (mixz) { iz0 = pz; iz1 = pz; mz = qz; }
+        }
+        const uint32_t oct0 = __shfl_sync(full, (d[0].x >= 0.f ? 1u : 0u) | (d[0].y >= 0.f ? 2u : 0u) | (d[0].z >= 0.f ? 4u : 0u), 0);   // mixed axes: lane 0 decides the order
+        const uint32_t octinv = (mixx ? (oct0 & 1u) : negx ? 0u : 1u) | (mixy ? (oct0 & 2u) : negy ? 0u : 2u) | (mixz ? (oct0 & 4u) : negz ? 0u : 4u);
+        // padding of the child boxes: 1/8 grid cell (the builder's own margin is 1/64) + 2e-6 of the largest coordinate involved
+        const uint4 root = sc.n_nodes ? __ldg(sc.nodes) : make_uint4(0u, 0u, 0u, 0u);
+        const float kx = (fabsf(__uint_as_float(root.x)) + 256.f * __uint_as_float((root.w & 0xffu) << 23) + fmaxf(fabsf(ox0), fabsf(ox1))) * 2e-6f;
+        const float ky = (fabsf(__uint_as_float(root.y)) + 256.f * __uint_as_float(((root.w >> 8) & 0xffu) << 23) + fmaxf(fabsf(oy0), fabsf(oy1))) * 2e-6f;
+        const float kz = (fabsf(__uint_as_float(root.z)) + 256.f * __uint_as_float(((root.w >> 16) & 0xffu) << 23) + fmaxf(fabsf(oz0), fabsf(oz1))) * 2e-6f;
+        // entry plane = lo (pos) / hi (neg) against the origin bound that makes the entry earliest; exit plane likewise latest
+        const float onx = negx ? ox0 : ox1, ofx = negx ? ox1 : ox0, ony = negy ? oy0 : oy1, ofy = negy ? oy1 : oy0, onz = negz ? oz0 : oz1, ofz = negz ? oz1 : oz0;
+        // (32768 + q) * s + (g -+ k -+ (32768 +- 1/8) s) = g + (q -+ 1/8) s -+ k
+        const float cn_x = negx ? -32767.875f : -32768.125f, cf_x = negx ? -32768.125f : -32767.875f, kn_x = negx ? kx : -kx;
+        const float cn_y = negy ? -32767.875f : -32768.125f, cf_y = negy ? -32768.125f : -32767.875f, kn_y = negy ? ky : -ky;
+        const float cn_z = negz ? -32767.875f : -32768.125f, cf_z = negz ? -32768.125f : -32767.875f, kn_z = negz ? kz : -kz;
+
+        uint2 ng = sc.n_nodes ? make_uint2(0u, (1u << (24 + octinv)) | 1u) : make_uint2(0u, 0u);
+        int sp = 0;
+        for (;;) {
+            if ((ng.y & 0xff000000u) == 0u) { if (sp == 0) break; ng = stack[--sp]; }
+            const int bit = 31 - __clz(ng.y);
+            ng.y &= ~(1u << bit);
+            if (ng.y & 0xff000000u) { stack[sp] = ng; sp++; }          // depth <= kStackSize, guarded at build time
+            const uint32_t cslot = (uint32_t) (bit - 24) ^ octinv;
+            const uint32_t rel = __popc(ng.y & 0xffu & ~(0xffffffffu << cslot));
+            const uint4 *np = sc.nodes + (size_t) (ng.x + rel) * 5;
+            const uint4 w0 = __ldg(np), w1 = __ldg(np + 1), w2 = __ldg(np + 2), w3 = __ldg(np + 3), w4 = __ldg(np + 4);
+            if (lane == 0) cnt.add(C_NODES);
+            // child c of this node against the interval of the rays
+            const float sx = __uint_as_float((w0.w & 0xffu) << 23), sy = __uint_as_float(((w0.w >> 8) & 0xffu) << 23), sz = __uint_as_float(((w0.w >> 16) & 0xffu) << 23);
+            const float gx = __uint_as_float(w0.x), gy = __uint_as_float(w0.y), gz = __uint_as_float(w0.z);
+            const uint32_t lxw = chi ? w2.y : w2.x, lyw = chi ? w2.w : w2.z, lzw = chi ? w3.y : w3.x, hxw = chi ? w3.w : w3.z, hyw = chi ? w4.y : w4.x, hzw = chi ? w4.w : w4.z;
+            const float qnx = __uint_as_float(__byte_perm(negx ? hxw : lxw, sc.qmagic, psel)), qfx = __uint_as_float(__byte_perm(negx ? lxw : hxw, sc.qmagic, psel));
+            const float qny = __uint_as_float(__byte_perm(negy ? hyw : lyw, sc.qmagic, psel)), qfy = __uint_as_float(__byte_perm(negy ? lyw : hyw, sc.qmagic, psel));
+            const float qnz = __uint_as_float(__byte_perm(negz ? hzw : lzw, sc.qmagic, psel)), qfz = __uint_as_float(__byte_perm(negz ? lzw : hzw, sc.qmagic, psel));
+            const float nx = fmaf(qnx, sx, fmaf(cn_x, sx, (gx + kn_x) - onx)), fx = fmaf(qfx, sx, fmaf(cf_x, sx, (gx - kn_x) - ofx));
+            const float ny = fmaf(qny, sy, fmaf(cn_y, sy, (gy + kn_y) - ony)), fy = fmaf(qfy, sy, fmaf(cf_y, sy, (gy - kn_y) - ofy));
+            const float nz = fmaf(qnz, sz, fmaf(cn_z, sz, (gz + kn_z) - onz)), fz = fmaf(qfz, sz, fmaf(cf_z, sz, (gz - kn_z) - ofz));
+            float tnx = fminf(nx * ix0, nx * ix1), tny = fminf(ny * iy0, ny * iy1), tnz = fminf(nz * iz0, nz * iz1);
+            float tfx = fmaxf(fx * ix0, fx * ix1), tfy = fmaxf(fy * iy0, fy * iy1), tfz = fmaxf(fz * iz0, fz * iz1);
+            if (anymix) {
+                if (mixx) { tfx = kPkInf; tnx = fmaxf(tnx, fx * mx); }
+                if (mixy) { tfy = kPkInf; tny = fmaxf(tny, fy * my); }
+                if (mixz) { tfz = kPkInf; tnz = fmaxf(tnz, fz * mz); }
+            }
+            float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.f));
+            float tf = fminf(fminf(tfx, tfy), fminf(tfz, tbest_w * kFarPad));
+            tn *= 0.999995f; tf = fmaf(fabsf(tf), 5e-6f, tf);
+            const uint32_t mw = ((chi ? w1.w : w1.z) >> csh) & 0xffu;
+            const uint32_t mine = (lane < 8 && !(tn > tf)) ? __funnelshift_l(0u, (mw >> 5) & 7u, mw) : 0u;
+            const uint32_t hitmask = __reduce_or_sync(full, mine);
+            ng = make_uint2(w1.x, (permute_octant(hitmask, octinv) << 24) | (w0.w >> 24));
+            uint32_t tm = hitmask & 0x00ffffffu;
+            if (tm) {
+                const float4 *tb = sc.tris + (size_t) w1.y * 3;
+                float tw = 0.f;
+                do {
+                    const int i = __ffs(tm) - 1;
+                    tm &= tm - 1;
+                    const float4 *tp = tb + i * 3;
+                    const float4 r0 = __ldg(tp), r1 = __ldg(tp + 1), r2 = __ldg(tp + 2);
+                    cnt.add(C_TRIS, R);
+                    const f3 e1(r1.x, r1.y, r1.z), e2(r2.x, r2.y, r2.z), p0(r0.x, r0.y, r0.z);
+                    const uint32_t face = __float_as_uint(r0.w);
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        // Mesh::moeller_trumbore (mesh.h:469-492), operation for operation as in k_wf_trace
+                        const f3 pvec = cross(d[r], e2);
+                        const float inv_det = rcp(dot(e1, pvec));
+                        const f3 tvec = o[r] - p0;
+                        const float u = dot(tvec, pvec) * inv_det;
+                        bool ok = u >= 0.f && u <= 1.f;
+                        const f3 qvec = cross(tvec, e1);
+                        const float v = dot(d[r], qvec) * inv_det;
+                        ok = ok && v >= 0.f && u + v <= 1.f;
+                        const float t = dot(e2, qvec) * inv_det;
+                        ok = ok && t >= 0.f && t <= tbest[r];
+                        if (ok && (t < tbest[r] || face < bface[r])) { tbest[r] = t; bu[r] = u; bv[r] = v; bface[r] = face; bmesh[r] = __float_as_uint(r1.w); }
+                    }
+                } while (tm);
+#pragma unroll
+                for (int r = 0; r < R; ++r) tw = fmaxf(tw, tbest[r]);
+                tbest_w = __uint_as_float(__reduce_max_sync(full, __float_as_uint(tw)));
+            }
+        }
+        // ---- epilogue: the hit record and the class byte of each ray (queue position = lane slot on bounce 0)
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const uint32_t e = base + 32u * r + lane;
+            if (e < total) {
+                const bool found = bface[r] != 0xffffffffu;
+                const uint32_t cls = found ? (bmesh[r] >> 28) : (uint32_t) CLS_MISS;
+                Elem h;
+                h.a = make_float4(tbest[r], bu[r], bv[r], __uint_as_float(bface[r]));
+                h.b = make_float4(__uint_as_float(found ? (bmesh[r] & 0x0fffffffu) : 0xffffffffu), __uint_as_float(cls), 0.f, 0.f);
+                st256(&st.hit[e], h);
+                st.cls_q[e] = (uint8_t) cls;
+            }
+        }
+    }
+    trace_flush_counters(cnt, p.counters);
+}
+
 int wf_trace_blocks(bool count, int sm_count) {
     int occ = 0;
     if (count) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, false>, kTraceThreads, 0);
@@ -249,9 +439,14 @@ int wf_trace_blocks(bool count, int sm_count) {
     return occ * sm_count;
 }
 
+// B2_PRIMARY_PACKET=0 traces bounce 0 with the per-ray kernel (k_wf_trace<., true>) instead of the packet kernel
+static bool primary_packet() { const char *e = getenv("B2_PRIMARY_PACKET"); return !(e && atoi(e) == 0); }
+
 void wf_launch_trace(bool count, bool primary, const RenderParams &p, const WfLaunch &w, int blocks, cudaStream_t stream) {
     wf_tm_begin(WF_K_TRACE, stream);
-    if (count) { if (primary) k_wf_trace<true, true><<<blocks, kTraceThreads, 0, stream>>>(p, w); else k_wf_trace<true, false><<<blocks, kTraceThreads, 0, stream>>>(p, w); }
+    if (primary && primary_packet()) {
+        if (count) k_wf_trace_packet<true, B2_PACKET_RAYS><<<blocks, kPacketThreads, 0, stream>>>(p, w); else k_wf_trace_packet<false, B2_PACKET_RAYS><<<blocks, kPacketThreads, 0, stream>>>(p, w);
+    } else if (count) { if (primary) k_wf_trace<true, true><<<blocks, kTraceThreads, 0, stream>>>(p, w); else k_wf_trace<true, false><<<blocks, kTraceThreads, 0, stream>>>(p, w); }
     else { if (primary) k_wf_trace<false, true><<<blocks, kTraceThreads, 0, stream>>>(p, w); else k_wf_trace<false, false><<<blocks, kTraceThreads, 0, stream>>>(p, w); }
     wf_tm_end(stream);
 }

@@ -153,7 +153,7 @@ def test_triangle_soup_render_parity(kernel):
 
 
 @pytest.mark.parametrize("variant", [0, 1, 2])
-def test_wavefront_equals_megakernel(variant):
+def test_wavefront_equals_megakernel(variant, monkeypatch):
     """Both kernel organisations run the same per-lane arithmetic: images agree up to the film's fp32 summation order,
     event counters agree exactly."""
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
@@ -162,6 +162,12 @@ def test_wavefront_equals_megakernel(variant):
     a, ca = ds.render(counters=True, kernel=0, all_shadow_rays=True, **kw)
     b, cb = ds.render(counters=True, kernel=1, **kw)
     np.testing.assert_allclose(a.cpu().numpy(), b.cpu().numpy(), rtol=2e-5, atol=1e-6)
+    # bounce 0 through the per-ray trace kernel instead of the packet kernel: same image; its traversal counters are the ones
+    # comparable with the megakernel's (the packet kernel counts one node fetch per warp and the union of the warp's triangles)
+    monkeypatch.setenv("B2_PRIMARY_PACKET", "0")
+    a0, ca = ds.render(counters=True, kernel=0, all_shadow_rays=True, **kw)
+    monkeypatch.delenv("B2_PRIMARY_PACKET")
+    np.testing.assert_allclose(a0.cpu().numpy(), a.cpu().numpy(), rtol=2e-5, atol=1e-6)
     # default product path: shadow rays of emitter samples whose value is exactly zero are not traced -- same image
     e, ce = ds.render(counters=True, kernel=0, **kw)
     np.testing.assert_allclose(e.cpu().numpy(), a.cpu().numpy(), rtol=2e-5, atol=1e-6)
