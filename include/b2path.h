@@ -29,6 +29,7 @@
  *   b2_kernel_times        <- dr.kernel_history() as printed by path.py:332-351
  *   b2_trace               <- Scene::ray_intersect_preliminary / ray_test (mi3/src/render/scene.cpp:191-235)
  *   b2_debug_sampler       <- PCG32Sampler::seed + next_1d (mi3/src/render/sampler.cpp:129-148, samplers/independent.cpp:88-97)
+ *   b2_debug_primary_hits  <- SamplingIntegrator::sample_rays + Scene::ray_intersect_preliminary (integrator.cpp:419-436, scene.cpp:191-214)
  *   b2_trace_noalloc       <- no counterpart in the reference
  */
 #ifndef B2PATH_H
@@ -264,6 +265,13 @@ int  b2_trace_noalloc(b2_scene *scene, const float *rays_dev, uint64_t n, int an
    when it is not NULL.  `args` supplies seed / spp (lane -> pixel); nothing is rendered. */
 int  b2_debug_sampler(b2_scene *scene, const b2_render_args *args, uint64_t lane_begin, uint32_t n_lanes, uint32_t n_draws,
                       float *out_dev, float *pos_dev, uintptr_t stream);
+/* unit-test hook for the bounce-0 trace: hits_dev [n_lanes] = the closest hit of the primary ray of lanes lane_begin ..
+   lane_begin + n_lanes - 1 of pass 0 (sample position from the lane's stream, sensor ray: integrator.cpp:293-310,419-436,
+   perspective.cpp:239-280; Scene::ray_intersect_preliminary, scene.cpp:191-214).  kernel 1 / 2 = the packet kernel the renders use
+   for bounce 0 from 8 samples per pixel on (one warp-uniform traversal per 32 / 64 consecutive lanes), kernel 0 = the per-ray trace
+   kernel: all must agree bit for bit.  `args` supplies seed / spp / sample shard; nothing is rendered. */
+int  b2_debug_primary_hits(b2_scene *scene, const b2_render_args *args, uint64_t lane_begin, uint32_t n_lanes, int kernel,
+                           b2_hit *hits_dev, uintptr_t stream);
 /* host-buffer convenience entry points (what a reference-side binding with host arrays calls):
    upload/download happen inside; film_rgbw_host is accumulated into */
 int  b2_render_host(b2_scene *scene, const b2_render_args *args, float *film_rgbw_host, float *image_rgb_host, b2_counters *counters);

@@ -113,7 +113,7 @@ class GradTarget(C.Structure):
 
 # every symbol include/b2path.h declares for the product library
 EXPORTS = ["b2_init", "b2_shutdown", "b2_scene_create", "b2_scene_destroy", "b2_scene_build_accel",
-           "b2_scene_set_param", "b2_render", "b2_develop", "b2_render_backward", "b2_render_forward", "b2_trace", "b2_trace_noalloc", "b2_debug_sampler",
+           "b2_scene_set_param", "b2_render", "b2_develop", "b2_render_backward", "b2_render_forward", "b2_trace", "b2_trace_noalloc", "b2_debug_sampler", "b2_debug_primary_hits",
            "b2_render_host", "b2_set_kernel_timing", "b2_kernel_times", "b2_last_error", "b2_abi_version"]
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -162,13 +162,14 @@ def load_library() -> C.CDLL:
     lib.b2_trace.argtypes = [vp, vp, u64, C.c_int, vp, up]
     lib.b2_trace_noalloc.argtypes = [vp, vp, u64, C.c_int, vp, up]
     lib.b2_debug_sampler.argtypes = [vp, C.POINTER(RenderArgs), u64, C.c_uint32, C.c_uint32, vp, vp, up]
+    lib.b2_debug_primary_hits.argtypes = [vp, C.POINTER(RenderArgs), u64, C.c_uint32, C.c_int, vp, up]
     lib.b2_render_host.argtypes = [vp, C.POINTER(RenderArgs), vp, vp, C.POINTER(Counters)]
     lib.b2_set_kernel_timing.argtypes = [vp, C.c_int]
     lib.b2_kernel_times.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(u64)]
     lib.b2_last_error.restype = C.c_char_p
     lib.b2_abi_version.restype = C.c_int
     for name in ("b2_init", "b2_scene_create", "b2_scene_build_accel", "b2_scene_set_param", "b2_render",
-                 "b2_develop", "b2_render_backward", "b2_render_forward", "b2_trace", "b2_trace_noalloc", "b2_debug_sampler", "b2_render_host", "b2_set_kernel_timing", "b2_kernel_times"):
+                 "b2_develop", "b2_render_backward", "b2_render_forward", "b2_trace", "b2_trace_noalloc", "b2_debug_sampler", "b2_debug_primary_hits", "b2_render_host", "b2_set_kernel_timing", "b2_kernel_times"):
         getattr(lib, name).restype = C.c_int
     if lib.b2_abi_version() != B2_ABI_VERSION:
         raise B2Error("libb2path.so ABI version mismatch")

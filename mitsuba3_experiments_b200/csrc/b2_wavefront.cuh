@@ -88,6 +88,7 @@ void wf_tm_end(cudaStream_t st);
 // trace launches (wf_trace.cu).  primary: rays of bounce 0 come from the sensor (needs the full RenderParams).
 int wf_trace_blocks(bool count, int sm_count);          // resident grid of the persistent trace kernel (0 = cannot be resident)
 void wf_launch_trace(bool count, bool primary, const RenderParams &p, const WfLaunch &w, int blocks, cudaStream_t stream);
+void wf_launch_trace_primary(int packet_rays, const RenderParams &p, const WfLaunch &w, int blocks, cudaStream_t stream);   // bounce 0 with an explicit kernel: 0 per-ray, 1 / 2 = packets of 32 / 64 lanes
 
 // host entry points (wavefront.cu)
 size_t wf_state_bytes(uint32_t capacity);
@@ -104,6 +105,8 @@ long wf_trace_rays(RenderParams p, WfState &st, const float *rays, uint64_t n, i
 constexpr uint64_t kNoAllocMaxRays = 32768;
 long wf_trace_rays_noalloc(RenderParams p, uint32_t class_mask, int device, const float *rays, uint64_t n, int any_hit, b2_hit *hits,
                            int sm_count, cudaStream_t stream, const char **err);
+// b2_debug_primary_hits: the bounce-0 trace alone for lanes [lane_begin, lane_begin + n) of pass 0; packet = rays per lane of k_wf_trace_packet (1, 2), 0 = k_wf_trace<., true>
+long wf_trace_primary(RenderParams p, WfState &st, uint64_t lane_begin, uint32_t n, int packet, b2_hit *hits, int sm_count, cudaStream_t stream, const char **err);
 long wf_weights(RenderParams p, int sm_count, cudaStream_t stream, const char **err);
 long wf_render(int variant, bool count, RenderParams p, WfState &st, int sm_count, cudaStream_t stream, const char **err);
 

@@ -650,6 +650,24 @@ int b2_debug_sampler(b2_scene *s, const b2_render_args *a, uint64_t lane_begin, 
     return 0;
 }
 
+int b2_debug_primary_hits(b2_scene *s, const b2_render_args *a, uint64_t lane_begin, uint32_t n_lanes, int kernel, b2_hit *hits, uintptr_t stream) {
+    if (!s || !a || (n_lanes && !hits)) return fail(-1, "b2_debug_primary_hits: null argument");
+    CUDA_OK(cudaSetDevice(s->ctx->device));
+    RenderParams p; int blocks; size_t smem;
+    if (int rc = setup_params(s, a, MODE_WEIGHTS, false, p, blocks, smem, 0, 0)) return rc;
+    if (lane_begin + n_lanes > p.lane_end) return fail(-2, "b2_debug_primary_hits: lanes beyond the wavefront of the pass");
+    if (kernel < 0 || kernel > 2) return fail(-2, "b2_debug_primary_hits: kernel must be 0 (per ray), 1 or 2 (packets of 32 / 64 lanes)");
+    if (n_lanes) {
+        if (int rc = wf_reserve(s, n_lanes, 0, (cudaStream_t) stream)) return rc;
+        const char *err = nullptr;
+        const long l = wf_trace_primary(p, s->wf, lane_begin, n_lanes, kernel, hits, s->ctx->sm_count, (cudaStream_t) stream, &err);
+        if (l < 0) return fail(-11, err ? err : "primary trace failed");
+        s->launches += (uint64_t) l;
+    }
+    CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
 int b2_render_host(b2_scene *s, const b2_render_args *a, float *film_host, float *image_host, b2_counters *counters) {
     if (!s || !a || !film_host) return fail(-1, "b2_render_host: null argument");
     CUDA_OK(cudaSetDevice(s->ctx->device));

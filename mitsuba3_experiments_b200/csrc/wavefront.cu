@@ -583,6 +583,19 @@ long wf_trace_rays(RenderParams p, WfState &st, const float *rays, uint64_t n, i
     return launches;
 }
 
+long wf_trace_primary(RenderParams p, WfState &st, uint64_t lane_begin, uint32_t n, int packet, b2_hit *hits, int sm_count, cudaStream_t stream, const char **err) {
+    const int g_trace = wf_trace_blocks(false, sm_count);
+    if (g_trace <= 0) { *err = "wavefront: the trace kernel cannot be resident"; return -1; }
+    if (n > st.capacity) { *err = "wavefront: more lanes than the reserved state holds"; return -1; }
+    WfLaunch w = wf_launch_defaults(st, lane_begin, n); w.it = 0; w.first = 1u;
+    const int g = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) sm_count * 8);
+    cudaMemsetAsync(st.ctl, 0, sizeof(WfCtl), stream);
+    wf_launch_trace_primary(packet, p, w, g_trace, stream);
+    k_wf_hits_out<<<g, 256, 0, stream>>>(w, nullptr, 0, hits);
+    if (cudaGetLastError() != cudaSuccess) { *err = "wavefront: kernel launch failed"; return -1; }
+    return 2;
+}
+
 long wf_render_backward(bool count, RenderParams p, WfState &st, void *hit_history, int sm_count, cudaStream_t stream, const char **err) {
     return count ? wf_render_backward_t<true>(p, st, (Elem *) hit_history, sm_count, stream, err) : wf_render_backward_t<false>(p, st, (Elem *) hit_history, sm_count, stream, err);
 }

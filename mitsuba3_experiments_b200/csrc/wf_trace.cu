@@ -254,9 +254,6 @@ B2_DEV float warp_max_f(float f) { return __int_as_float(f_ord(__reduce_max_sync
 
 constexpr int kPacketThreads = 256;
 constexpr float kPkInf = 3.402823466e38f;
-#ifndef B2_PACKET_RAYS
-#define B2_PACKET_RAYS 2                  // rays per lane: a packet is 32 * B2_PACKET_RAYS consecutive lanes
-#endif
 #ifndef B2_PACKET_MINBLOCKS
 #define B2_PACKET_MINBLOCKS 4
 #endif
@@ -276,17 +273,25 @@ __global__ void __launch_bounds__(kPacketThreads, B2_PACKET_MINBLOCKS) k_wf_trac
     uint32_t next = 0;
     if (lane == 0) next = atomicAdd(fetch, 32u * R);
     for (;;) {
-        const uint32_t base = __shfl_sync(full, next, 0);
-        if (base >= total) break;
+        const uint32_t batch = __shfl_sync(full, next, 0);
+        if (batch >= total) break;
         if (lane == 0) next = atomicAdd(fetch, 32u * R);
-        // ---- the lane's rays (as stage C of k_wf_trace<., true>); lanes past the end repeat the last ray and store nothing
+        const uint32_t batch_end = min(batch + 32u * R, total);
+        // a batch is cut where an image row ends (the rays of two rows are the left and the right edge of the frustum: their interval
+        // would span the whole width); each piece [base, end) is one packet
+        for (uint32_t base = batch, end; base < batch_end; base = end) {
+        {
+            const uint64_t row_lanes = (uint64_t) p.sc.sensor.grid_w * p.spp_per_pass, l0 = w.chunk_begin + base;
+            end = (uint32_t) min((uint64_t) batch_end, (l0 / row_lanes + 1u) * row_lanes - w.chunk_begin);
+        }
+        // ---- the lane's rays (as stage C of k_wf_trace<., true>); lanes past the end of the packet repeat its last ray and store nothing
         f3 o[R], d[R]; float tbest[R], bu[R], bv[R]; uint32_t bface[R], bmesh[R];
         float ix0 = kPkInf, ix1 = -kPkInf, iy0 = kPkInf, iy1 = -kPkInf, iz0 = kPkInf, iz1 = -kPkInf;
         float ox0 = kPkInf, ox1 = -kPkInf, oy0 = kPkInf, oy1 = -kPkInf, oz0 = kPkInf, oz1 = -kPkInf;
         float tbest_w = 0.f;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const uint32_t e = min(base + 32u * r + lane, total - 1u);
+            const uint32_t e = min(base + 32u * r + lane, end - 1u);
             Pcg32 rng;
             const uint32_t ln = (uint32_t) (w.chunk_begin + e);
             if (w.pass == 0) rng.seed_lane(p.seed, global_lane(p, ln));
@@ -301,7 +306,7 @@ __global__ void __launch_bounds__(kPacketThreads, B2_PACKET_MINBLOCKS) k_wf_trac
             ox0 = fminf(ox0, ray.o.x); ox1 = fmaxf(ox1, ray.o.x); oy0 = fminf(oy0, ray.o.y); oy1 = fmaxf(oy1, ray.o.y); oz0 = fminf(oz0, ray.o.z); oz1 = fmaxf(oz1, ray.o.z);
             tbest_w = fmaxf(tbest_w, ray.maxt);
         }
-        cnt.add(C_CLOSEST, min(total - base, 32u * R) > (uint32_t) lane ? (min(total - base, 32u * R) - lane + 31u) / 32u : 0u);
+        cnt.add(C_CLOSEST, end - base > (uint32_t) lane ? (end - base - lane + 31u) / 32u : 0u);
         // ---- intervals of the packet
         ix0 = warp_min_f(ix0); ix1 = warp_max_f(ix1); iy0 = warp_min_f(iy0); iy1 = warp_max_f(iy1); iz0 = warp_min_f(iz0); iz1 = warp_max_f(iz1);
         ox0 = warp_min_f(ox0); ox1 = warp_max_f(ox1); oy0 = warp_min_f(oy0); oy1 = warp_max_f(oy1); oz0 = warp_min_f(oz0); oz1 = warp_max_f(oz1);
@@ -416,7 +421,7 @@ __global__ void __launch_bounds__(kPacketThreads, B2_PACKET_MINBLOCKS) k_wf_trac
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const uint32_t e = base + 32u * r + lane;
-            if (e < total) {
+            if (e < end) {
                 const bool found = bface[r] != 0xffffffffu;
                 const uint32_t cls = found ? (bmesh[r] >> 28) : (uint32_t) CLS_MISS;
                 Elem h;
@@ -426,6 +431,7 @@ __global__ void __launch_bounds__(kPacketThreads, B2_PACKET_MINBLOCKS) k_wf_trac
                 st.cls_q[e] = (uint8_t) cls;
             }
         }
+        }   // pieces of the batch
     }
     trace_flush_counters(cnt, p.counters);
 }
@@ -439,16 +445,31 @@ int wf_trace_blocks(bool count, int sm_count) {
     return occ * sm_count;
 }
 
-// B2_PRIMARY_PACKET=0 traces bounce 0 with the per-ray kernel (k_wf_trace<., true>) instead of the packet kernel
-static bool primary_packet() { const char *e = getenv("B2_PRIMARY_PACKET"); return !(e && atoi(e) == 0); }
+// Bounce 0: rays per lane of the packet kernel (0 = the per-ray kernel k_wf_trace<., true>).  A packet of 32 R consecutive lanes spans
+// 32 R / spp pixels of a row; the wider it is, the more of the tree it visits that its single rays would not.  Measured on the bedroom
+// stand-in, 1280 x 720 (profiles/README.md): 64-lane packets win from 8 samples per pixel on (8 pixels per packet: 10.8 vs 11.2 ms; 64 spp:
+// 66.2 vs 73.0 ms), 32-lane packets at 4 .. 7 (6.60 vs 6.74 ms), the per-ray kernel below that (1 spp: 3.5 vs 7.9 ms).
+// B2_PRIMARY_PACKET = 0 / 1 / 2 forces the choice (tests, experiments).
+static int primary_packet_rays(const RenderParams &p) {
+    if (const char *e = getenv("B2_PRIMARY_PACKET")) return std::max(0, std::min(2, atoi(e)));
+    return p.spp_per_pass >= 8u ? 2 : p.spp_per_pass >= 4u ? 1 : 0;
+}
 
-void wf_launch_trace(bool count, bool primary, const RenderParams &p, const WfLaunch &w, int blocks, cudaStream_t stream) {
+static void launch_trace(bool count, bool primary, int packet_rays, const RenderParams &p, const WfLaunch &w, int blocks, cudaStream_t stream) {
     wf_tm_begin(WF_K_TRACE, stream);
-    if (primary && primary_packet()) {
-        if (count) k_wf_trace_packet<true, B2_PACKET_RAYS><<<blocks, kPacketThreads, 0, stream>>>(p, w); else k_wf_trace_packet<false, B2_PACKET_RAYS><<<blocks, kPacketThreads, 0, stream>>>(p, w);
+    if (primary && packet_rays == 2) {
+        if (count) k_wf_trace_packet<true, 2><<<blocks, kPacketThreads, 0, stream>>>(p, w); else k_wf_trace_packet<false, 2><<<blocks, kPacketThreads, 0, stream>>>(p, w);
+    } else if (primary && packet_rays == 1) {
+        if (count) k_wf_trace_packet<true, 1><<<blocks, kPacketThreads, 0, stream>>>(p, w); else k_wf_trace_packet<false, 1><<<blocks, kPacketThreads, 0, stream>>>(p, w);
     } else if (count) { if (primary) k_wf_trace<true, true><<<blocks, kTraceThreads, 0, stream>>>(p, w); else k_wf_trace<true, false><<<blocks, kTraceThreads, 0, stream>>>(p, w); }
     else { if (primary) k_wf_trace<false, true><<<blocks, kTraceThreads, 0, stream>>>(p, w); else k_wf_trace<false, false><<<blocks, kTraceThreads, 0, stream>>>(p, w); }
     wf_tm_end(stream);
+}
+void wf_launch_trace(bool count, bool primary, const RenderParams &p, const WfLaunch &w, int blocks, cudaStream_t stream) {
+    launch_trace(count, primary, primary ? primary_packet_rays(p) : 0, p, w, blocks, stream);
+}
+void wf_launch_trace_primary(int packet_rays, const RenderParams &p, const WfLaunch &w, int blocks, cudaStream_t stream) {
+    launch_trace(false, true, packet_rays, p, w, blocks, stream);
 }
 
 }  // namespace b2

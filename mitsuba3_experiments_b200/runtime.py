@@ -194,6 +194,16 @@ class DeviceScene:
         torch.cuda.synchronize(self.device)
         return out.cpu().numpy(), pos.cpu().numpy()
 
+    def debug_primary_hits(self, lane_begin, n_lanes, kernel=1, **kw):
+        """Unit-test hook: closest hits of the primary rays of lanes ``lane_begin .. lane_begin + n_lanes`` (pass 0), through the
+        packet kernel renders use for bounce 0 (``kernel=1`` / ``2``: packets of 32 / 64 lanes) or the per-ray trace kernel (``kernel=0``)."""
+        torch = _torch()
+        a = self.make_args(**kw)
+        hits = torch.empty((n_lanes, 4), dtype=torch.float32, device=self.device)
+        capi.check(self.lib.b2_debug_primary_hits(self.handle, C.byref(a), int(lane_begin), int(n_lanes), int(kernel), hits.data_ptr(), self._stream()))
+        torch.cuda.synchronize(self.device)
+        return hits.cpu().numpy().view(np.dtype([("t", "f4"), ("u", "f4"), ("v", "f4"), ("prim", "u4")])).reshape(-1)
+
     def set_kernel_timing(self, enabled: bool):
         """Kernel history (``dr.kernel_history`` analogue): bracket every wavefront launch with CUDA events."""
         capi.check(self.lib.b2_set_kernel_timing(self.handle, int(bool(enabled))))

@@ -89,6 +89,30 @@ def test_trace_bit_exact(scene_name, builder, kernel):
     assert np.array_equal(ga["prim"], ca["prim"])
 
 
+@pytest.mark.parametrize("scene_name", ["cornell", "materials", "soup"])
+def test_primary_packet_trace_bit_exact(scene_name):
+    """Bounce 0 of every render goes through k_wf_trace_packet (from 8 samples per pixel on): one warp-uniform traversal per 32 or 64 consecutive lanes, children
+    culled against the interval of the packet's rays, per-ray Moeller-Trumbore.  The closest hit of a ray is the minimum of
+    (t, face) over the triangles it intersects, whatever the traversal, so (t, u, v, prim) must equal the per-ray trace kernel's
+    bit for bit: for whole images (packets around the image centre contain rays of both signs on an axis), for 1 .. 64 samples
+    per pixel (one sample: a packet spans 64 pixels and the row ends), ragged lane ranges and sample shards."""
+    torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
+    d = {"cornell": lambda: cornell_box(40, 32), "materials": lambda: materials_scene(56, 40, 4, envmap=True), "soup": lambda: triangles_scene(30000, 48, 36)}[scene_name]()
+    ds = DeviceScene(d)
+    w, h = {"cornell": (40, 32), "materials": (56, 40), "soup": (48, 36)}[scene_name]
+    some_hit = False
+    for spp, kw in ((1, {}), (3, {}), (16, {}), (64, {}), (64, dict(sample_begin=24, sample_count=24)), (5, dict(sample_begin=2, sample_count=3))):
+        n = w * h * kw.get("sample_count", spp)
+        for lane0, cnt in ((0, n), (37, min(n - 37, 1000 + 13)), (n - 65, 65), (n // 2 + 5, 1)):
+            b = ds.debug_primary_hits(lane0, cnt, kernel=0, seed=5, spp=spp, **kw)
+            for kernel in (1, 2):
+                a = ds.debug_primary_hits(lane0, cnt, kernel=kernel, seed=5, spp=spp, **kw)
+                for f in ("prim", "t", "u", "v"):
+                    assert np.array_equal(a[f].view(np.uint32), b[f].view(np.uint32)), (scene_name, spp, kw, lane0, cnt, kernel, f)
+            some_hit |= bool((a["prim"] != 0xffffffff).any())
+    assert some_hit
+
+
 @pytest.mark.parametrize("builder", BUILDERS)
 def test_bvh_stats_and_edge_cases(builder):
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
