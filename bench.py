@@ -11,8 +11,9 @@ RGBW film, the films are summed with one NCCL all-reduce, the result is develope
 Prints ONE JSON line (rank 0):
   value        device-timed throughput with the scene resident in HBM (CUDA events, max over ranks)
   e2e          the same metric through the host-buffer C-ABI call (film H2D + render + develop + film / image D2H timed)
-  roofline     the dominant kernel, k_wf_trace: algorithmic bytes = rays x B_ray (exact ray counters) over the
-               CUDA-event time of its launches inside the timed region, against the measured HBM copy bandwidth
+  roofline     the dominant kernel, k_wf_trace on the rays of bounces >= 1: algorithmic bytes = rays x B_ray (exact ray
+               counters) over the CUDA-event time of its launches inside the timed region, against the measured HBM copy bandwidth;
+               bounce 0 (k_wf_trace_packet, one traversal per 64 lanes) is timed alone and reported beside it
   cpu_baseline the CPU oracle (a port of the reference's llvm_ad_rgb path; Mitsuba itself cannot be installed here) on a
                bounded sample of the same workload; the same oracle image is the checker of the `parity` record
   parity       CUDA vs oracle on the benchmark scene itself (same seed, the cpu_baseline sample) + converged relMSE of C1
@@ -261,6 +262,16 @@ def main():
     barrier()
     ktimes = ds.kernel_times(); ds.set_kernel_timing(False)
     clk = clocks.result()
+    # bounce 0 goes through the packet variant of the trace kernel (k_wf_trace_packet): time that launch alone (same lanes, max_depth 1,
+    # untimed region, L2 flushed) so that the roofline of the dominant kernel -- k_wf_trace on the incoherent rays of bounces >= 1 -- excludes it
+    kw_primary = dict(kw, max_depth=1)
+    for i in range(2 + args.steps):
+        if i == 2:
+            ds.set_kernel_timing(True); ds.kernel_times()
+        flush.zero_(); film.zero_()
+        for a, b in plan:
+            ds.render_film(film=film, seed=0, spp=spp, lane_begin=a, lane_end=b, **shard_kw, **kw_primary)
+    primary_ms, primary_n = ds.kernel_times()["trace"]; ds.set_kernel_timing(False)
     step_ms = [e0.elapsed_time(e2) for e0, _, e2 in ev]
     kern_ms = [e0.elapsed_time(e1) for e0, e1, _ in ev]
     ms_per_step, kernel_ms = max_over_ranks([np.mean(step_ms), np.mean(kern_ms)])
@@ -303,8 +314,11 @@ def main():
         return
     peak, peak_kind = measured_peak()
     alg_bytes, b_ray = algorithmic_bytes(cnt, ds.desc.c.n_faces)
-    tr_ms, tr_n = ktimes["trace"]                           # summed over the timed steps
-    tr_bytes_step = trace_bytes(cnt, ds.desc.c.n_faces)
+    tr_all_ms, tr_all_n = ktimes["trace"]                   # summed over the timed steps, bounce 0 (packet kernel) included
+    primary_n = args.steps * len(plan)                      # (a max_depth 1 render also makes an empty second trace launch: its few us stay in primary_ms)
+    tr_ms, tr_n = tr_all_ms - primary_ms, tr_all_n - primary_n
+    primary_rays = cnt["samples"]                           # one primary ray per path
+    tr_bytes_step = trace_bytes(cnt, ds.desc.c.n_faces) - primary_rays * ray_bytes(ds.desc.c.n_faces)
     tr_ms_launch = tr_ms / max(tr_n, 1)
     achieved = tr_bytes_step * args.steps / (tr_ms * 1e-3) / 1e9 if tr_ms > 0 else 0.0
     step_gbs = alg_bytes / (kernel_ms * 1e-3) / 1e9
@@ -338,9 +352,13 @@ def main():
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "kernel": "k_wf_trace", "kernel_ms_per_launch": tr_ms_launch, "launches_per_step": tr_n // max(args.steps, 1),
                      "kernel_share_of_step": tr_ms / max(args.steps, 1) / kernel_ms,
+                     "rays_per_step": cnt["closest_rays"] + cnt["shadow_rays"] - primary_rays,
+                     "bounce0_packet_kernel": {"kernel": "k_wf_trace_packet", "ms_per_launch": primary_ms / max(primary_n, 1), "launches_per_step": primary_n // max(args.steps, 1),
+                                               "rays_per_step": primary_rays, "model_GBps_at_bytes_per_ray": primary_rays * ray_bytes(ds.desc.c.n_faces) / max(primary_ms / max(args.steps, 1) * 1e-3, 1e-12) / 1e9,
+                                               "note": "timed alone (max_depth 1 run of the same lanes); one traversal per 64 consecutive lanes, so its real node traffic is ~1/64 of the per-ray model"},
                      "algorithmic_bytes_per_launch": tr_bytes_step / max(tr_n // max(args.steps, 1), 1), "bytes_per_ray": b_ray, "peak_kind": peak_kind,
                      "whole_step": {"achieved": step_gbs, "frac": step_gbs / peak, "algorithmic_bytes": alg_bytes, "render_ms": kernel_ms,
-                                    "ms_per_step_by_kind": {k: v[0] / max(args.steps, 1) for k, v in ktimes.items()},
+                                    "ms_per_step_by_kind": {k: v[0] / max(args.steps, 1) for k, v in ktimes.items()}, "trace_ms_bounce0": primary_ms / max(args.steps, 1),
                                     "dram_bytes_per_step_by_kind": dram_by_kind},
                      "note": "irregular gathers: nodes + triangles (100 MB) stay L2-resident on B200, so DRAM traffic is below the algorithmic bytes; the binding limit of k_wf_trace is the ALU pipe / SIMT efficiency, not DRAM (profiles/README.md, DESIGN.md 4.3)"},
     }
