@@ -148,6 +148,62 @@ B2_DEV uint32_t film_taps_group(const RenderParams &p, f2 pos, f3 L, bool valid,
     return valid ? nx * ny : 0u;
 }
 
+// Butterfly variant of film_taps_group for pixel groups of G = 8 / 16 / 32 adjacent lanes and a C x C footprint (C = 3, 5; RGBW).
+// The 4 C^2 tap values of a lane are reduced G at a time by a transposing butterfly -- G - 1 shuffles per G values instead of
+// G log2 G -- after which lane j of the group holds the group's sum of value j = (tap j >> 2, channel j & 3) and adds it itself:
+// one add per lane and chunk, in parallel, instead of 4 C^2 serial ones by the group's leader (fp32 adds to shared memory are
+// compare-and-swap loops).  C^2 is odd and G / 4 even: exactly one tap is left over and goes the xor-reduction way.
+// add1(x, y, channel, value) receives crop-relative in-bounds coordinates.  Returns this lane's own in-bounds tap count.
+template <int G, int C, class ADD1>
+B2_DEV uint32_t film_taps_bfly(const RenderParams &p, f2 pos, f3 L, bool valid, uint32_t lid, ADD1 &&add1) {
+    const DSensor &s = p.sc.sensor;
+    constexpr int n = (C - 1) / 2, NT = C * C, TPC = G / 4;
+    const int pix = (int) floorf(pos.x) - n, piy = (int) floorf(pos.y) - n;
+    float relx = (float) pix + .5f - pos.x, rely = (float) piy + .5f - pos.y;
+    float wx[C], wy[C];
+#pragma unroll
+    for (int i = 0; i < C; ++i) {
+        wx[i] = valid ? rfilter_eval(s, relx) : 0.f; wy[i] = valid ? rfilter_eval(s, rely) : 0.f; relx += 1.f; rely += 1.f;
+    }
+    // the footprint of the group is its leader's (lanes past the end of the unit carry zeros and a meaningless position)
+    const uint32_t gl = lid & (uint32_t) (G - 1), lead = lid & ~(uint32_t) (G - 1);
+    const int lx = __shfl_sync(0xffffffffu, pix - s.crop_offset_x, lead), ly = __shfl_sync(0xffffffffu, piy - s.crop_offset_y, lead);
+    const bool gvalid = __shfl_sync(0xffffffffu, valid ? 1 : 0, lead) != 0;
+    const float Lc[4] = { L.x, L.y, L.z, 1.f };
+#pragma unroll
+    for (int t0 = 0; t0 + TPC <= NT; t0 += TPC) {
+        float v[G];
+#pragma unroll
+        for (int j = 0; j < G; ++j) { const int t = t0 + (j >> 2); v[j] = Lc[j & 3] * (wy[t / C] * wx[t % C]); }
+#pragma unroll
+        for (int o = G / 2; o >= 1; o >>= 1) {
+            const bool up = (gl & (uint32_t) o) != 0u;
+#pragma unroll
+            for (int i = 0; i < o; ++i) {
+                const float send = up ? v[i] : v[i + o], keep = up ? v[i + o] : v[i];
+                v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+            }
+        }
+        const int t = t0 + (int) (gl >> 2), ys = t / C, xs = t - ys * C;
+        if (gvalid && (unsigned) (lx + xs) < (unsigned) s.crop_width && (unsigned) (ly + ys) < (unsigned) s.crop_height) add1(lx + xs, ly + ys, (int) (gl & 3u), v[0]);
+    }
+    {   // the last tap
+        const float wgt = wy[C - 1] * wx[C - 1];
+        float4 v = make_float4(L.x * wgt, L.y * wgt, L.z * wgt, 1.f * wgt);
+#pragma unroll
+        for (int o = G / 2; o >= 1; o >>= 1) {
+            v.x += __shfl_xor_sync(0xffffffffu, v.x, o); v.y += __shfl_xor_sync(0xffffffffu, v.y, o); v.z += __shfl_xor_sync(0xffffffffu, v.z, o); v.w += __shfl_xor_sync(0xffffffffu, v.w, o);
+        }
+        const int xs = C - 1, ys = C - 1;
+        if (gvalid && gl < 4u && (unsigned) (lx + xs) < (unsigned) s.crop_width && (unsigned) (ly + ys) < (unsigned) s.crop_height)
+            add1(lx + xs, ly + ys, (int) gl, gl == 0u ? v.x : gl == 1u ? v.y : gl == 2u ? v.z : v.w);
+    }
+    uint32_t nx = 0, ny = 0;
+#pragma unroll
+    for (int i = 0; i < C; ++i) { nx += (unsigned) (lx + i) < (unsigned) s.crop_width; ny += (unsigned) (ly + i) < (unsigned) s.crop_height; }
+    return valid ? nx * ny : 0u;
+}
+
 // jitter + sensor ray of a lane (SamplingIntegrator::render_sample, integrator.cpp:419-436): consumes the first two draws of
 // the lane's stream.  Shared by the trace kernel of bounce 0 and the first shade launch, which must derive the identical ray.
 B2_DEV Ray primary_ray(const RenderParams &p, uint32_t lane, Pcg32 &rng, f2 &pos) {

@@ -309,8 +309,20 @@ __global__ void __launch_bounds__(256) k_wf_splat(const __grid_constant__ Render
                 const int lax = __shfl_sync(0xffffffffu, ax, lead), lay = __shfl_sync(0xffffffffu, ay, lead);
                 fast = __all_sync(0xffffffffu, !valid || (key == lk && ax == lax && ay == lay));
             }
+            auto add1 = [&](int x, int y, int ch, float val) {
+                const int cx = x - tx0, cy = y - ty0;
+                if ((unsigned) cx < p.tile_cols && (unsigned) cy < p.tile_rows) atomicAdd((float *) s_tile + (cy * p.tile_cols + cx) * 4 + ch, val);
+                else atomicAdd(p.film + 4 * ((size_t) y * sn.crop_width + x) + ch, val);
+            };
             uint32_t taps;
-            if (fast) taps = film_taps_group<WEIGHTS_ONLY>(p, ps, L, valid, g, lid == lead, add);
+            const uint32_t fn = sn.rfilter == B2_RFILTER_BOX ? 0u : (uint32_t) p.filter_n;
+            if (!WEIGHTS_ONLY && fast && g == 32u && fn == 1u) taps = film_taps_bfly<32, 3>(p, ps, L, valid, lid, add1);
+            else if (!WEIGHTS_ONLY && fast && g == 32u && fn == 2u) taps = film_taps_bfly<32, 5>(p, ps, L, valid, lid, add1);
+            else if (!WEIGHTS_ONLY && fast && g == 16u && fn == 1u) taps = film_taps_bfly<16, 3>(p, ps, L, valid, lid, add1);
+            else if (!WEIGHTS_ONLY && fast && g == 16u && fn == 2u) taps = film_taps_bfly<16, 5>(p, ps, L, valid, lid, add1);
+            else if (!WEIGHTS_ONLY && fast && g == 8u && fn == 1u) taps = film_taps_bfly<8, 3>(p, ps, L, valid, lid, add1);
+            else if (!WEIGHTS_ONLY && fast && g == 8u && fn == 2u) taps = film_taps_bfly<8, 5>(p, ps, L, valid, lid, add1);
+            else if (fast) taps = film_taps_group<WEIGHTS_ONLY>(p, ps, L, valid, g, lid == lead, add);
             else taps = film_taps_group<WEIGHTS_ONLY>(p, ps, L, valid, 1u, true, add);
             cnt.add(C_TAPS, taps); if (valid) cnt.add(C_SAMPLES);
         }
