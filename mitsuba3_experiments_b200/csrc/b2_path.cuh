@@ -204,6 +204,42 @@ B2_DEV uint32_t film_taps_bfly(const RenderParams &p, f2 pos, f3 L, bool valid, 
     return valid ? nx * ny : 0u;
 }
 
+// The weight film (W channel only) the same way: the C^2 <= G weights of a lane are one butterfly chunk, lane j < C^2 adds tap j.
+template <int G, int C, class ADD1>
+B2_DEV uint32_t film_weights_bfly(const RenderParams &p, f2 pos, bool valid, uint32_t lid, ADD1 &&add1) {
+    static_assert(C * C <= G, "one chunk");
+    const DSensor &s = p.sc.sensor;
+    constexpr int n = (C - 1) / 2, NT = C * C;
+    const int pix = (int) floorf(pos.x) - n, piy = (int) floorf(pos.y) - n;
+    float relx = (float) pix + .5f - pos.x, rely = (float) piy + .5f - pos.y;
+    float wx[C], wy[C];
+#pragma unroll
+    for (int i = 0; i < C; ++i) {
+        wx[i] = valid ? rfilter_eval(s, relx) : 0.f; wy[i] = valid ? rfilter_eval(s, rely) : 0.f; relx += 1.f; rely += 1.f;
+    }
+    const uint32_t gl = lid & (uint32_t) (G - 1), lead = lid & ~(uint32_t) (G - 1);
+    const int lx = __shfl_sync(0xffffffffu, pix - s.crop_offset_x, lead), ly = __shfl_sync(0xffffffffu, piy - s.crop_offset_y, lead);
+    const bool gvalid = __shfl_sync(0xffffffffu, valid ? 1 : 0, lead) != 0;
+    float v[G];
+#pragma unroll
+    for (int j = 0; j < G; ++j) v[j] = j < NT ? 1.f * (wy[(j < NT ? j : 0) / C] * wx[(j < NT ? j : 0) % C]) : 0.f;
+#pragma unroll
+    for (int o = G / 2; o >= 1; o >>= 1) {
+        const bool up = (gl & (uint32_t) o) != 0u;
+#pragma unroll
+        for (int i = 0; i < o; ++i) {
+            const float send = up ? v[i] : v[i + o], keep = up ? v[i + o] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+    }
+    const int ys = (int) gl / C, xs = (int) gl - ys * C;
+    if (gvalid && gl < (uint32_t) NT && (unsigned) (lx + xs) < (unsigned) s.crop_width && (unsigned) (ly + ys) < (unsigned) s.crop_height) add1(lx + xs, ly + ys, 3, v[0]);
+    uint32_t nx = 0, ny = 0;
+#pragma unroll
+    for (int i = 0; i < C; ++i) { nx += (unsigned) (lx + i) < (unsigned) s.crop_width; ny += (unsigned) (ly + i) < (unsigned) s.crop_height; }
+    return valid ? nx * ny : 0u;
+}
+
 // jitter + sensor ray of a lane (SamplingIntegrator::render_sample, integrator.cpp:419-436): consumes the first two draws of
 // the lane's stream.  Shared by the trace kernel of bounce 0 and the first shade launch, which must derive the identical ray.
 B2_DEV Ray primary_ray(const RenderParams &p, uint32_t lane, Pcg32 &rng, f2 &pos) {

@@ -322,6 +322,9 @@ __global__ void __launch_bounds__(256) k_wf_splat(const __grid_constant__ Render
             else if (!WEIGHTS_ONLY && fast && g == 16u && fn == 2u) taps = film_taps_bfly<16, 5>(p, ps, L, valid, lid, add1);
             else if (!WEIGHTS_ONLY && fast && g == 8u && fn == 1u) taps = film_taps_bfly<8, 3>(p, ps, L, valid, lid, add1);
             else if (!WEIGHTS_ONLY && fast && g == 8u && fn == 2u) taps = film_taps_bfly<8, 5>(p, ps, L, valid, lid, add1);
+            else if (WEIGHTS_ONLY && fast && g == 32u && fn == 1u) taps = film_weights_bfly<32, 3>(p, ps, valid, lid, add1);
+            else if (WEIGHTS_ONLY && fast && g == 32u && fn == 2u) taps = film_weights_bfly<32, 5>(p, ps, valid, lid, add1);
+            else if (WEIGHTS_ONLY && fast && g == 16u && fn == 1u) taps = film_weights_bfly<16, 3>(p, ps, valid, lid, add1);
             else if (fast) taps = film_taps_group<WEIGHTS_ONLY>(p, ps, L, valid, g, lid == lead, add);
             else taps = film_taps_group<WEIGHTS_ONLY>(p, ps, L, valid, 1u, true, add);
             cnt.add(C_TAPS, taps); if (valid) cnt.add(C_SAMPLES);
