@@ -18,7 +18,7 @@
 
 namespace b2 {
 
-struct Hit { float t, u, v; uint32_t face, mesh; B2_DEV bool valid() const { return face != 0xffffffffu; } };
+struct Hit { float t, u, v; uint32_t face, mesh, cls; B2_DEV bool valid() const { return face != 0xffffffffu; } };   // cls: shading class of the hit face (wavefront)
 
 
 B2_DEV uint32_t byte_of(uint32_t lo, uint32_t hi, int s) { return ((s < 4 ? lo : hi) >> ((s & 3) * 8)) & 0xffu; }
@@ -83,7 +83,7 @@ B2_DEV uint32_t permute_octant(uint32_t hitmask, uint32_t octinv) {
 // Ties at equal t resolve to the lower face index, independent of traversal order.
 template <bool ANY, bool COUNT>
 B2_DEV bool bvh_trace(const DScene &sc, f3 o, f3 d, float tmax, Hit &hit, Counters<COUNT> &cnt) {
-    hit.t = tmax; hit.u = 0.f; hit.v = 0.f; hit.face = 0xffffffffu; hit.mesh = 0;
+    hit.t = tmax; hit.u = 0.f; hit.v = 0.f; hit.face = 0xffffffffu; hit.mesh = 0; hit.cls = 0;
     if (sc.n_nodes == 0) return false;
     const float ray_maxt = tmax;
     const float tiny = kTinyDir;
@@ -140,7 +140,7 @@ B2_DEV bool bvh_trace(const DScene &sc, f3 o, f3 d, float tmax, Hit &hit, Counte
                 if (ANY) { hit.t = t; hit.face = __float_as_uint(r0.w); return true; }
                 const uint32_t face = __float_as_uint(r0.w);
                 if (!found || t < hit.t || (t == hit.t && face < hit.face)) {
-                    found = true; hit.t = t; hit.u = u; hit.v = v; hit.face = face; hit.mesh = __float_as_uint(r1.w) & 0x0fffffffu;
+                    found = true; hit.t = t; hit.u = u; hit.v = v; hit.face = face; hit.mesh = __float_as_uint(r1.w) & 0x0fffffffu; hit.cls = __float_as_uint(r1.w) >> 28;
                 }
             }
         }

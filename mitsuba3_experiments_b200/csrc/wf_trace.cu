@@ -240,6 +240,41 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
     trace_flush_counters(cnt, p.counters);
 }
 
+// ------------------------------------------------------------------------------------------ small trees: one thread per ray
+// A tree of a few nodes (the Cornell box: 3 nodes, 36 triangles) gives the vote-scheduled kernel nothing to schedule: a ray is
+// 1.4 node steps and 4 triangle tests, and the ray pipeline, the votes and the parked-triangle queue cost more than the traversal.
+// k_wf_trace_simple walks such trees with the per-thread traversal of b2_bvh.cuh (the megakernel's), one queue entry per thread,
+// same queues in, same records out.  Chosen by the host when the tree has at most kSimpleTraceNodes nodes (B2_SIMPLE_TRACE_NODES).
+template <bool COUNT>
+__global__ void __launch_bounds__(256) k_wf_trace_simple(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
+    const DScene &sc = p.sc; const WfState &st = w.st;
+    const uint32_t nc = st.ctl->n_closest[w.it & 3u], ns = st.ctl->n_shadow[(w.it + 3u) & 3u], total = nc + ns;
+    const uint32_t *qc = st.q[w.it & 1u], *qs = st.q_shadow;
+    Counters<COUNT> cnt;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+        const bool any = e >= nc;
+        const uint32_t slot = any ? qs[e - nc] : qc[e];
+        const Elem r = ld256(any ? &st.shr[slot] : &st.ray[slot]);
+        Hit h;
+        cnt.add(any ? C_SHADOW : C_CLOSEST);
+        if (any) {
+            if (!bvh_trace<true, COUNT>(sc, f3(r.a.x, r.a.y, r.a.z), f3(r.b.x, r.b.y, r.b.z), r.a.w, h, cnt)) {
+                if (r.b.w != 0.f) cnt.add(C_TEX);
+                st.shf[slot].a.w = 1.f;
+            }
+        } else {
+            const bool found = bvh_trace<false, COUNT>(sc, f3(r.a.x, r.a.y, r.a.z), f3(r.b.x, r.b.y, r.b.z), r.a.w, h, cnt);
+            const uint32_t cls = found ? h.cls : (uint32_t) CLS_MISS;
+            Elem o;
+            o.a = make_float4(h.t, h.u, h.v, __uint_as_float(h.face));
+            o.b = make_float4(__uint_as_float(found ? h.mesh : 0xffffffffu), __uint_as_float(cls), 0.f, 0.f);
+            st256(&st.hit[slot], o);
+            st.cls_q[e] = (uint8_t) cls;
+        }
+    }
+    trace_flush_counters(cnt, p.counters);
+}
+
 // ------------------------------------------------------------------------------------------ bounce 0: packet traversal
 // The 32 primary rays of a warp are consecutive lanes, i.e. samples of one pixel (or of neighbouring pixels): they visit the same
 // nodes.  k_wf_trace_packet walks the tree ONCE per warp: the stack and the node / triangle groups are warp-uniform, lane c < 8
@@ -455,9 +490,14 @@ static int primary_packet_rays(const RenderParams &p) {
     return p.spp_per_pass >= 8u ? 2 : p.spp_per_pass >= 4u ? 1 : 0;
 }
 
+static uint32_t simple_trace_nodes() { const char *e = getenv("B2_SIMPLE_TRACE_NODES"); return e ? (uint32_t) atoi(e) : 32u; }
+
 static void launch_trace(bool count, bool primary, int packet_rays, const RenderParams &p, const WfLaunch &w, int blocks, cudaStream_t stream) {
     wf_tm_begin(WF_K_TRACE, stream);
-    if (primary && packet_rays == 2) {
+    if (!primary && p.sc.n_nodes <= simple_trace_nodes()) {
+        const int g = 8 * std::max(blocks / 4, 1);           // blocks = 4 per SM of the persistent kernel -> 8 per SM, grid-stride
+        if (count) k_wf_trace_simple<true><<<g, 256, 0, stream>>>(p, w); else k_wf_trace_simple<false><<<g, 256, 0, stream>>>(p, w);
+    } else if (primary && packet_rays == 2) {
         if (count) k_wf_trace_packet<true, 2><<<blocks, kPacketThreads, 0, stream>>>(p, w); else k_wf_trace_packet<false, 2><<<blocks, kPacketThreads, 0, stream>>>(p, w);
     } else if (primary && packet_rays == 1) {
         if (count) k_wf_trace_packet<true, 1><<<blocks, kPacketThreads, 0, stream>>>(p, w); else k_wf_trace_packet<false, 1><<<blocks, kPacketThreads, 0, stream>>>(p, w);
