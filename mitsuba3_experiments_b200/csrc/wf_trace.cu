@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
             const bool can_node = node_work && (tg.y == 0u || (fl & TF_NQ_MASK) < ((uint32_t) kTriQueue << TF_NQ_SHIFT));
             const uint32_t P = __ballot_sync(smask, tg.y != 0u), N = __ballot_sync(smask, can_node);
             if (N == 0u || (uint32_t) __popc(P) >= w.tri_thresh) {
-                if (tg.y) {
+                do if (tg.y) {
                     const int i = __ffs(tg.y) - 1;
                     tg.y &= tg.y - 1;
                     const float4 *tp = sc.tris + (size_t) (tg.x + i) * 3;
@@ -192,6 +192,9 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
                     }
                     if (tg.y == 0u && (fl & TF_NQ_MASK)) { fl -= TF_NQ_ONE; tg = s_pend[(fl & TF_NQ_MASK) >> TF_NQ_SHIFT][tid]; }
                 }
+                // stay in triangle steps for as long as the vote would choose one again: skips the refill check and the node vote
+                // (bedroom trace 38.2 -> 37.1 ms; the 10 M soup 39.5 -> 39.9 ms)
+                while ((uint32_t) __popc(__ballot_sync(smask, tg.y != 0u)) >= w.tri_thresh);
             } else if (can_node) {
                 if ((ng.y & 0xff000000u) == 0u) { --sp; ng = sp < kSmemStack ? s_stack[sp][tid] : l_stack[sp - kSmemStack]; }
                 const int bit = 31 - __clz(ng.y);
