@@ -82,6 +82,7 @@ enum { WF_K_TRACE = 0, WF_K_SHADE = 1, WF_K_SPLAT = 2, WF_K_OTHER = 3, WF_K_COUN
 struct WfTiming { std::vector<cudaEvent_t> ev; std::vector<int> kind; size_t used = 0; };
 void wf_set_timing(WfTiming *t);          // nullptr = off (default)
 void wf_collect_timing(WfTiming &t, double ms[WF_K_COUNT], uint64_t n[WF_K_COUNT]);   // after the stream has been synchronised
+void wf_set_film_ready_event(cudaEvent_t e);   // nullptr = the film is ready when the render is enqueued (default); thread-local
 void wf_tm_begin(int kind, cudaStream_t st);
 void wf_tm_end(cudaStream_t st);
 

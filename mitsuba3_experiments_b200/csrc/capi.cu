@@ -25,6 +25,7 @@ struct b2_scene {
     DScene d{};
     Bvh bvh;
     float *host_film = nullptr, *host_image = nullptr;   // device staging of b2_render_host
+    cudaStream_t copy_stream = nullptr; cudaEvent_t film_ready = nullptr;   // b2_render_host: film upload overlapped with the bounces
     std::vector<void *> allocs;
     std::vector<b2_bsdf> bsdfs;                 // host mirror (for set_param / grad target validation)
     std::vector<DTexture> textures;             // host mirror of the device texture records
@@ -46,7 +47,7 @@ struct b2_scene {
         if (n && host) e = cudaMemcpy(q, host, n * sizeof(T), cudaMemcpyHostToDevice);
         return e;
     }
-    ~b2_scene() { for (cudaEvent_t e : timing.ev) cudaEventDestroy(e); for (void *q : allocs) cudaFree(q); if (wf_mem) cudaFree(wf_mem); if (wf_hist) cudaFree(wf_hist); bvh_free(bvh); }
+    ~b2_scene() { for (cudaEvent_t e : timing.ev) cudaEventDestroy(e); if (film_ready) cudaEventDestroy(film_ready); if (copy_stream) cudaStreamDestroy(copy_stream); for (void *q : allocs) cudaFree(q); if (wf_mem) cudaFree(wf_mem); if (wf_hist) cudaFree(wf_hist); bvh_free(bvh); }
 };
 
 extern "C" {
@@ -676,8 +677,16 @@ int b2_render_host(b2_scene *s, const b2_render_args *a, float *film_host, float
     if (!s->host_film) { CUDA_OK(cudaMalloc((void **) &s->host_film, npix * 16)); s->allocs.push_back(s->host_film); }
     if (image_host && !s->host_image) { CUDA_OK(cudaMalloc((void **) &s->host_image, npix * 12)); s->allocs.push_back(s->host_image); }
     cudaStream_t st = 0;
-    CUDA_OK(cudaMemcpyAsync(s->host_film, film_host, npix * 16, cudaMemcpyHostToDevice, st));
+    // the film upload runs on its own stream: the wavefront touches the film only in its splat launches, which wait for the event
+    if (!s->copy_stream) { CUDA_OK(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking)); CUDA_OK(cudaEventCreateWithFlags(&s->film_ready, cudaEventDisableTiming)); }
+    CUDA_OK(cudaMemcpyAsync(s->host_film, film_host, npix * 16, cudaMemcpyHostToDevice, s->copy_stream));
+    CUDA_OK(cudaEventRecord(s->film_ready, s->copy_stream));
+    const bool overlap = a->kernel == B2_KERNEL_WAVEFRONT;
+    if (!overlap) CUDA_OK(cudaStreamWaitEvent(st, s->film_ready, 0));
+    wf_set_film_ready_event(overlap ? s->film_ready : nullptr);
     int rc = b2_render(s, a, s->host_film, (uintptr_t) st, counters);
+    wf_set_film_ready_event(nullptr);
+    CUDA_OK(cudaStreamWaitEvent(st, s->film_ready, 0));          // (a render without a splat launch: empty lane range)
     if (rc == 0 && image_host) rc = b2_develop(s, s->host_film, s->host_image, (uintptr_t) st);
     if (rc != 0) return rc;
     CUDA_OK(cudaMemcpyAsync(film_host, s->host_film, npix * 16, cudaMemcpyDeviceToHost, st));

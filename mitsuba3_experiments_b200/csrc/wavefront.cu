@@ -364,6 +364,10 @@ void wf_bind(WfState &st, void *base, uint32_t cap) {
 
 // optional per-kernel-kind device timing (bench.py's roofline): CUDA events around every launch, summed after the render
 static thread_local WfTiming *g_tm = nullptr;
+// The film is first touched by the splat launches: a caller whose film arrives on another stream (b2_render_host's upload) hands
+// over the event that marks it complete instead of delaying the whole render behind the copy.
+static thread_local cudaEvent_t g_film_ready = nullptr;
+void wf_set_film_ready_event(cudaEvent_t e) { g_film_ready = e; }
 void wf_set_timing(WfTiming *t) { g_tm = t; }
 void wf_tm_begin(int kind, cudaStream_t st) {
     WfTiming *t = g_tm; if (!t) return;
@@ -470,6 +474,7 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
             ps.unit_end = (uint32_t) ((pix1 / W) * p.units_per_row + (pix1 % W) / P) + 1;
             cudaMemsetAsync(p.unit_counter, 0, 4, stream);
             const int g_splat = (int) std::min<uint32_t>(ps.unit_end - ps.unit_begin, (uint32_t) (occ_splat * sm_count));
+            if (g_film_ready) cudaStreamWaitEvent(stream, g_film_ready, 0);      // b2_render_host: the film upload overlaps the bounces
             tm_begin(WF_K_SPLAT, stream); k_wf_splat<V, COUNT, false><<<g_splat, 256, smem_splat, stream>>>(ps, w); tm_end(stream); launches++;
         }
     }
@@ -536,6 +541,7 @@ static long wf_render_backward_t(RenderParams p, WfState &st, Elem *hist, int sm
             ps.unit_end = (uint32_t) ((pix1 / W) * p.units_per_row + (pix1 % W) / P) + 1;
             cudaMemsetAsync(p.unit_counter, 0, 4, stream);
             const int g_splat = (int) std::min<uint32_t>(ps.unit_end - ps.unit_begin, (uint32_t) (occ_splat * sm_count));
+            if (g_film_ready) cudaStreamWaitEvent(stream, g_film_ready, 0);      // b2_render_host: the film upload overlaps the bounces
             tm_begin(WF_K_SPLAT, stream); k_wf_splat<V, COUNT, false><<<g_splat, 256, smem_splat, stream>>>(ps, w); tm_end(stream); launches++;
         }
     }
