@@ -125,9 +125,13 @@ __global__ void __launch_bounds__(256) k_wf_classify(const __grid_constant__ WfL
 // states what every BSDF of the scene is -- single-class scenes such as the Cornell box skip the sort).
 // w.first: bounce 0 of a pass -- the lane state does not exist yet; it is derived from the lane index exactly as the trace
 // kernel derived the camera ray (start_path), so nothing but the hit record is read.
+#ifndef B2_SHADE_THREADS
+#define B2_SHADE_THREADS 256
+#endif
+constexpr int kShadeT = B2_SHADE_THREADS, kShadeW = kShadeT / 32;
 template <int V, bool COUNT, bool ADJ = false, int CLS = CLS_GENERIC, bool SORTED = (CLS != CLS_GENERIC)>
-__global__ void __launch_bounds__(256, (CLS == CLS_DIFFUSE || CLS == CLS_MISS) ? 4 : B2_SHADE_MINBLOCKS) k_wf_shade(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
-    __shared__ uint32_t s_cnt[2][8], s_base[2];
+__global__ void __launch_bounds__(kShadeT, ((CLS == CLS_DIFFUSE || CLS == CLS_MISS) ? 4 : B2_SHADE_MINBLOCKS) * (256 / kShadeT)) k_wf_shade(const __grid_constant__ RenderParams p, const __grid_constant__ WfLaunch w) {
+    __shared__ uint32_t s_cnt[2][kShadeW], s_base[2];
     __shared__ float s_gconst[kMaxGradTargets * 3];     // adjoint: per-block sums of the constant-albedo gradients
     const WfState &st = w.st;
     const uint32_t it = w.it;
@@ -140,7 +144,7 @@ __global__ void __launch_bounds__(256, (CLS == CLS_DIFFUSE || CLS == CLS_MISS) ?
     if (ADJ) { if (tid < kMaxGradTargets * 3) s_gconst[tid] = 0.f; __syncthreads(); }
     if (!SORTED && blockIdx.x == 0 && tid == 0) { const uint32_t z = (it + 2u) & 3u; st.ctl->n_closest[z] = 0u; st.ctl->n_shadow[z] = 0u; st.ctl->fetch[z] = 0u; }
 
-    for (uint32_t base = blockIdx.x * 256u; base < n; base += gridDim.x * 256u) {
+    for (uint32_t base = blockIdx.x * (uint32_t) kShadeT; base < n; base += gridDim.x * (uint32_t) kShadeT) {
         const uint32_t i = base + tid;
         bool alive = false, shadow = false; uint32_t slot = 0;
         if (i < n) {
@@ -187,7 +191,7 @@ __global__ void __launch_bounds__(256, (CLS == CLS_DIFFUSE || CLS == CLS_MISS) ?
         __syncthreads();
         if (tid < 2) {
             uint32_t tot = 0;
-            for (int k = 0; k < 8; ++k) { const uint32_t c = s_cnt[tid][k]; s_cnt[tid][k] = tot; tot += c; }
+            for (int k = 0; k < kShadeW; ++k) { const uint32_t c = s_cnt[tid][k]; s_cnt[tid][k] = tot; tot += c; }
             s_base[tid] = tot ? atomicAdd(tid == 0 ? &st.ctl->n_closest[(it + 1u) & 3u] : &st.ctl->n_shadow[it & 3u], tot) : 0u;
         }
         __syncthreads();
@@ -396,13 +400,13 @@ static const int tune_sort = getenv("B2_SHADE_SORT") ? atoi(getenv("B2_SHADE_SOR
 // resident blocks per SM of one kernel instantiation (queried once): every shade specialisation gets the grid its own
 // register count allows (the diffuse kernels fit 4 blocks/SM, the glossy ones 3)
 template <auto Kern> static int occ_of() {
-    static const int occ = [] { int o = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, Kern, 256, 0); return std::max(o, 1); }();
+    static const int occ = [] { int o = 0; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, Kern, kShadeT, 0); return std::max(o, 1); }();
     return occ;
 }
 static const int tune_shade_mult = getenv("B2_SHADE_GRID_MULT") ? std::max(1, atoi(getenv("B2_SHADE_GRID_MULT"))) : 1;
 #define B2_SHADE_LAUNCH(...) do { constexpr auto kern_ = k_wf_shade<__VA_ARGS__>; \
-    const int g_ = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_of<kern_>() * sm_count * tune_shade_mult); \
-    tm_begin(WF_K_SHADE, stream); kern_<<<g_, 256, 0, stream>>>(p, w); tm_end(stream); launches++; } while (0)
+    const int g_ = (int) std::min<uint64_t>((n + kShadeT - 1) / kShadeT, (uint64_t) occ_of<kern_>() * sm_count * tune_shade_mult); \
+    tm_begin(WF_K_SHADE, stream); kern_<<<g_, kShadeT, 0, stream>>>(p, w); tm_end(stream); launches++; } while (0)
 
 static WfLaunch wf_launch_defaults(const WfState &st, uint64_t c0, uint32_t n) {
     WfLaunch w{}; w.st = st; w.chunk_begin = c0; w.n = n; w.tri_thresh = tune_tri; w.refill_thresh = std::min(tune_refill, 32u);
@@ -418,7 +422,7 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
     const size_t smem_splat = sizeof(float4) * (size_t) p.tile_cols * p.tile_rows;
     cudaFuncSetAttribute(k_wf_splat<V, COUNT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem_splat);
     const int g_trace = wf_trace_blocks(COUNT, sm_count);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<V, COUNT>, 256, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<V, COUNT>, kShadeT, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_splat, k_wf_splat<V, COUNT, false>, 256, smem_splat);
     if (g_trace <= 0 || occ_shade <= 0 || occ_splat <= 0) { *err = "wavefront: a kernel cannot be resident (occupancy 0)"; return -1; }
     const uint64_t lane_lo = p.lane_begin, lane_hi = p.lane_end;
@@ -490,8 +494,8 @@ static long wf_render_backward_t(RenderParams p, WfState &st, Elem *hist, int sm
     long launches = 0;
     int occ_shade = 0, occ_adj = 0;
     const int g_trace = wf_trace_blocks(COUNT, sm_count);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<V, COUNT, false>, 256, 0);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_adj, k_wf_shade<V, COUNT, true>, 256, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_shade, k_wf_shade<V, COUNT, false>, kShadeT, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_adj, k_wf_shade<V, COUNT, true>, kShadeT, 0);
     int occ_splat = 1; const size_t smem_splat = sizeof(float4) * (size_t) p.tile_cols * p.tile_rows;
     if (B2_FWD(p)) {
         cudaFuncSetAttribute(k_wf_splat<V, COUNT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem_splat);
@@ -506,7 +510,7 @@ static long wf_render_backward_t(RenderParams p, WfState &st, Elem *hist, int sm
         const uint32_t n = (uint32_t) std::min<uint64_t>(st.capacity, p.lane_end - c0);
         WfLaunch w = wf_launch_defaults(st, c0, n);
         const int g_gen = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) sm_count * 8);
-        const int g_adj = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_adj * sm_count);
+        const int g_adj = (int) std::min<uint64_t>((n + kShadeT - 1) / kShadeT, (uint64_t) occ_adj * sm_count);
         // ---- primal pass (common.py:750-760): L per lane, and the visibility bit of every emitter sample
         cudaMemsetAsync(st.ctl, 0, sizeof(WfCtl), stream);
         w.record_vis = 1u;
@@ -527,7 +531,7 @@ static long wf_render_backward_t(RenderParams p, WfState &st, Elem *hist, int sm
             w.it = it; w.bounce = k;
             if (hist) w.st.hit = hist + (size_t) k * st.capacity;               // the hits the primal pass recorded for this bounce
             else { wf_launch_trace(COUNT, false, p, w, g_trace, stream); launches++; }
-            tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, true><<<g_adj, 256, 0, stream>>>(p, w); tm_end(stream); launches++;
+            tm_begin(WF_K_SHADE, stream); k_wf_shade<V, COUNT, true><<<g_adj, kShadeT, 0, stream>>>(p, w); tm_end(stream); launches++;
             ++it;
         }
         w.st.hit = st.hit;
