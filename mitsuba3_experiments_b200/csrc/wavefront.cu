@@ -393,7 +393,7 @@ void wf_collect_timing(WfTiming &t, double ms[WF_K_COUNT], uint64_t n[WF_K_COUNT
 
 // tuning knobs (environment overrides are for sweeps on the GPU box; the defaults are the measured optimum)
 static int env_int(const char *name, int def) { const char *v = getenv(name); return v ? std::max(1, atoi(v)) : def; }
-static const uint32_t tune_tri = (uint32_t) env_int("B2_TRI_THRESH", 10);
+static const uint32_t tune_tri = (uint32_t) env_int("B2_TRI_THRESH", 12);
 static const uint32_t tune_refill = (uint32_t) env_int("B2_REFILL_THRESH", 6);
 static const int tune_sort = getenv("B2_SHADE_SORT") ? atoi(getenv("B2_SHADE_SORT")) : -1;   // 0/1 force, -1 = by scene content
 

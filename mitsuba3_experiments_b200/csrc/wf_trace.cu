@@ -1,6 +1,12 @@
-// wf_trace.cu -- k_wf_trace: Scene::ray_intersect_preliminary + Scene::ray_test of the wavefront (scene.cpp:191-235;
-// Embree / OptiX in the reference, scene_embree.inl:245-433, scene_optix.inl:602-743).
+// wf_trace.cu -- Scene::ray_intersect_preliminary + Scene::ray_test of the wavefront (scene.cpp:191-235; Embree / OptiX in the
+// reference, scene_embree.inl:245-433, scene_optix.inl:602-743).  Three kernels, same queues in and same records out:
+//   k_wf_trace          the general one (below): incoherent rays of bounces >= 1, closest and shadow rays in one launch
+//   k_wf_trace_packet   bounce 0 from 4 samples per pixel on: one warp-uniform traversal per 32 / 64 consecutive primary rays
+//   k_wf_trace_simple   trees of a few nodes (the Cornell box): one thread per ray, the per-thread traversal of b2_bvh.cuh
+// All three return bit-identical hit records: the closest hit of a ray is the lexicographic minimum of (t, face) over the
+// triangles it intersects (same Moeller-Trumbore arithmetic everywhere), whatever the traversal order.
 //
+// k_wf_trace:
 // Persistent warps.  Each warp owns a three-stage ray pipeline so that a lane whose ray ends can be refilled within a
 // few instructions instead of a dependent global-load chain:
 //   stage A   lane 0 reserves the next 32 queue entries (atomicAdd on the launch's fetch counter)

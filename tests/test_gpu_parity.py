@@ -72,7 +72,7 @@ def test_sampler_stream_bit_exact():
 @pytest.mark.parametrize("kernel", [pytest.param(0, id="wavefront"), pytest.param(1, id="megakernel")])
 @pytest.mark.parametrize("builder", BUILDERS)
 @pytest.mark.parametrize("scene_name", ["cornell", "soup"])
-def test_trace_bit_exact(scene_name, builder, kernel):
+def test_trace_bit_exact(scene_name, builder, kernel, monkeypatch):
     """b2_trace through the production trace kernel (k_wf_trace: staged rays, vote-scheduled node / triangle steps) and through
     the megakernel's per-thread traversal: (t, u, v, prim) equal the oracle's exact BVH bit for bit."""
     torch, DeviceScene, SceneDesc, cornell_box, OracleScene = _mods()
@@ -87,6 +87,15 @@ def test_trace_bit_exact(scene_name, builder, kernel):
         assert np.array_equal(g[k][hit], c[k][hit]), k
     ga, ca = ds.trace(rays, any_hit=True, kernel=kernel), orc.trace(rays, any_hit=True)
     assert np.array_equal(ga["prim"], ca["prim"])
+    if kernel == 0:
+        # the wavefront path picks its trace kernel by tree size (k_wf_trace_simple up to 32 wide nodes, k_wf_trace above): force the
+        # other one on the same rays -- identical records
+        monkeypatch.setenv("B2_SIMPLE_TRACE_NODES", "0" if ds.build_stats.as_dict()["n_nodes8"] <= 32 else "1000000000")
+        g2, ga2 = ds.trace(rays, kernel=kernel), ds.trace(rays, any_hit=True, kernel=kernel)
+        monkeypatch.delenv("B2_SIMPLE_TRACE_NODES")
+        for k in ("prim", "t", "u", "v"):
+            assert np.array_equal(g2[k].view(np.uint32), g[k].view(np.uint32)), k
+        assert np.array_equal(ga2["prim"], ga["prim"]) and np.array_equal(ga2["t"].view(np.uint32), ga["t"].view(np.uint32))
 
 
 @pytest.mark.parametrize("scene_name", ["cornell", "materials", "soup"])
