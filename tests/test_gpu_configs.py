@@ -118,6 +118,27 @@ def test_c2_bedroom_720p_render_parity(bedroom):
     np.testing.assert_allclose(img2.cpu().numpy(), img.cpu().numpy(), rtol=2e-5, atol=1e-6)
 
 
+def test_c2_bedroom_primary_packets_bit_exact_at_64spp(bedroom):
+    """Bounce 0 of the headline run: the 64-lane packet kernel (one warp-uniform traversal per pixel at 64 spp) against the per-ray
+    trace kernel on the 1.8 M-triangle tree -- (t, u, v, prim) bit for bit on row segments spread over the image (centre row and
+    column included: packets whose rays have both signs on an axis), and the oracle's exact BVH on the rays of a few pixels."""
+    torch, DeviceScene, SceneDesc, OracleScene = _mods()
+    ds = DeviceScene(bedroom)
+    W, H, spp = 1280, 720, 64
+    checked = 0
+    for row, x0, npx in ((0, 0, 400), (359, 0, 1280), (360, 440, 400), (200, 600, 80), (719, 880, 400), (511, 3, 97)):
+        lane0, n = (row * W + x0) * spp, npx * spp
+        a = ds.debug_primary_hits(lane0, n, kernel=2, seed=0, spp=spp)
+        b = ds.debug_primary_hits(lane0, n, kernel=0, seed=0, spp=spp)
+        c = ds.debug_primary_hits(lane0 + 17, n - 17, kernel=1, seed=0, spp=spp)          # 32-lane packets, not aligned to a pixel
+        for f in ("prim", "t", "u", "v"):
+            assert np.array_equal(a[f].view(np.uint32), b[f].view(np.uint32)), (row, x0, f)
+            assert np.array_equal(c[f].view(np.uint32), b[f][17:].view(np.uint32)), (row, x0, f, "32-lane")
+        checked += n
+        assert (a["prim"] != 0xffffffff).mean() > 0.5
+    assert checked >= 150_000
+
+
 # ------------------------------------------------------------------------------------------------ C3
 def test_c3_prb_512_32spp_woodfloor_gradient():
     """BASELINE configs[2]: Cornell box 512 x 512, 32 spp, `white` reflectance = WoodFloor 960 x 870 fp32 bitmap parameter;
