@@ -121,7 +121,8 @@ def test_c2_bedroom_720p_render_parity(bedroom):
 def test_c2_bedroom_primary_packets_bit_exact_at_64spp(bedroom):
     """Bounce 0 of the headline run: the 64-lane packet kernel (one warp-uniform traversal per pixel at 64 spp) against the per-ray
     trace kernel on the 1.8 M-triangle tree -- (t, u, v, prim) bit for bit on row segments spread over the image (centre row and
-    column included: packets whose rays have both signs on an axis), and the oracle's exact BVH on the rays of a few pixels."""
+    column included: packets whose rays have both signs on an axis).  The per-ray kernel itself is pinned to the oracle's exact BVH
+    by test_c2_bedroom_trace_bit_exact_2m_rays."""
     torch, DeviceScene, SceneDesc, OracleScene = _mods()
     ds = DeviceScene(bedroom)
     W, H, spp = 1280, 720, 64
