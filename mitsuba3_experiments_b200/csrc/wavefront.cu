@@ -86,8 +86,9 @@ B2_DEV void wf_flush_counters(const Counters<COUNT> &cnt, unsigned long long *ou
 // Sorts the closest hits of iteration `it` by shading class (miss / diffuse / textured diffuse / glossy / delta) into
 // per-class queues, so that every warp of a shade kernel runs one BSDF and the kernels can be specialised: block-wide
 // counting sort step = five ballots, one atomic per block and class.
+constexpr int kClassifyLanes = 4;       // lanes per thread between two block-wide scans: the scan's atomics are a ~1 us round trip
 __global__ void __launch_bounds__(256) k_wf_classify(const __grid_constant__ WfLaunch w) {
-    __shared__ uint32_t s_cnt[CLS_COUNT][8], s_base[CLS_COUNT];
+    __shared__ uint32_t s_cnt[CLS_COUNT][8 * kClassifyLanes], s_base[CLS_COUNT];
     const WfState &st = w.st;
     const uint32_t it = w.it, n = w.first ? w.n : st.ctl->n_closest[it & 3u];
     const uint32_t *qin = st.q[it & 1u];
@@ -97,25 +98,34 @@ __global__ void __launch_bounds__(256) k_wf_classify(const __grid_constant__ WfL
         if (tid == 0) { st.ctl->n_closest[z] = 0u; st.ctl->n_shadow[z] = 0u; st.ctl->fetch[z] = 0u; }
         st.ctl->n_class[z][tid] = 0u;
     }
-    for (uint32_t base = blockIdx.x * 256u; base < n; base += gridDim.x * 256u) {
-        const uint32_t i = base + tid;
-        uint32_t slot = 0; int cls = -1;
-        if (i < n) { slot = w.first ? i : qin[i]; cls = (int) st.cls_q[i]; if (cls >= CLS_COUNT) cls = CLS_MISS; }   // class by queue position, written by trace(it)
-        uint32_t mine = 0;
+    constexpr uint32_t kGroup = 256u * kClassifyLanes;
+    for (uint32_t base = blockIdx.x * kGroup; base < n; base += gridDim.x * kGroup) {
+        uint32_t slot[kClassifyLanes], mine[kClassifyLanes]; int cls[kClassifyLanes];
 #pragma unroll
-        for (int k = 0; k < CLS_COUNT; ++k) {
-            const uint32_t m = __ballot_sync(0xffffffffu, cls == k);
-            if (lane == 0) s_cnt[k][warp] = __popc(m);
-            if (cls == k) mine = m;
+        for (int u = 0; u < kClassifyLanes; ++u) {
+            const uint32_t i = base + u * 256u + tid;
+            slot[u] = 0; cls[u] = -1; mine[u] = 0;
+            if (i < n) { slot[u] = w.first ? i : qin[i]; cls[u] = (int) st.cls_q[i]; if (cls[u] >= CLS_COUNT) cls[u] = CLS_MISS; }   // class by queue position, written by trace(it)
+        }
+#pragma unroll
+        for (int u = 0; u < kClassifyLanes; ++u) {
+#pragma unroll
+            for (int k = 0; k < CLS_COUNT; ++k) {
+                const uint32_t m = __ballot_sync(0xffffffffu, cls[u] == k);
+                if (lane == 0) s_cnt[k][u * 8 + warp] = __popc(m);
+                if (cls[u] == k) mine[u] = m;
+            }
         }
         __syncthreads();
         if (tid < CLS_COUNT) {
             uint32_t tot = 0;
-            for (int k = 0; k < 8; ++k) { const uint32_t c = s_cnt[tid][k]; s_cnt[tid][k] = tot; tot += c; }
+            for (int k = 0; k < 8 * kClassifyLanes; ++k) { const uint32_t c = s_cnt[tid][k]; s_cnt[tid][k] = tot; tot += c; }
             s_base[tid] = tot ? atomicAdd(&st.ctl->n_class[it & 3u][tid], tot) : 0u;
         }
         __syncthreads();
-        if (cls >= 0) st.qc[cls][s_base[cls] + s_cnt[cls][warp] + __popc(mine & ((1u << lane) - 1u))] = slot;
+#pragma unroll
+        for (int u = 0; u < kClassifyLanes; ++u)
+            if (cls[u] >= 0) st.qc[cls[u]][s_base[cls[u]] + s_cnt[cls[u]][u * 8 + warp] + __popc(mine[u] & ((1u << lane) - 1u))] = slot[u];
         __syncthreads();
     }
 }
@@ -434,7 +444,7 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
         const uint32_t n = (uint32_t) std::min<uint64_t>(st.capacity, lane_hi - c0);
         WfLaunch w = wf_launch_defaults(st, c0, n);
         w.store_pos = p.n_passes > 1 ? 1u : 0u;
-        const int g_shade = (int) std::min<uint64_t>((n + 255) / 256, (uint64_t) occ_shade * sm_count);
+        const int g_classify = (int) std::min<uint64_t>((n + 256 * kClassifyLanes - 1) / (256 * kClassifyLanes), (uint64_t) 8 * sm_count);
         for (uint32_t pass = 0; pass < p.n_passes; ++pass) {
             w.pass = pass;
             cudaMemsetAsync(st.ctl, 0, sizeof(WfCtl), stream);          // queue bookkeeping of a pass starts from zero
@@ -450,7 +460,7 @@ static long wf_render_t(RenderParams p, WfState &st, int sm_count, cudaStream_t 
                                                   : (__builtin_popcount(cmask) >= 2 && (cmask & ((1u << CLS_CONDUCTOR) | (1u << CLS_DIELECTRIC) | (1u << CLS_PLASTIC) | (1u << CLS_ROUGHDIEL))) != 0));
                 if (!sort && cmask == (1u << CLS_DIFFUSE)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_DIFFUSE, false);
                 else if (sort) {
-                    tm_begin(WF_K_SHADE, stream); k_wf_classify<<<g_shade, 256, 0, stream>>>(w); tm_end(stream); launches++;
+                    tm_begin(WF_K_SHADE, stream); k_wf_classify<<<g_classify, 256, 0, stream>>>(w); tm_end(stream); launches++;
                     const uint32_t cm = st.class_mask;
                     if (cm & (1u << CLS_DIFFUSE)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_DIFFUSE);
                     if (cm & (1u << CLS_DIFFUSE_TEX)) B2_SHADE_LAUNCH(V, COUNT, false, CLS_DIFFUSE_TEX);
