@@ -70,6 +70,8 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
     __shared__ uint2 s_pend[kTriQueue][kTraceThreads];
     __shared__ float4 s_so[kTraceWarps][2][32], s_sd[kTraceWarps][2][32];     // staged rays: o | maxt, d | flag word
     __shared__ uint32_t s_ss[kTraceWarps][2][32];                             // staged lane slot | any << 31
+    extern __shared__ float4 s_inv_dyn[];                                     // [kTraceWarps][32] current batch: 1 / d (x, y, z), octant -- computed by all 32 lanes at once
+    float4 (*s_inv)[32] = (float4 (*)[32]) s_inv_dyn;                         // (dynamic: the static arrays above fill the 48 KB static limit)
     __shared__ float2 s_uv[kTraceThreads];                                    // closest hit so far: u, v
     __shared__ uint2 s_fm[kTraceThreads], s_id[kTraceThreads];                // face, mesh | class << 28 ; lane slot, queue index
     const DScene &sc = p.sc; const WfState &st = w.st;
@@ -136,6 +138,14 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
                     if (!PRIMARY) cp_async_wait_all();
                     __syncwarp();
                     cur ^= 1u; cons = 0; base_c = base_n; cnt_c = cnt_n;
+                    {   // reciprocal directions of the whole batch with full lanes (a refill pass runs at ~6 of 32)
+                        const float4 dd = s_sd[warp][cur][lane];
+                        const float tiny = kTinyDir;
+                        const uint32_t oi = (dd.x >= 0.f ? 1u : 0u) | (dd.y >= 0.f ? 2u : 0u) | (dd.z >= 0.f ? 4u : 0u);
+                        s_inv[warp][lane] = make_float4(1.f / (fabsf(dd.x) > tiny ? dd.x : copysignf(tiny, dd.x)), 1.f / (fabsf(dd.y) > tiny ? dd.y : copysignf(tiny, dd.y)),
+                                                        1.f / (fabsf(dd.z) > tiny ? dd.z : copysignf(tiny, dd.z)), __uint_as_float(oi));
+                        __syncwarp();
+                    }
                     stage_c(); stage_b(); stage_a();
                     if (cnt_c == 0u) exhausted = true;
                 }
@@ -145,11 +155,9 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
                     const float4 o4 = s_so[warp][cur][e], d4 = s_sd[warp][cur][e];
                     const uint32_t sl = s_ss[warp][cur][e];
                     o = f3(o4.x, o4.y, o4.z); d = f3(d4.x, d4.y, d4.z); tbest = o4.w;
-                    const float tiny = kTinyDir;
-                    idx = 1.f / (fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x));
-                    idy = 1.f / (fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y));
-                    idz = 1.f / (fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z));
-                    const uint32_t octinv = (d.x >= 0.f ? 1u : 0u) | (d.y >= 0.f ? 2u : 0u) | (d.z >= 0.f ? 4u : 0u);
+                    const float4 iv = s_inv[warp][e];
+                    idx = iv.x; idy = iv.y; idz = iv.z;
+                    const uint32_t octinv = __float_as_uint(iv.w);
                     const bool any = !PRIMARY && (sl >> 31) != 0u;
                     fl = TF_HAVE | octinv | (any ? TF_ANY : 0u) | ((any && d4.w != 0.f) ? TF_TEX : 0u);
                     s_id[tid] = make_uint2(sl & 0x7fffffffu, base_c + e);
@@ -480,10 +488,18 @@ __global__ void __launch_bounds__(kPacketThreads, B2_PACKET_MINBLOCKS) k_wf_trac
     trace_flush_counters(cnt, p.counters);
 }
 
+constexpr size_t kTraceDynSmem = sizeof(float4) * 32 * kTraceWarps;
+static void trace_smem_opt_in() {       // function attributes belong to the current device: set on every call (one per render)
+    cudaFuncSetAttribute(k_wf_trace<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kTraceDynSmem);
+    cudaFuncSetAttribute(k_wf_trace<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kTraceDynSmem);
+    cudaFuncSetAttribute(k_wf_trace<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kTraceDynSmem);
+    cudaFuncSetAttribute(k_wf_trace<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kTraceDynSmem);
+}
 int wf_trace_blocks(bool count, int sm_count) {
     int occ = 0;
-    if (count) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, false>, kTraceThreads, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<false, false>, kTraceThreads, 0);
+    trace_smem_opt_in();
+    if (count) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<true, false>, kTraceThreads, kTraceDynSmem);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_wf_trace<false, false>, kTraceThreads, kTraceDynSmem);
     static const int tune_blocks = getenv("B2_TRACE_BLOCKS") ? atoi(getenv("B2_TRACE_BLOCKS")) : 0;
     if (tune_blocks > 0) occ = std::min(occ, tune_blocks);
     return occ * sm_count;
@@ -510,8 +526,8 @@ static void launch_trace(bool count, bool primary, int packet_rays, const Render
         if (count) k_wf_trace_packet<true, 2><<<blocks, kPacketThreads, 0, stream>>>(p, w); else k_wf_trace_packet<false, 2><<<blocks, kPacketThreads, 0, stream>>>(p, w);
     } else if (primary && packet_rays == 1) {
         if (count) k_wf_trace_packet<true, 1><<<blocks, kPacketThreads, 0, stream>>>(p, w); else k_wf_trace_packet<false, 1><<<blocks, kPacketThreads, 0, stream>>>(p, w);
-    } else if (count) { if (primary) k_wf_trace<true, true><<<blocks, kTraceThreads, 0, stream>>>(p, w); else k_wf_trace<true, false><<<blocks, kTraceThreads, 0, stream>>>(p, w); }
-    else { if (primary) k_wf_trace<false, true><<<blocks, kTraceThreads, 0, stream>>>(p, w); else k_wf_trace<false, false><<<blocks, kTraceThreads, 0, stream>>>(p, w); }
+    } else if (count) { if (primary) k_wf_trace<true, true><<<blocks, kTraceThreads, kTraceDynSmem, stream>>>(p, w); else k_wf_trace<true, false><<<blocks, kTraceThreads, kTraceDynSmem, stream>>>(p, w); }
+    else { if (primary) k_wf_trace<false, true><<<blocks, kTraceThreads, kTraceDynSmem, stream>>>(p, w); else k_wf_trace<false, false><<<blocks, kTraceThreads, kTraceDynSmem, stream>>>(p, w); }
     wf_tm_end(stream);
 }
 void wf_launch_trace(bool count, bool primary, const RenderParams &p, const WfLaunch &w, int blocks, cudaStream_t stream) {
