@@ -42,7 +42,7 @@ constexpr int kTriQueue = 4;                        // parked leaf-triangle grou
 #endif
 
 // lane flag word
-enum : uint32_t { TF_OCT = 7u, TF_ANY = 8u, TF_TEX = 16u, TF_FOUND = 32u, TF_NQ_SHIFT = 8, TF_NQ_ONE = 1u << 8, TF_NQ_MASK = 7u << 8, TF_HAVE = 1u << 31 };
+enum : uint32_t { TF_OCT = 7u, TF_ANY = 8u, TF_TEX = 16u, TF_FOUND = 32u, TF_NQ_SHIFT = 8, TF_NQ_ONE = 1u << 8, TF_NQ_MASK = 7u << 8, TF_DONE = 1u << 30, TF_HAVE = 1u << 31 };
 
 B2_DEV void cp_async16(void *smem, const void *gmem) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"((uint32_t) __cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
@@ -131,9 +131,31 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
     for (;;) {
         // ---- refill idle lanes from the staged rays (warp converged here)
         const uint32_t idle = __ballot_sync(full, !(fl & TF_HAVE));
-        if (idle && !exhausted) {
+        if (idle) {
             const uint32_t k = __popc(idle);
-            if (k >= w.refill_thresh || idle == full) {
+            if (k >= w.refill_thresh || idle == full || exhausted) {
+                // ---- epilogue of the finished rays (stores only), for all finished lanes of the warp at once
+                if (fl & TF_DONE) {
+                    const uint2 id = s_id[tid];
+                    if (fl & TF_ANY) {
+                        if (!(fl & TF_FOUND)) {         // the emitter sample arrives: the lane's next shade (or the splat) adds fma(a, b, L)
+                            if (fl & TF_TEX) cnt.add(C_TEX);
+                            st.shf[id.x].a.w = 1.f;
+                        }
+                    } else {
+                        const uint2 fm = s_fm[tid]; const float2 uv = s_uv[tid];
+                        const bool found = fm.x != 0xffffffffu;
+                        const uint32_t cls = found ? (fm.y >> 28) : (uint32_t) CLS_MISS;
+                        Elem h;
+                        h.a = make_float4(tbest, uv.x, uv.y, __uint_as_float(fm.x));
+                        h.b = make_float4(__uint_as_float(found ? (fm.y & 0x0fffffffu) : 0xffffffffu), __uint_as_float(cls), 0.f, 0.f);
+                        st256(&st.hit[id.x], h);
+                        st.cls_q[id.y] = (uint8_t) cls;                      // for classify(it), by queue position
+                    }
+                    fl = 0u;
+                }
+            }
+            if (!exhausted && (k >= w.refill_thresh || idle == full)) {
                 if (cons == cnt_c) {            // advance the pipeline: the staged batch becomes current
                     if (!PRIMARY) cp_async_wait_all();
                     __syncwarp();
@@ -232,26 +254,8 @@ __global__ void __launch_bounds__(kTraceThreads, B2_TRACE_MINBLOCKS) k_wf_trace(
                     else { s_pend[(fl & TF_NQ_MASK) >> TF_NQ_SHIFT][tid] = make_uint2(w1.y, thits); fl += TF_NQ_ONE; }
                 }
             }
-            // ---- epilogue of a finished ray: stores only
-            if ((ng.y & 0xff000000u) == 0u && sp == 0 && tg.y == 0u && (fl & TF_NQ_MASK) == 0u) {
-                const uint2 id = s_id[tid];
-                if (fl & TF_ANY) {
-                    if (!(fl & TF_FOUND)) {         // the emitter sample arrives: the lane's next shade (or the splat) adds fma(a, b, L)
-                        if (fl & TF_TEX) cnt.add(C_TEX);
-                        st.shf[id.x].a.w = 1.f;
-                    }
-                } else {
-                    const uint2 fm = s_fm[tid]; const float2 uv = s_uv[tid];
-                    const bool found = fm.x != 0xffffffffu;
-                    const uint32_t cls = found ? (fm.y >> 28) : (uint32_t) CLS_MISS;
-                    Elem h;
-                    h.a = make_float4(tbest, uv.x, uv.y, __uint_as_float(fm.x));
-                    h.b = make_float4(__uint_as_float(found ? (fm.y & 0x0fffffffu) : 0xffffffffu), __uint_as_float(cls), 0.f, 0.f);
-                    st256(&st.hit[id.x], h);
-                    st.cls_q[id.y] = (uint8_t) cls;                      // for classify(it), by queue position
-                }
-                fl = 0u;
-            }
+            // ---- a finished ray: its stores wait for the next refill, where all finished lanes of the warp do them together
+            if ((ng.y & 0xff000000u) == 0u && sp == 0 && tg.y == 0u && (fl & TF_NQ_MASK) == 0u) fl = (fl & (TF_ANY | TF_TEX | TF_FOUND)) | TF_DONE;
         }
     }
     trace_flush_counters(cnt, p.counters);
