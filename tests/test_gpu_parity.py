@@ -285,6 +285,17 @@ def test_render_host_and_errors():
     img, _ = ds.render(seed=0, spp=4)
     np.testing.assert_allclose(image, img.cpu().numpy(), rtol=2e-5, atol=1e-6)
     assert np.isfinite(film).all() and (film[..., 3] > 0).all()
+    # the host film is accumulated into: its upload runs on a second stream and only the splat launches wait for it
+    film2 = film.copy(); ds.render_host(film2, image, seed=0, spp=4)
+    np.testing.assert_allclose(film2, 2.0 * film, rtol=2e-5, atol=1e-6)
+    big = DeviceScene(cornell_box(768, 768, spp=1))                       # a 9.4 MB film against a ~0.5 ms render
+    base = np.random.RandomState(3).uniform(1.0, 2.0, (768, 768, 4)).astype(np.float32)
+    zero = np.zeros_like(base); acc = base.copy()
+    big.render_host(zero, None, seed=5, spp=1); big.render_host(acc, None, seed=5, spp=1)
+    np.testing.assert_allclose(acc - base, zero, rtol=0, atol=2e-5 * float(np.abs(zero).max() + 2.0))
+    for kern in (capi.KERNEL_MEGAKERNEL,):
+        acc2 = base.copy(); big.render_host(acc2, None, seed=5, spp=1, kernel=kern)
+        np.testing.assert_allclose(acc2 - base, zero, rtol=0, atol=2e-5 * float(np.abs(zero).max() + 2.0))
     with pytest.raises(capi.B2Error):
         ds.render(seed=0, spp=6, spp_per_pass=4)             # sample_count must be a multiple of spp_per_pass
     with pytest.raises(capi.B2Error):
