@@ -25,8 +25,9 @@
 // at kStackSize).  Per-ray values that are touched once per ray (lane slot, queue index, u, v, face, mesh) live in
 // shared memory, which keeps the kernel at 64 registers without spills.
 //
-// Epilogue = stores only: a closest ray writes its 32-byte hit record with one 256-bit store (+ the class byte for the
-// counting sort); a shadow ray that arrives sets the `arrived` word of the lane's deferred-NEE record.
+// Epilogue = stores only, done at the next refill by all finished lanes of the warp together: a closest ray writes its 32-byte hit
+// record with one 256-bit store (+ the class byte for the counting sort); a shadow ray that arrives sets the `arrived` word of the
+// lane's deferred-NEE record.  The reciprocal directions of a staged batch are computed once, by all 32 lanes, when it becomes current.
 #include "b2_path.cuh"
 #include "b2_wavefront.cuh"
 
